@@ -1,0 +1,161 @@
+"""
+Tier-1 pin (builder container only): the oracle restatement must reproduce the UNMODIFIED
+reference modules (loaded from /root/reference with oracle/pyg_shim) on identical weights,
+batches and injected reparameterisation noise -- fp64, tolerance 1e-10.
+"""
+import copy
+
+import pytest
+import torch
+
+from oracle import sampler_ref as R
+from oracle.vgpgae_ref import VGPGAERef
+from tests import helpers as H
+from tests.ref_harness import load_reference, quiet
+
+pytestmark = pytest.mark.reference
+
+
+@pytest.fixture(autouse=True)
+def _fp64_sparse_values():
+    load_reference()
+    import torch_sparse
+    old = torch_sparse.DEFAULT_DTYPE
+    torch_sparse.DEFAULT_DTYPE = torch.float64
+    yield
+    torch_sparse.DEFAULT_DTYPE = old
+
+
+def build_reference_module(ref, adata, cfg, conv_layer, node_label_method, n_addon_gp):
+    feat = copy.deepcopy(cfg["features_idx_dict"])
+    with quiet():
+        m = ref.modules.VGPGAE(
+            n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+            n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"],
+            n_addon_gp=n_addon_gp, cat_covariates_embeds_nums=[],
+            n_output_genes=cfg["n_output_genes"],
+            target_rna_decoder_mask=cfg["target_rna_mask"],
+            source_rna_decoder_mask=cfg["source_rna_mask"],
+            features_idx_dict=feat,
+            features_scale_factors=torch.ones(2 * cfg["n_output_genes"]),
+            conv_layer_encoder=conv_layer, encoder_n_attention_heads=cfg["heads"],
+            node_label_method=node_label_method, active_gp_thresh_ratio=0.01,
+            include_cat_covariates_contrastive_loss=False)
+    return m.double()
+
+
+def make_batches(adata, dtype=torch.float64, edge_bs=16, node_bs=8):
+    torch.manual_seed(0)
+    x = H.dense_x(adata, dtype)
+    n = adata.n_obs
+    ei = R.adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
+    splits = R.edge_level_split(ei, n, 0.1)
+    train_mask, _ = R.node_level_split_mask(n, 0.1)
+    nl = R.NodeLoaderRef(x, ei, n, train_mask, node_bs)
+    ll = R.LinkLoaderRef(x, splits["train"].edge_index, n, splits["train"].edge_label_index, edge_bs)
+    return next(iter(nl)), next(iter(ll))
+
+
+@pytest.mark.parametrize("conv_layer,node_label_method,n_addon", [
+    ("gatv2conv", "one-hop-norm", 3),
+    ("gcnconv", "one-hop-sum", 3),
+    ("gatv2conv", "one-hop-attention", 0),
+])
+def test_forward_loss_grads_match_reference(conv_layer, node_label_method, n_addon):
+    ref = load_reference()
+    adata = H.tiny_problem()
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=n_addon, conv_layer=conv_layer,
+                                  node_label_method=node_label_method)
+    torch.manual_seed(1)
+    m = build_reference_module(ref, adata, cfg, conv_layer, node_label_method, n_addon)
+    m.train()
+    # non-trivial biases (PyG zero-initialises them)
+    with torch.no_grad():
+        for k, p in m.named_parameters():
+            if k.endswith("bias"):
+                p.uniform_(-0.1, 0.1)
+    params = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point and
+                                                   not k.endswith(("mask", "running_mean_abs_mu")))
+              for k, v in m.state_dict().items()}
+    orc = VGPGAERef(cfg, params)
+    node_b, edge_b = make_batches(adata)
+    P = cfg["n_prior_gp"] + n_addon
+    g = torch.Generator().manual_seed(5)
+    eps_n = torch.randn(node_b.batch_size, P, generator=g, dtype=torch.float64)
+    eps_e = torch.randn(2 * edge_b.edge_label_index.size(1), P, generator=g, dtype=torch.float64)
+
+    draws = [eps_n, eps_e]
+    real_randn_like = torch.randn_like
+
+    def fake_randn_like(t, *a, **k):
+        return draws.pop(0)
+
+    torch.randn_like = fake_randn_like
+    try:
+        rn = m(data_batch=node_b, decoder="omics")
+        re_ = m(data_batch=edge_b, decoder="graph")
+    finally:
+        torch.randn_like = real_randn_like
+    lam = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lambda_l1_addon=30.,
+               lambda_group_lasso=2., lambda_gene_expr_recon=300., lambda_edge_recon=500000.)
+    # reference indexes params with a None mask -> param[None] (all entries)
+    rl = m.loss(edge_model_output=re_, node_model_output=rn, **lam)
+    rl["optim_loss"].backward()
+
+    on = orc.forward(node_b, "omics", eps=eps_n)
+    oe = orc.forward(edge_b, "graph", eps=eps_e)
+    ol = orc.loss(oe, on, **lam)
+    ol["optim_loss"].backward()
+
+    for k in ("mu", "logstd", "target_rna_nb_means", "source_rna_nb_means"):
+        assert H.rel_err(on[k], rn[k]) < 1e-10, k
+    for k in ("target_rna", "source_rna"):
+        assert H.rel_err(on["node_labels"][k], rn["node_labels"][k]) < 1e-12, k
+    assert H.rel_err(oe["edge_recon_logits"], re_["edge_recon_logits"]) < 1e-10
+    for k, v in rl.items():
+        assert H.rel_err(torch.as_tensor(ol[k]), torch.as_tensor(v)) < 1e-10, k
+    assert H.rel_err(orc.running_mean_abs_mu, m.running_mean_abs_mu) < 1e-12
+    n_checked = 0
+    for k, p in m.named_parameters():
+        if p.grad is None:
+            continue
+        assert params[k].grad is not None, k
+        assert H.rel_err(params[k].grad, p.grad) < 1e-9, k
+        n_checked += 1
+    assert n_checked >= 10
+    # active-GP mask + latent (eval mode)
+    m.eval()
+    orc.training = False
+    assert torch.equal(orc.get_active_gp_mask(), m.get_active_gp_mask())
+    mu_r, std_r = m.get_latent_representation(node_b, only_active_gps=True, return_mu_std=True)
+    mu_o, std_o = orc.get_latent_representation(node_b, only_active_gps=True, return_mu_std=True)
+    assert H.rel_err(mu_o, mu_r) < 1e-10 and H.rel_err(std_o, std_r) < 1e-10
+
+
+def test_only_active_gps_path_matches_reference():
+    ref = load_reference()
+    adata = H.tiny_problem(seed=3)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=3)
+    torch.manual_seed(2)
+    m = build_reference_module(ref, adata, cfg, "gatv2conv", "one-hop-norm", 3)
+    m.train()
+    with torch.no_grad():
+        m.running_mean_abs_mu.copy_(torch.rand(cfg["n_prior_gp"] + 3, dtype=torch.float64) ** 6)
+    params = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    orc = VGPGAERef(cfg, params)
+    node_b, _ = make_batches(adata)
+    P = cfg["n_prior_gp"] + 3
+    eps_n = torch.randn(node_b.batch_size, P, dtype=torch.float64)
+    real = torch.randn_like
+    torch.randn_like = lambda t, *a, **k: eps_n
+    try:
+        with torch.no_grad():
+            rn = m(data_batch=node_b, decoder="omics", use_only_active_gps=True)
+    finally:
+        torch.randn_like = real
+    with torch.no_grad():
+        on = orc.forward(node_b, "omics", use_only_active_gps=True, eps=eps_n)
+    assert on["target_rna_nb_means"].shape == rn["target_rna_nb_means"].shape
+    for k in ("target_rna_nb_means", "source_rna_nb_means"):
+        assert H.rel_err(on[k], rn[k]) < 1e-10, k
+    assert H.rel_err(orc.running_mean_abs_mu, m.running_mean_abs_mu) < 1e-12
