@@ -1,0 +1,424 @@
+// bf16 GEMM on the 5th-gen tensor cores: TMA (cp.async.bulk.tensor) -> 128B-swizzled smem ring
+// -> tcgen05.mma (accumulators in TMEM, double buffered) -> tcgen05.ld epilogue with fused
+// bias / ReLU / gene-program mask / accumulate.  Persistent, one CTA per SM, warp-specialised:
+//   warp 0 : TMA producer          warp 1 : TMEM allocator + MMA issuer (one elected lane)
+//   warps 2-5 : epilogue (TMEM lane quarter = warp_id % 4)
+//   C[M,N] (+)= act(opA(A) * opB(B) + bias) (* mask)
+// A: [M,K] (K-major) or, trans_a, [K,M] (MN-major).  B: [N,K] (K-major) or, trans_b, [K,N].
+// Replaces the cuBLAS call sites nn/encoders.py:179 (fc_l1), PyG GATv2Conv lin_l/lin_r,
+// GCNConv lin, nn/layercomponents.py:77-80 (MaskedLinear) and all their backward GEMMs.
+#include <cuda.h>
+
+#include "common.cuh"
+
+extern void nc_count_launch(int n);
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle-128B atom
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+constexpr int A_STAGE_BYTES = BM * BK * 2;
+
+template <int BN> struct Cfg {
+    static constexpr int B_STAGE_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    static constexpr int STAGES = (BN == 256) ? 4 : 6;
+    static constexpr int TMEM_COLS = 2 * BN;       // two accumulator stages (power of two)
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+struct Epilogue {
+    void* C;
+    int64_t ldc;
+    const float* bias;
+    const float* mask;
+    int64_t ldmask;
+    int c_bf16;
+    int relu;
+    int accumulate;
+};
+
+// ------------------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra.uni WAIT_DONE;\n\t"
+        "bra.uni WAIT_LOOP;\n\t"
+        "WAIT_DONE:\n\t"
+        "}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"((uint64_t)tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// smem matrix descriptor (sm_100 UMMA): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) |
+// version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+// instruction descriptor: D=f32 [4,6)=1, A=bf16 [7,10)=1, B=bf16 [10,13)=1, a_major bit15,
+// b_major bit16 (1 = MN-major), N>>3 [17,23), M>>4 [24,29)
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, bool a_mn, bool b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn ? 1u : 0u) << 15) | ((b_mn ? 1u : 0u) << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------- epilogue helpers
+__device__ __forceinline__ void epi_store_chunk(const Epilogue& e, const uint32_t (&r)[32], int row, int col0,
+                                                int M, int N) {
+    if (row >= M) return;
+    const float* mrow = e.mask ? e.mask + (int64_t)row * e.ldmask : nullptr;
+    if (e.c_bf16) {
+        __nv_bfloat16* crow = (__nv_bfloat16*)e.C + (int64_t)row * e.ldc;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {          // 8 columns (16 B of bf16) per group
+            const int c = col0 + g * 8;
+            if (c >= N) break;
+            float v[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                v[t] = __uint_as_float(r[g * 8 + t]);
+                const int cc = c + t;
+                if (cc < N) {
+                    if (e.bias) v[t] += __ldg(e.bias + cc);
+                    if (e.relu) v[t] = fmaxf(v[t], 0.f);
+                    if (mrow) v[t] *= __ldg(mrow + cc);
+                    if (e.accumulate) v[t] += __bfloat162float(crow[cc]);
+                }
+            }
+            if (c + 7 < N) {
+                uint4 q;
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[0], v[1]), p1 = __floats2bfloat162_rn(v[2], v[3]);
+                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[4], v[5]), p3 = __floats2bfloat162_rn(v[6], v[7]);
+                q.x = *reinterpret_cast<uint32_t*>(&p0); q.y = *reinterpret_cast<uint32_t*>(&p1);
+                q.z = *reinterpret_cast<uint32_t*>(&p2); q.w = *reinterpret_cast<uint32_t*>(&p3);
+                *reinterpret_cast<uint4*>(crow + c) = q;
+            } else {
+                for (int t = 0; t < 8 && c + t < N; ++t) crow[c + t] = __float2bfloat16_rn(v[t]);
+            }
+        }
+    } else {
+        float* crow = (float*)e.C + (int64_t)row * e.ldc;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {          // 4 columns (16 B of fp32) per group
+            const int c = col0 + g * 4;
+            if (c >= N) break;
+            float v[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                v[t] = __uint_as_float(r[g * 4 + t]);
+                const int cc = c + t;
+                if (cc < N) {
+                    if (e.bias) v[t] += __ldg(e.bias + cc);
+                    if (e.relu) v[t] = fmaxf(v[t], 0.f);
+                    if (mrow) v[t] *= __ldg(mrow + cc);
+                    if (e.accumulate) v[t] += crow[cc];
+                }
+            }
+            if (c + 3 < N) {
+                *reinterpret_cast<float4*>(crow + c) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+                for (int t = 0; t < 4 && c + t < N; ++t) crow[c + t] = v[t];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------- the kernel
+template <int BN, bool TA, bool TB>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const Epilogue epi, int M, int N, int K) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + C::STAGES * A_STAGE_BYTES;
+    uint64_t* bars = (uint64_t*)(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* full_bar = bars;
+    uint64_t* empty_bar = bars + C::STAGES;
+    uint64_t* tmem_full = bars + 2 * C::STAGES;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_base_slot = (uint32_t*)(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN;
+    const int num_tiles = num_m * num_n;
+    const int num_kb = (K + BK - 1) / BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmA) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmB) : "memory");
+        for (int s = 0; s < C::STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 128);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_slot)),
+                     "r"((uint32_t)C::TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_base_slot;
+
+    if (warp == 0) {
+        // ===================================================== TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile % num_m) * BM, n0 = (tile / num_m) * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                    uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
+                    uint8_t* sb = smem_b + stage * C::B_STAGE_BYTES;
+                    const int k0 = kb * BK;
+                    if (TA) {
+#pragma unroll
+                        for (int s = 0; s < BM / 64; ++s)
+                            tma_load_2d(sa + s * (BK * 128), &tmA, &full_bar[stage], m0 + s * 64, k0);
+                    } else {
+                        tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+                    }
+                    if (TB) {
+#pragma unroll
+                        for (int s = 0; s < BN / 64; ++s)
+                            tma_load_2d(sb + s * (BK * 128), &tmB, &full_bar[stage], n0 + s * 64, k0);
+                    } else {
+                        tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+                    }
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================== MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(BM, BN, TA, TB);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                tcgen05_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tcgen05_fence_after();
+                    const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
+                    const uint32_t sb = smem_u32(smem_b + stage * C::B_STAGE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        // K-major: +32 B per UMMA_K inside the swizzle atom, SBO = 8 rows * 128 B.
+                        // MN-major: 64-wide slabs LBO = BK*128 B apart, 8-row k-groups SBO = 1024 B apart,
+                        //           +2 k-groups (2048 B) per UMMA_K.
+                        const uint64_t adesc = TA ? make_desc(sa + k * 2048, BK * 128, 1024)
+                                                  : make_desc(sa + k * 32, 16, 1024);
+                        const uint64_t bdesc = TB ? make_desc(sb + k * 2048, BK * 128, 1024)
+                                                  : make_desc(sb + k * 32, 16, 1024);
+                        umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0);
+                    }
+                    umma_commit(&empty_bar[stage]);          // frees the smem slot when the MMAs retire
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tmem_full[acc]);                // accumulator complete
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        // ===================================================== epilogue (warps 2..5)
+        const int q = warp & 3;                              // TMEM lane quarter of this warp
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile % num_m) * BM, n0 = (tile / num_m) * BN;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tcgen05_fence_after();
+            const int row = m0 + q * 32 + lane;
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                if (n0 + c >= N) break;                      // warp-uniform
+                uint32_t r[32];
+                tmem_ld32(t_row + (uint32_t)c, r);
+                epi_store_chunk(epi, r, row, n0 + c, M, N);
+            }
+            tcgen05_fence_before();
+            mbar_arrive(&tmem_empty[acc]);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    tcgen05_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
+                     : "memory");
+    }
+}
+
+// ------------------------------------------------------------------------- host side
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+PFN_encodeTiled get_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (PFN_encodeTiled)p;
+    }
+    return fn;
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements.
+int make_tmap(CUtensorMap* tm, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
+    PFN_encodeTiled fn = get_encode_fn();
+    if (!fn) { nc_set_error("nc_gemm_bf16: cuTensorMapEncodeTiled unavailable (no CUDA driver?)"); return NC_ECUDA; }
+    cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        nc_set_error("nc_gemm_bf16: cuTensorMapEncodeTiled failed (%d) inner=%lld outer=%lld ld=%lld", (int)r,
+                     (long long)inner, (long long)outer, (long long)ld);
+        return NC_ECUDA;
+    }
+    return NC_OK;
+}
+
+template <int BN, bool TA, bool TB>
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epilogue& epi, int M, int N, int K, cudaStream_t s) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_gemm_bf16<BN, TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg<BN>::SMEM_BYTES);
+        if (e != cudaSuccess) { nc_set_error("nc_gemm_bf16: cannot opt in to %d B smem: %s", Cfg<BN>::SMEM_BYTES, cudaGetErrorString(e)); return NC_ECUDA; }
+        attr_set = true;
+    }
+    const int tiles = (int)(nc_cdiv(M, BM) * nc_cdiv(N, BN));
+    const int grid = tiles < nc_num_sms() ? tiles : nc_num_sms();
+    k_gemm_bf16<BN, TA, TB><<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, s>>>(tmA, tmB, epi, M, N, K);
+    nc_count_launch(1);
+    return NC_OK;
+}
+
+}  // namespace
+
+extern "C" int nc_gemm_bf16(const void* A, int64_t lda, int trans_a, const void* B, int64_t ldb, int trans_b,
+                            void* Cp, int c_dtype, int64_t ldc, int32_t M, int32_t N, int32_t K, const float* bias,
+                            int relu, const float* mask, int64_t ldmask, int accumulate, void* stream) {
+    NC_REQUIRE(M >= 0 && N >= 0 && K > 0, NC_ESHAPE, "nc_gemm_bf16: need M,N >= 0 and K > 0 (M=%d N=%d K=%d)", M, N, K);
+    NC_REQUIRE(c_dtype == NC_F32 || c_dtype == NC_BF16, NC_EINVAL, "nc_gemm_bf16: bad c_dtype %d", c_dtype);
+    NC_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)Cp % 16 == 0), NC_EINVAL,
+               "nc_gemm_bf16: A, B and C must be 16-byte aligned");
+    NC_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % (c_dtype == NC_BF16 ? 8 : 4) == 0, NC_EINVAL,
+               "nc_gemm_bf16: lda/ldb must be multiples of 8, ldc of %d (lda=%lld ldb=%lld ldc=%lld)",
+               c_dtype == NC_BF16 ? 8 : 4, (long long)lda, (long long)ldb, (long long)ldc);
+    NC_REQUIRE(ldc >= N && lda >= (trans_a ? M : K) && ldb >= (trans_b ? N : K), NC_ESHAPE,
+               "nc_gemm_bf16: leading dimension too small (M=%d N=%d K=%d lda=%lld ldb=%lld ldc=%lld)", M, N, K,
+               (long long)lda, (long long)ldb, (long long)ldc);
+    if (M == 0 || N == 0) return NC_OK;
+    // BN=256 tiles when they still give every SM a few tiles, else 128-wide tiles
+    const int64_t tiles256 = nc_cdiv(M, BM) * nc_cdiv(N, 256);
+    const bool wide = tiles256 >= 2 * (int64_t)nc_num_sms() || (N % 256 == 0 && tiles256 >= nc_num_sms());
+    const int BNsel = wide ? 256 : 128;
+    CUtensorMap tmA, tmB;
+    int rc;
+    if (trans_a) rc = make_tmap(&tmA, A, M, K, lda, 64, BK);
+    else         rc = make_tmap(&tmA, A, K, M, lda, BK, BM);
+    if (rc) return rc;
+    if (trans_b) rc = make_tmap(&tmB, B, N, K, ldb, 64, BK);
+    else         rc = make_tmap(&tmB, B, K, N, ldb, BK, BNsel);
+    if (rc) return rc;
+    Epilogue epi{Cp, ldc, bias, mask, ldmask, c_dtype == NC_BF16, relu, accumulate};
+    cudaStream_t s = (cudaStream_t)stream;
+#define DISPATCH(BN)                                                                       \
+    do {                                                                                   \
+        if (trans_a && trans_b) rc = launch<BN, true, true>(tmA, tmB, epi, M, N, K, s);    \
+        else if (trans_a) rc = launch<BN, true, false>(tmA, tmB, epi, M, N, K, s);         \
+        else if (trans_b) rc = launch<BN, false, true>(tmA, tmB, epi, M, N, K, s);         \
+        else rc = launch<BN, false, false>(tmA, tmB, epi, M, N, K, s);                     \
+    } while (0)
+    if (BNsel == 256) DISPATCH(256); else DISPATCH(128);
+#undef DISPATCH
+    if (rc) return rc;
+    NC_CHECK_LAUNCH("nc_gemm_bf16");
+    return NC_OK;
+}

@@ -1,0 +1,434 @@
+// Graph helpers, one-hop aggregator SpMM, and feature-store gathers.
+// Reference call sites: nn/aggregators.py:205-213,260-264 (torch_sparse spmm_sum + gcn_norm),
+// data/datasets.py:59-71 + PyG loader x[n_id] slicing, modules/vgpgae.py:598-601.
+#include "common.cuh"
+
+extern void nc_count_launch(int n);
+
+// ============================================================================ gcn-norm weights
+__global__ void k_zero_i32(int32_t* p, int32_t n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = 0;
+}
+
+__global__ void k_degree(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                         int32_t n_nodes, int use_out_degree, int32_t* __restrict__ deg) {
+    int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n_nodes) return;
+    int cnt = 0;
+    for (int e = rowptr[v]; e < rowptr[v + 1]; ++e) {
+        int j = col[e];
+        if (j == v) continue;
+        if (use_out_degree) atomicAdd(&deg[j], 1);
+        else ++cnt;
+    }
+    if (!use_out_degree) deg[v] = cnt;
+}
+
+__global__ void k_norm_weights(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                               int32_t n_rows, const int32_t* __restrict__ deg,
+                               float* __restrict__ w, float* __restrict__ wself) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rows) return;
+    const float di = 1.0f / sqrtf((float)(deg[i] + 1));
+    for (int e = rowptr[i]; e < rowptr[i + 1]; ++e) {
+        int j = col[e];
+        w[e] = (j == i) ? 0.f : (1.0f / sqrtf((float)(deg[j] + 1))) * di;
+    }
+    wself[i] = di * di;
+}
+
+extern "C" int nc_gcn_norm_weights(const int32_t* rowptr, const int32_t* col, int32_t n_nodes,
+                                   int32_t n_rows, int use_out_degree, int32_t* deg_ws, float* w,
+                                   float* wself, void* stream) {
+    NC_REQUIRE(n_nodes >= 0 && n_rows >= 0 && n_rows <= n_nodes, NC_ESHAPE,
+               "nc_gcn_norm_weights: need 0 <= n_rows <= n_nodes (got %d, %d)", n_rows, n_nodes);
+    if (n_nodes == 0) return NC_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int T = 256;
+    k_zero_i32<<<nc_cdiv(n_nodes, T), T, 0, s>>>(deg_ws, n_nodes);
+    k_degree<<<nc_cdiv(n_nodes, T), T, 0, s>>>(rowptr, col, n_nodes, use_out_degree, deg_ws);
+    if (n_rows > 0) k_norm_weights<<<nc_cdiv(n_rows, T), T, 0, s>>>(rowptr, col, n_rows, deg_ws, w, wself);
+    nc_count_launch(n_rows > 0 ? 3 : 2);
+    NC_CHECK_LAUNCH("nc_gcn_norm_weights");
+    return NC_OK;
+}
+
+// ============================================================================ reverse CSR
+__global__ void k_rev_count(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                            int32_t n_rows, int add_self, int32_t* __restrict__ cnt) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rows) return;
+    for (int e = rowptr[i]; e < rowptr[i + 1]; ++e) {
+        int j = col[e];
+        if (j != i) atomicAdd(&cnt[j], 1);
+    }
+    if (add_self) atomicAdd(&cnt[i], 1);
+}
+
+// single-CTA exclusive scan: out[0..n] (n+1 entries), in[0..n)
+__global__ void k_exclusive_scan_i32(const int32_t* __restrict__ in, int32_t* __restrict__ out, int32_t n) {
+    __shared__ int32_t warp_tot[32];
+    __shared__ int32_t carry_s;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += blockDim.x) {
+        int i = base + tid;
+        int v = (i < n) ? in[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_tot[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            int t = (lane < (blockDim.x >> 5)) ? warp_tot[lane] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(0xffffffffu, t, o);
+                if (lane >= o) t += y;
+            }
+            warp_tot[lane] = t;
+        }
+        __syncthreads();
+        int carry = carry_s;
+        int excl = carry + (warp > 0 ? warp_tot[warp - 1] : 0) + x - v;
+        if (i < n) out[i] = excl;
+        __syncthreads();
+        if (tid == blockDim.x - 1) carry_s = carry + warp_tot[(blockDim.x >> 5) - 1];
+        __syncthreads();
+    }
+    if (tid == 0) out[n] = carry_s;
+}
+
+__global__ void k_rev_fill(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                           int32_t n_rows, int add_self, const int32_t* __restrict__ rptr,
+                           int32_t* __restrict__ cursor, int32_t* __restrict__ rdst,
+                           int32_t* __restrict__ rslot) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rows) return;
+    for (int e = rowptr[i]; e < rowptr[i + 1]; ++e) {
+        int j = col[e];
+        if (j == i) continue;
+        int pos = rptr[j] + atomicAdd(&cursor[j], 1);
+        rdst[pos] = i;
+        rslot[pos] = e + i;
+    }
+    if (add_self) {
+        int pos = rptr[i] + atomicAdd(&cursor[i], 1);
+        rdst[pos] = i;
+        rslot[pos] = rowptr[i + 1] + i;
+    }
+}
+
+__global__ void k_rev_sort(const int32_t* __restrict__ rptr, int32_t n_nodes,
+                           int32_t* __restrict__ rdst, int32_t* __restrict__ rslot) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_nodes) return;
+    const int lo = rptr[j], hi = rptr[j + 1];
+    for (int a = lo + 1; a < hi; ++a) {           // insertion sort by slot (segments are tiny)
+        int s = rslot[a], d = rdst[a], b = a - 1;
+        while (b >= lo && rslot[b] > s) {
+            rslot[b + 1] = rslot[b];
+            rdst[b + 1] = rdst[b];
+            --b;
+        }
+        rslot[b + 1] = s;
+        rdst[b + 1] = d;
+    }
+}
+
+extern "C" int nc_reverse_csr(const int32_t* rowptr, const int32_t* col, int32_t n_nodes,
+                              int32_t n_rows, int add_self, int32_t* rptr, int32_t* rdst,
+                              int32_t* rslot, int32_t* cursor_ws, void* stream) {
+    NC_REQUIRE(n_nodes >= 0 && n_rows >= 0 && n_rows <= n_nodes, NC_ESHAPE,
+               "nc_reverse_csr: need 0 <= n_rows <= n_nodes (got %d, %d)", n_rows, n_nodes);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int T = 256;
+    if (n_nodes > 0) k_zero_i32<<<nc_cdiv(n_nodes, T), T, 0, s>>>(cursor_ws, n_nodes);
+    if (n_rows > 0) k_rev_count<<<nc_cdiv(n_rows, T), T, 0, s>>>(rowptr, col, n_rows, add_self, cursor_ws);
+    k_exclusive_scan_i32<<<1, 1024, 0, s>>>(cursor_ws, rptr, n_nodes);
+    if (n_nodes > 0) k_zero_i32<<<nc_cdiv(n_nodes, T), T, 0, s>>>(cursor_ws, n_nodes);
+    if (n_rows > 0) {
+        k_rev_fill<<<nc_cdiv(n_rows, T), T, 0, s>>>(rowptr, col, n_rows, add_self, rptr, cursor_ws, rdst, rslot);
+        k_rev_sort<<<nc_cdiv(n_nodes, T), T, 0, s>>>(rptr, n_nodes, rdst, rslot);
+    }
+    nc_count_launch(6);
+    NC_CHECK_LAUNCH("nc_reverse_csr");
+    return NC_OK;
+}
+
+// ============================================================================ dense-x CSR SpMM
+// grid = (n_rows, column chunks); block = 128 threads; each thread owns VPT float4 vectors.
+constexpr int SPMM_T = 128;
+constexpr int SPMM_VPT = 2;
+constexpr int SPMM_CHUNK = SPMM_T * 4 * SPMM_VPT;   // 1024 columns per CTA
+constexpr int SPMM_STAGE = 128;                      // edges staged in smem per pass
+
+template <typename TX, typename TO, bool VEC>
+__global__ void __launch_bounds__(SPMM_T)
+k_spmm_csr(const TX* __restrict__ x, int64_t ldx, int32_t n_cols,
+           const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+           const float* __restrict__ w, const float* __restrict__ wself, int skip_self,
+           TO* __restrict__ out, int64_t ldo) {
+    __shared__ int32_t s_col[SPMM_STAGE];
+    __shared__ float s_w[SPMM_STAGE];
+    const int i = blockIdx.x;
+    const int c_base = blockIdx.y * SPMM_CHUNK;
+    const int tid = threadIdx.x;
+    float4 acc[SPMM_VPT];
+#pragma unroll
+    for (int v = 0; v < SPMM_VPT; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int e0 = rowptr[i], e1 = rowptr[i + 1];
+    const bool has_self = (wself != nullptr);
+    const int total = (e1 - e0) + (has_self ? 1 : 0);
+    for (int base = 0; base < total; base += SPMM_STAGE) {
+        const int n_here = min(SPMM_STAGE, total - base);
+        __syncthreads();
+        if (tid < n_here) {
+            int t = base + tid;
+            int j;
+            float wt;
+            if (t < e1 - e0) {
+                j = col[e0 + t];
+                wt = w ? w[e0 + t] : 1.f;
+                if (skip_self && j == i) wt = 0.f;
+            } else {
+                j = i;
+                wt = wself[i];
+            }
+            s_col[tid] = j;
+            s_w[tid] = wt;
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int t = 0; t < n_here; ++t) {
+            const float wt = s_w[t];
+            if (wt == 0.f) continue;
+            const TX* xr = x + (int64_t)s_col[t] * ldx;
+#pragma unroll
+            for (int v = 0; v < SPMM_VPT; ++v) {
+                const int c = c_base + (v * SPMM_T + tid) * 4;
+                if (VEC) {
+                    if (c + 3 < n_cols) {
+                        float4 q = Elem<TX>::ld4(xr + c);
+                        acc[v].x += wt * q.x; acc[v].y += wt * q.y;
+                        acc[v].z += wt * q.z; acc[v].w += wt * q.w;
+                        continue;
+                    }
+                }
+                if (c < n_cols) acc[v].x += wt * Elem<TX>::ld(xr + c);
+                if (c + 1 < n_cols) acc[v].y += wt * Elem<TX>::ld(xr + c + 1);
+                if (c + 2 < n_cols) acc[v].z += wt * Elem<TX>::ld(xr + c + 2);
+                if (c + 3 < n_cols) acc[v].w += wt * Elem<TX>::ld(xr + c + 3);
+            }
+        }
+    }
+    TO* orow = out + (int64_t)i * ldo;
+#pragma unroll
+    for (int v = 0; v < SPMM_VPT; ++v) {
+        const int c = c_base + (v * SPMM_T + tid) * 4;
+        if (VEC && c + 3 < n_cols) {
+            Elem<TO>::st4(orow + c, acc[v]);
+        } else {
+            if (c < n_cols) Elem<TO>::st(orow + c, acc[v].x);
+            if (c + 1 < n_cols) Elem<TO>::st(orow + c + 1, acc[v].y);
+            if (c + 2 < n_cols) Elem<TO>::st(orow + c + 2, acc[v].z);
+            if (c + 3 < n_cols) Elem<TO>::st(orow + c + 3, acc[v].w);
+        }
+    }
+}
+
+template <typename TX, typename TO>
+static int launch_spmm(const void* x, int64_t ldx, int32_t n_cols, const int32_t* rowptr,
+                       const int32_t* col, const float* w, const float* wself, int skip_self,
+                       int32_t n_rows, void* out, int64_t ldo, cudaStream_t s) {
+    const size_t ax = sizeof(TX) * 4, ao = sizeof(TO) * 4;
+    const bool vec = (ldx % 4 == 0) && (ldo % 4 == 0) && ((uintptr_t)x % ax == 0) && ((uintptr_t)out % ao == 0);
+    dim3 grid(n_rows, (unsigned)nc_cdiv(n_cols, SPMM_CHUNK));
+    if (vec)
+        k_spmm_csr<TX, TO, true><<<grid, SPMM_T, 0, s>>>((const TX*)x, ldx, n_cols, rowptr, col, w, wself, skip_self, (TO*)out, ldo);
+    else
+        k_spmm_csr<TX, TO, false><<<grid, SPMM_T, 0, s>>>((const TX*)x, ldx, n_cols, rowptr, col, w, wself, skip_self, (TO*)out, ldo);
+    nc_count_launch(1);
+    return 0;
+}
+
+extern "C" int nc_spmm_csr(const void* x, int x_dtype, int64_t ldx, int32_t n_cols,
+                           const int32_t* rowptr, const int32_t* col, const float* w,
+                           const float* wself, int skip_self, int32_t n_rows, void* out,
+                           int out_dtype, int64_t ldo, void* stream) {
+    NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldx >= n_cols && ldo >= n_cols, NC_ESHAPE,
+               "nc_spmm_csr: bad shape n_rows=%d n_cols=%d ldx=%lld ldo=%lld", n_rows, n_cols,
+               (long long)ldx, (long long)ldo);
+    if (n_rows == 0) return NC_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (x_dtype == NC_F32 && out_dtype == NC_F32)
+        launch_spmm<float, float>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+    else if (x_dtype == NC_BF16 && out_dtype == NC_F32)
+        launch_spmm<__nv_bfloat16, float>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+    else if (x_dtype == NC_BF16 && out_dtype == NC_BF16)
+        launch_spmm<__nv_bfloat16, __nv_bfloat16>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+    else if (x_dtype == NC_F32 && out_dtype == NC_BF16)
+        launch_spmm<float, __nv_bfloat16>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+    else
+        NC_REQUIRE(false, NC_EINVAL, "nc_spmm_csr: unknown dtype %d/%d", x_dtype, out_dtype);
+    NC_CHECK_LAUNCH("nc_spmm_csr");
+    return NC_OK;
+}
+
+// ============================================================================ CSR-store SpMM
+// One CTA per output row; the output row is staged in shared memory (n_cols floats) and the
+// neighbours' sparse count rows are accumulated into it with shared-memory atomics.
+constexpr int STORE_T = 256;
+
+__global__ void __launch_bounds__(STORE_T)
+k_spmm_csr_store(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict__ x_col,
+                 const float* __restrict__ x_val, int32_t n_cols, const int32_t* __restrict__ n_id,
+                 const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                 const float* __restrict__ w, const float* __restrict__ wself, int skip_self,
+                 float* __restrict__ out, int64_t ldo) {
+    extern __shared__ float s_row[];
+    const int i = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int c = tid; c < n_cols; c += STORE_T) s_row[c] = 0.f;
+    __syncthreads();
+    const int e0 = rowptr[i], e1 = rowptr[i + 1];
+    const int total = (e1 - e0) + (wself ? 1 : 0);
+    for (int t = warp; t < total; t += STORE_T / 32) {
+        int j;
+        float wt;
+        if (t < e1 - e0) {
+            j = col[e0 + t];
+            wt = w ? w[e0 + t] : 1.f;
+            if (skip_self && j == i) wt = 0.f;
+        } else {
+            j = i;
+            wt = wself[i];
+        }
+        if (wt == 0.f) continue;
+        const int64_t g = n_id ? (int64_t)n_id[j] : (int64_t)j;
+        const int64_t p0 = x_rowptr[g], p1 = x_rowptr[g + 1];
+        for (int64_t p = p0 + lane; p < p1; p += 32)
+            atomicAdd(&s_row[__ldg(x_col + p)], wt * __ldg(x_val + p));
+    }
+    __syncthreads();
+    float* orow = out + (int64_t)i * ldo;
+    for (int c = tid; c < n_cols; c += STORE_T) orow[c] = s_row[c];
+}
+
+extern "C" int nc_spmm_csr_store(const int64_t* x_rowptr, const int32_t* x_col, const float* x_val,
+                                 int32_t n_cols, const int32_t* n_id, const int32_t* rowptr,
+                                 const int32_t* col, const float* w, const float* wself,
+                                 int skip_self, int32_t n_rows, float* out, int64_t ldo,
+                                 void* stream) {
+    NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldo >= n_cols, NC_ESHAPE,
+               "nc_spmm_csr_store: bad shape n_rows=%d n_cols=%d ldo=%lld", n_rows, n_cols, (long long)ldo);
+    const size_t smem = (size_t)n_cols * sizeof(float);
+    NC_REQUIRE(smem <= 200 * 1024, NC_EUNSUPPORTED,
+               "nc_spmm_csr_store: n_cols=%d needs %zu B of shared memory (> 200 KiB)", n_cols, smem);
+    if (n_rows == 0) return NC_OK;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_spmm_csr_store, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    k_spmm_csr_store<<<n_rows, STORE_T, smem, (cudaStream_t)stream>>>(
+        x_rowptr, x_col, x_val, n_cols, n_id, rowptr, col, w, wself, skip_self, out, ldo);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_spmm_csr_store");
+    return NC_OK;
+}
+
+// ============================================================================ row gathers
+template <typename TO>
+__global__ void __launch_bounds__(256)
+k_csr_gather_rows(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict__ x_col,
+                  const float* __restrict__ x_val, int32_t n_cols, const int32_t* __restrict__ n_id,
+                  int apply_log1p, TO* __restrict__ out, int64_t ldo) {
+    extern __shared__ float s_row[];
+    const int r = blockIdx.x, tid = threadIdx.x;
+    const int width = (int)ldo;
+    for (int c = tid; c < width; c += 256) s_row[c] = 0.f;
+    __syncthreads();
+    const int64_t g = n_id ? (int64_t)n_id[r] : (int64_t)r;
+    const int64_t p0 = x_rowptr[g], p1 = x_rowptr[g + 1];
+    for (int64_t p = p0 + tid; p < p1; p += 256) {
+        float v = __ldg(x_val + p);
+        s_row[__ldg(x_col + p)] = apply_log1p ? logf(1.0f + v) : v;
+    }
+    __syncthreads();
+    TO* orow = out + (int64_t)r * ldo;
+    if ((width & 3) == 0 && ((uintptr_t)orow % (sizeof(TO) * 4) == 0)) {
+        for (int c = tid * 4; c < width; c += 256 * 4)
+            Elem<TO>::st4(orow + c, make_float4(s_row[c], s_row[c + 1], s_row[c + 2], s_row[c + 3]));
+    } else {
+        for (int c = tid; c < width; c += 256) Elem<TO>::st(orow + c, s_row[c]);
+    }
+}
+
+extern "C" int nc_csr_gather_rows(const int64_t* x_rowptr, const int32_t* x_col, const float* x_val,
+                                  int32_t n_cols, const int32_t* n_id, int32_t n_rows,
+                                  int apply_log1p, void* out, int out_dtype, int64_t ldo,
+                                  void* stream) {
+    NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldo >= n_cols, NC_ESHAPE,
+               "nc_csr_gather_rows: bad shape n_rows=%d n_cols=%d ldo=%lld", n_rows, n_cols, (long long)ldo);
+    const size_t smem = (size_t)ldo * sizeof(float);
+    NC_REQUIRE(smem <= 200 * 1024, NC_EUNSUPPORTED,
+               "nc_csr_gather_rows: ldo=%lld needs %zu B of shared memory (> 200 KiB)", (long long)ldo, smem);
+    if (n_rows == 0) return NC_OK;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_csr_gather_rows<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(k_csr_gather_rows<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (out_dtype == NC_F32)
+        k_csr_gather_rows<float><<<n_rows, 256, smem, s>>>(x_rowptr, x_col, x_val, n_cols, n_id, apply_log1p, (float*)out, ldo);
+    else if (out_dtype == NC_BF16)
+        k_csr_gather_rows<__nv_bfloat16><<<n_rows, 256, smem, s>>>(x_rowptr, x_col, x_val, n_cols, n_id, apply_log1p, (__nv_bfloat16*)out, ldo);
+    else
+        NC_REQUIRE(false, NC_EINVAL, "nc_csr_gather_rows: unknown dtype %d", out_dtype);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_csr_gather_rows");
+    return NC_OK;
+}
+
+template <typename TO>
+__global__ void __launch_bounds__(256)
+k_dense_gather_rows(const float* __restrict__ x, int64_t ldx, int32_t n_cols,
+                    const int32_t* __restrict__ n_id, int apply_log1p, TO* __restrict__ out, int64_t ldo) {
+    const int r = blockIdx.x;
+    const int64_t g = n_id ? (int64_t)n_id[r] : (int64_t)r;
+    const float* xr = x + g * ldx;
+    TO* orow = out + (int64_t)r * ldo;
+    for (int c = threadIdx.x; c < (int)ldo; c += 256) {
+        float v = 0.f;
+        if (c < n_cols) {
+            v = __ldg(xr + c);
+            if (apply_log1p) v = logf(1.0f + v);
+        }
+        Elem<TO>::st(orow + c, v);
+    }
+}
+
+extern "C" int nc_dense_gather_rows(const float* x, int64_t ldx, int32_t n_cols, const int32_t* n_id,
+                                    int32_t n_rows, int apply_log1p, void* out, int out_dtype,
+                                    int64_t ldo, void* stream) {
+    NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldo >= n_cols && ldx >= n_cols, NC_ESHAPE,
+               "nc_dense_gather_rows: bad shape n_rows=%d n_cols=%d", n_rows, n_cols);
+    if (n_rows == 0) return NC_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (out_dtype == NC_F32)
+        k_dense_gather_rows<float><<<n_rows, 256, 0, s>>>(x, ldx, n_cols, n_id, apply_log1p, (float*)out, ldo);
+    else if (out_dtype == NC_BF16)
+        k_dense_gather_rows<__nv_bfloat16><<<n_rows, 256, 0, s>>>(x, ldx, n_cols, n_id, apply_log1p, (__nv_bfloat16*)out, ldo);
+    else
+        NC_REQUIRE(false, NC_EINVAL, "nc_dense_gather_rows: unknown dtype %d", out_dtype);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_dense_gather_rows");
+    return NC_OK;
+}

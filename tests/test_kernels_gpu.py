@@ -1,0 +1,153 @@
+"""GPU parity of the individual kernels (through the C ABI) against the CPU oracle / fp64 torch."""
+import numpy as np
+import pytest
+import torch
+
+from nichecompass_b200 import ops
+from nichecompass_b200.data.store import CSRFeatureStore
+from oracle import pyg_semantics as S
+from oracle import sampler_ref as R
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _subgraph(n_cells=300, n_genes=50, seed=0, node_bs=24):
+    adata = H.tiny_problem(n_cells=n_cells, n_genes=n_genes, k=5, seed=seed)
+    torch.manual_seed(seed)
+    x = H.dense_x(adata)
+    ei = R.adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
+    mask = torch.ones(n_cells, dtype=torch.bool)
+    b = next(iter(R.NodeLoaderRef(x, ei, n_cells, mask, node_bs)))
+    return adata, b
+
+
+@pytest.mark.parametrize("n_genes", [50, 1037])
+@pytest.mark.parametrize("mode", ["norm", "sum"])
+def test_aggregator_spmm_matches_oracle(mode, n_genes):
+    adata, b = _subgraph(n_genes=n_genes)
+    n_sub = b.x.size(0)
+    ref = (S.one_hop_gcn_norm_aggregate if mode == "norm" else S.one_hop_sum_aggregate)(
+        b.x.double(), b.edge_index)[0]
+    ei = b.edge_index.to(DEV)
+    rowptr, col = ops.coo_to_dst_csr(ei, n_sub)
+    x = b.x.to(DEV)
+    if mode == "norm":
+        w, wself = ops.gcn_norm_weights(rowptr, col, n_sub, n_sub, use_out_degree=True)
+        out = ops.spmm_csr(x, rowptr, col, w, wself, True, n_sub)
+    else:
+        out = ops.spmm_csr(x, rowptr, col, None, None, False, n_sub)
+    assert H.rel_err(out, ref) < 1e-6
+    # only the seed rows (what VGPGAE consumes)
+    nb = b.batch_size
+    if mode == "norm":
+        out_b = ops.spmm_csr(x, rowptr, col, w, wself, True, nb)
+        assert torch.equal(out_b, out[:nb])
+    # the same aggregation straight from the CSR count store
+    store = CSRFeatureStore.from_scipy(adata.X, DEV)
+    n_id = b.n_id.to(DEV, torch.int32)
+    if mode == "norm":
+        out_s = ops.spmm_csr_store(store, n_id, rowptr, col, w, wself, True, nb)
+    else:
+        out_s = ops.spmm_csr_store(store, n_id, rowptr, col, None, None, False, nb)
+    assert H.rel_err(out_s, ref[:nb]) < 1e-6
+
+
+def test_spmm_bf16_and_unaligned():
+    _, b = _subgraph(n_genes=61)
+    n_sub = b.x.size(0)
+    rowptr, col = ops.coo_to_dst_csr(b.edge_index.to(DEV), n_sub)
+    xb = b.x.to(DEV).to(torch.bfloat16)
+    ref = S.one_hop_sum_aggregate(xb.float().cpu().double(), b.edge_index)[0]
+    out = ops.spmm_csr(xb, rowptr, col, None, None, False, n_sub)
+    assert H.rel_err(out, ref) < 1e-6
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gather_rows(dtype):
+    adata, b = _subgraph(n_genes=77)
+    store = CSRFeatureStore.from_scipy(adata.X, DEV)
+    n_id = b.n_id.to(DEV, torch.int32)
+    ld = ops.pad8(77)
+    out = ops.csr_gather_rows(store, n_id, n_id.numel(), True, dtype, ld)
+    ref = torch.log(1 + b.x)
+    tol = 1e-6 if dtype == torch.float32 else 4e-3
+    assert H.rel_err(out[:, :77].float(), ref) < tol
+    assert float(out[:, 77:].float().abs().max()) == 0.0
+    xd = torch.tensor(np.asarray(adata.X.todense()), dtype=torch.float32, device=DEV)
+    out2 = ops.dense_gather_rows(xd, n_id, n_id.numel(), True, dtype, ld)
+    assert torch.equal(out2, out)
+    out3 = ops.csr_gather_rows(store, None, 10, False, torch.float32)
+    assert torch.equal(out3.cpu(), H.dense_x(adata)[:10])
+
+
+def test_reverse_csr():
+    _, b = _subgraph()
+    n_sub, nb = b.x.size(0), b.batch_size
+    rowptr, col = ops.coo_to_dst_csr(b.edge_index.to(DEV), n_sub)
+    rptr, rdst, rslot = ops.reverse_csr(rowptr, col, n_sub, nb, True)
+    rp, cl = rowptr.cpu().tolist(), col.cpu().tolist()
+    expect = {j: [] for j in range(n_sub)}
+    for i in range(nb):
+        for e in range(rp[i], rp[i + 1]):
+            if cl[e] != i:
+                expect[cl[e]].append((e + i, i))
+        expect[i].append((rp[i + 1] + i, i))
+    rptr, rdst, rslot = rptr.cpu().tolist(), rdst.cpu().tolist(), rslot.cpu().tolist()
+    for j in range(n_sub):
+        got = [(rslot[p], rdst[p]) for p in range(rptr[j], rptr[j + 1])]
+        assert got == sorted(expect[j]), j
+    assert rptr[n_sub] == sum(len(v) for v in expect.values())
+
+
+@pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
+def test_gemm_f32(ta, tb):
+    g = torch.Generator().manual_seed(0)
+    M, N, K = 150, 93, 70
+    A = torch.randn((K, M) if ta else (M, K), generator=g)
+    B = torch.randn((K, N) if tb else (N, K), generator=g)
+    bias = torch.randn(N, generator=g)
+    mask = (torch.rand(M, N, generator=g) > 0.5).float()
+    ref = torch.relu((A.t() if ta else A).double() @ (B if tb else B.t()).double() + bias.double()) * mask.double()
+    out = ops.gemm(A.to(DEV), B.to(DEV), ta, tb, bias=bias.to(DEV), relu=True, mask=mask.to(DEV))
+    assert H.rel_err(out, ref) < 1e-6
+    out2 = ops.gemm(A.to(DEV), B.to(DEV), ta, tb, out=out.clone(), accumulate=True)
+    ref2 = ref + (A.t() if ta else A).double() @ (B if tb else B.t()).double()
+    assert H.rel_err(out2, ref2) < 1e-6
+
+
+@pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("shape", [(128, 128, 64), (300, 200, 136), (1000, 1608, 520), (64, 5000, 1600)])
+def test_gemm_bf16_tcgen05(ta, tb, shape):
+    g = torch.Generator().manual_seed(1)
+    M, N, K = shape
+    def mk(r, c):
+        buf = torch.randn(r, ops.pad8(c), generator=g).to(torch.bfloat16)
+        return buf.to(DEV)[:, :c]
+    A = mk(K, M) if ta else mk(M, K)
+    B = mk(K, N) if tb else mk(N, K)
+    bias = torch.randn(N, generator=g).to(DEV)
+    Ad = (A.t() if ta else A).double().cpu()
+    Bd = (B if tb else B.t()).double().cpu()
+    ref = Ad @ Bd
+    out = ops.gemm(A, B, ta, tb, out_dtype=torch.float32)
+    assert H.rel_err(out, ref) < 1e-5, "plain"
+    out_b = ops.gemm(A, B, ta, tb, bias=bias, relu=True)
+    ref_b = torch.relu(ref + bias.double().cpu())
+    assert out_b.dtype == torch.bfloat16
+    assert H.rel_err(out_b.float(), ref_b) < 6e-3, "bias+relu bf16"
+    mask = (torch.rand(M, N, generator=g) > 0.5).float().to(DEV)
+    acc = out.clone()
+    ops.gemm(A, B, ta, tb, mask=mask, out=acc, accumulate=True)
+    assert H.rel_err(acc, ref + ref * mask.double().cpu()) < 1e-5, "mask+accumulate"
+
+
+def test_gemm_bf16_large_persistent():
+    g = torch.Generator().manual_seed(2)
+    M, N, K = 4100, 3080, 1600
+    A = torch.randn(M, K, generator=g).to(torch.bfloat16).to(DEV)
+    B = torch.randn(N, K, generator=g).to(torch.bfloat16).to(DEV)
+    out = ops.gemm(A, B, out_dtype=torch.float32)
+    ref = A.float() @ B.float().t()          # torch fp32 reference of the same op
+    assert H.rel_err(out, ref) < 1e-4
