@@ -70,12 +70,13 @@ int nc_reverse_csr(const int32_t* rowptr, const int32_t* col, int32_t n_nodes, i
  * (nn/aggregators.py:205-213 gcn-norm, :260-264 sum; torch_sparse spmm_sum)
  * out[i, :] = sum_e w[e] * x[col[e], :]  (+ wself[i] * x[i, :]),  i < n_rows.
  * w == NULL -> all ones; wself == NULL -> no extra self term; skip_self != 0 drops entries
- * with col[e] == i.  x: [*, ldx] of x_dtype; out: [n_rows, ldo] of out_dtype.
+ * with col[e] == i; bias (fp32 [n_cols], nullable) is added to every output row.
+ * x: [*, ldx] of x_dtype; out: [n_rows, ldo] of out_dtype.
  * Also used for GCNConv message passing (PyG GCNConv.propagate) and its backward.        */
 int nc_spmm_csr(const void* x, int x_dtype, int64_t ldx, int32_t n_cols,
                 const int32_t* rowptr, const int32_t* col, const float* w, const float* wself,
-                int skip_self, int32_t n_rows, void* out, int out_dtype, int64_t ldo,
-                void* stream);
+                const float* bias, int skip_self, int32_t n_rows, void* out, int out_dtype,
+                int64_t ldo, void* stream);
 
 /* Same aggregation read straight from the HBM-resident CSR count store (no dense x):
  * out[i, :] = sum_e w[e] * X[n_id[col[e]], :] (+ wself[i] * X[n_id[i], :]), fp32 out.
@@ -116,6 +117,118 @@ int nc_gemm_bf16(const void* A, int64_t lda, int trans_a, const void* B, int64_t
                  int trans_b, void* C, int c_dtype, int64_t ldc, int32_t M, int32_t N,
                  int32_t K, const float* bias, int relu, const float* mask, int64_t ldmask,
                  int accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused GATv2 edge kernels (PyG GATv2Conv.forward message passing; nn/encoders.py:124-140,
+ * 197-207): gather x_l[j] + x_r[i] -> LeakyReLU -> att dot -> segment
+ * softmax over the incoming edges of i -> alpha-weighted sum of x_l[j] -> mean over heads
+ * -> + bias, for all convs of the encoder in one launch.
+ * xl [n_src, ld], xr [n_dst, ld]: lin_l / lin_r outputs of all convs side by side; conv c
+ * head h occupies columns [off_c + h*C_c, off_c + (h+1)*C_c); att uses the same indexing.
+ * seg: int32[4*n_conv] = {off_c, C_c, out_off_c, 0} on the device, seg_host the same on the
+ * host (alignment checks).  Self loops are re-normalised as PyG does: CSR entries with
+ * col == i are ignored and one self edge is appended per target.  max_deg >= the longest
+ * CSR row among the n_dst targets.
+ * alpha [(rowptr[n_dst] + n_dst) * n_conv * H]: attention coefficient of "slot" s (entry e of
+ * row i -> s = e + i, appended self edge -> s = rowptr[i+1] + i), saved for the backward.
+ * out [n_dst, ldo] fp32, conv c written at columns [out_off_c, out_off_c + C_c).           */
+int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
+                 const float* bias, const int32_t* rowptr, const int32_t* col, int32_t n_dst,
+                 const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
+                 int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
+                 void* stream);
+/* Backward of the above.  rptr/rdst/rslot: nc_reverse_csr(..., add_self=1) of the same graph.
+ * dxl [n_src, ld] and dxr [n_dst, ld] (same dtype as xl) are fully overwritten; datt (indexed
+ * like att) and dbias (indexed like out columns, may be NULL) are ACCUMULATED with atomics.
+ * ds_ws: fp32 workspace of the size of alpha.                                               */
+int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
+                 const int32_t* rowptr, const int32_t* col, int32_t n_dst, int32_t n_src,
+                 const int32_t* rptr, const int32_t* rdst, const int32_t* rslot,
+                 const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
+                 int32_t max_deg, float neg_slope, const float* dout, int64_t ldo,
+                 const float* alpha, float* ds_ws, void* dxl, void* dxr, float* datt,
+                 float* dbias, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Decoder epilogue + negative-binomial loss, forward value and gradients in one pass
+ * (nn/layers.py:143 softmax over ALL features, nn/decoders.py:168 exp(log_lib)*softmax,
+ * modules/vgpgae.py:714-749 column selection + library size over selected columns,
+ * modules/losses.py:169-212 NB log-likelihood, theta = exp(theta_param)).
+ * logits [n_rows, ldl], x [n_rows, ldx] raw labels over all F features, sel[F] != 0 marks the
+ * reconstructed columns.  loss_sum += sum_rows sum_sel -ll (fp64; the caller multiplies by
+ * `scale` = lambda / n_rows); dlogits = scale * d(sum -ll)/dlogits; dtheta += scale * ...;
+ * means (nullable) receives exp(log_lib)*softmax over all F columns.                       */
+int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x, int64_t ldx,
+                     const uint8_t* sel, const float* theta_param, int32_t n_rows, int32_t F,
+                     float scale, float* means, int64_t ldm, double* loss_sum, float* dlogits,
+                     int64_t lddl, float* dtheta, void* stream);
+
+/* Cosine-similarity graph decoder (nn/decoders.py:56-62, nn/utils.py:8-36): rows [0,n_pairs)
+ * of z against rows [n_pairs, 2*n_pairs).  norms: fp32[2*n_pairs] saved for the backward.   */
+int nc_cosine_fwd(const float* z, int64_t ldz, int32_t P, int32_t n_pairs, float* logits,
+                  float* norms, void* stream);
+int nc_cosine_bwd(const float* z, int64_t ldz, int32_t P, int32_t n_pairs, const float* logits,
+                  const float* norms, const float* dlogits, float* dz, int64_t lddz,
+                  void* stream);
+/* Weighted BCE-with-logits, pos_weight = #neg/#pos over the included edges
+ * (modules/losses.py:123-166); loss_out = mean loss, dlogits = scale * dloss/dlogits.      */
+int nc_bce_fwd_bwd(const float* logits, const float* labels, const uint8_t* incl, int32_t n,
+                   float scale, float* loss_out, float* dlogits, void* stream);
+/* KL regulariser (modules/losses.py:255-284): sum_out += kl (fp64); dmu/dlogstd (nullable)
+ * = scale * dkl/d.                                                                          */
+int nc_kl_fwd_bwd(const float* mu, int64_t ldmu, const float* logstd, int64_t ldls, int32_t R,
+                  int32_t P, float scale, double* sum_out, float* dmu, int64_t lddmu,
+                  float* dlogstd, int64_t lddls, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Latent plumbing (modules/vgpgae.py:626-651, modules/vgaemodulemixin.py:34-41)
+ * ---------------------------------------------------------------------------------------- */
+int nc_gather_rows_f32(const float* src, int64_t lds, const int32_t* idx, int32_t R, int32_t C,
+                       float* dst, int64_t ldd, void* stream);
+int nc_scatter_add_rows_f32(const float* src, int64_t lds, const int32_t* idx, int32_t R,
+                            int32_t C, float* dst, int64_t ldd, void* stream);
+/* z = (mu + eps * exp(logstd)) with inactive gene programs zeroed (eps NULL -> z = mu,
+ * active NULL -> all active); optional bf16 copy for the decoder GEMM.                      */
+int nc_reparam_fwd(const float* mu, int64_t ldmu, const float* logstd, int64_t ldls,
+                   const float* eps, int64_t ldeps, const uint8_t* active, int32_t R, int32_t P,
+                   float* z, int64_t ldz, void* z_bf16, int64_t ldzb, void* stream);
+int nc_reparam_bwd(const float* logstd, int64_t ldls, const float* eps, int64_t ldeps,
+                   const uint8_t* active, int32_t R, int32_t P, const float* dz, int64_t lddz,
+                   float* dmu, int64_t lddmu, float* dlogstd, int64_t lddls, void* stream);
+/* ema = momentum * mean_rows |mu| + (1 - momentum) * ema  (vgpgae.py:641-646)               */
+int nc_abs_mean_ema(const float* mu, int64_t ldmu, int32_t R, int32_t P, float momentum,
+                    float* ema, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Gene-program weight regularisers and active-GP statistics on a decoder weight W [F, P]
+ * (modules/losses.py:215-252 group lasso, :287-339 L1; modules/vgpgae.py:1281-1312).
+ * Column statistics are ACCUMULATED (call once per decoder): abs_sum[c] += sum_f |W| * l1mask,
+ * sq_sum[c] += sum_f W^2, nnz[c] += #{W != 0}, mask_cnt[c] += #{mask != 0}.                 */
+int nc_weight_col_stats(const float* W, int64_t ld, int32_t F, int32_t P, const uint8_t* l1mask,
+                        const float* mask, int64_t ldmask, float* abs_sum, float* sq_sum,
+                        float* nnz, float* mask_cnt, void* stream);
+/* dW += l1_scale * sign(W) * l1mask + gl_coef[c] * W                                        */
+int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t P, float l1_scale,
+                       const uint8_t* l1mask, const float* gl_coef, float* dW, int64_t lddw,
+                       void* stream);
+
+/* Fused Adam over a flat parameter segment with torch.optim.Adam semantics
+ * (train/trainer.py:339-342,418-421): optional clip_grad_value_ (clip_value > 0), optional
+ * refresh of the bf16 shadow copy used by the tensor-core GEMMs.                            */
+int nc_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                 float beta2, float eps, float weight_decay, int32_t step, float clip_value,
+                 void* p_bf16, void* stream);
+/* fp32 [R, C] (lds) -> bf16 [R, ldd] (columns >= C zeroed), optionally multiplied by `mask`
+ * (nn/layercomponents.py:77-80: weight * mask before the contraction).                      */
+int nc_cast_bf16(const float* src, int64_t lds, const float* mask, int64_t ldmask, int32_t R,
+                 int32_t C, void* dst, int64_t ldd, void* stream);
+
+/* Bias gradients and ReLU backward of the encoder linears (autograd of nn/encoders.py:179):
+ * out[c] += sum_r x[r, c];   out = dh * (h > 0) cast to the activation dtype.              */
+int nc_col_sum(const void* x, int dtype, int64_t ld, int32_t R, int32_t C, float* out,
+               void* stream);
+int nc_relu_bwd(const float* dh, int64_t lddh, const void* h, int dtype, int64_t ldh, int32_t R,
+                int32_t C, void* out, int64_t ldo, void* stream);
 
 #ifdef __cplusplus
 }

@@ -103,6 +103,14 @@ def ptr(t: Optional[torch.Tensor]):
     return ctypes.c_void_p(t.data_ptr())
 
 
+class HostPtr:
+    """Marks a CPU tensor passed to one of the few ``*_host`` arguments of the C ABI."""
+
+    def __init__(self, t: torch.Tensor):
+        assert not t.is_cuda and t.is_contiguous()
+        self.t = t
+
+
 def stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
@@ -111,7 +119,8 @@ def call(name: str, *args):
     """Call ``name`` with torch tensors (-> device pointers), None (-> NULL) or scalars; the
     stream argument is appended automatically."""
     fn = getattr(_load(), name)
-    conv = [ptr(a) if (a is None or torch.is_tensor(a)) else a for a in args]
+    conv = [ctypes.c_void_p(a.t.data_ptr()) if isinstance(a, HostPtr)
+            else (ptr(a) if (a is None or torch.is_tensor(a)) else a) for a in args]
     rc = fn(*conv, stream())
     if rc != 0:
         msg = _lib.nc_last_error().decode()

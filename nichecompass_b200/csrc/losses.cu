@@ -1,0 +1,249 @@
+// Loss-side kernels: fused softmax -> NB means -> column select -> negative-binomial NLL
+// (forward value + gradients in one pass), cosine-similarity graph decoder, weighted BCE,
+// KL regulariser.  Reference: nn/layers.py:143, nn/decoders.py:168, modules/vgpgae.py:714-749,
+// modules/losses.py:123-166 (BCE), :169-212 (NB), :255-284 (KL), nn/utils.py:8-36 (cosine).
+#include <algorithm>
+
+#include "common.cuh"
+
+extern void nc_count_launch(int n);
+
+namespace {
+
+// digamma for x > 0 (fp64): recurrence up to x >= 6, then the asymptotic series
+__device__ double digamma_d(double x) {
+    double r = 0.0;
+    while (x < 6.0) { r -= 1.0 / x; x += 1.0; }
+    const double f = 1.0 / (x * x);
+    return r + log(x) - 0.5 / x - f * (1.0 / 12.0 - f * (1.0 / 120.0 - f * (1.0 / 252.0 - f * (1.0 / 240.0 - f * (1.0 / 132.0)))));
+}
+
+constexpr int NB_T = 256;
+
+// One CTA per row.  logits: decoder pre-activations over ALL F features; sel[c] != 0 marks the
+// reconstructed columns (softmax is over all F, library size and loss over selected columns).
+__global__ void __launch_bounds__(NB_T)
+k_nb_fused(const float* __restrict__ logits, int64_t ldl, const float* __restrict__ x, int64_t ldx,
+           const uint8_t* __restrict__ sel, const float* __restrict__ theta_param, int F, float scale,
+           float* __restrict__ means, int64_t ldm, double* __restrict__ loss_sum,
+           float* __restrict__ dlogits, int64_t lddl, float* __restrict__ dtheta) {
+    __shared__ float red[32];
+    __shared__ double redd[32];
+    const int r = blockIdx.x, tid = threadIdx.x;
+    const float* lr = logits + (int64_t)r * ldl;
+    const float* xr = x + (int64_t)r * ldx;
+    // row max, library size
+    float m = -INFINITY, lib = 0.f;
+    for (int c = tid; c < F; c += NB_T) {
+        m = fmaxf(m, lr[c]);
+        if (sel[c]) lib += xr[c];
+    }
+    m = block_max(m, red);
+    lib = block_sum(lib, red);
+    float se = 0.f;
+    for (int c = tid; c < F; c += NB_T) se += expf(lr[c] - m);
+    se = block_sum(se, red);
+    const double L = (double)lib;           // exp(log(library size))
+    const double inv_se = 1.0 / (double)se;
+    // loss and D = sum_c dmu_c * mu_c
+    double loss = 0.0, D = 0.0;
+    const double eps = 1e-8;
+    for (int c = tid; c < F; c += NB_T) {
+        const double p = (double)expf(lr[c] - m) * inv_se;
+        const double mu = L * p;
+        if (means) means[(int64_t)r * ldm + c] = (float)mu;
+        if (!sel[c]) continue;
+        const double xv = (double)xr[c];
+        const double th = exp((double)theta_param[c]);
+        const double ltm = log(th + mu + eps);
+        double ll = th * (log(th + eps) - ltm) + xv * (log(mu + eps) - ltm);
+        if (xv != 0.0) ll += lgamma(xv + th) - lgamma(th) - lgamma(xv + 1.0);
+        loss -= ll;
+        const double dmu = -(xv / (mu + eps) - (xv + th) / (th + mu + eps));   // d(-ll)/dmu
+        D += dmu * mu;
+        if (dtheta) {
+            double dth = log(th + eps) + th / (th + eps) - ltm - (th + xv) / (th + mu + eps);
+            if (xv != 0.0) dth += digamma_d(xv + th) - digamma_d(th);
+            atomicAdd(dtheta + c, (float)(-(double)scale * dth * th));
+        }
+    }
+    loss = block_sum_d(loss, redd);
+    D = block_sum_d(D, redd);
+    if (tid == 0) atomicAdd(loss_sum, loss);
+    if (dlogits) {
+        float* dr = dlogits + (int64_t)r * lddl;
+        for (int c = tid; c < F; c += NB_T) {
+            const double p = (double)expf(lr[c] - m) * inv_se;
+            const double mu = L * p;
+            double dmu = 0.0;
+            if (sel[c]) {
+                const double xv = (double)xr[c];
+                const double th = exp((double)theta_param[c]);
+                dmu = -(xv / (mu + eps) - (xv + th) / (th + mu + eps));
+            }
+            dr[c] = (float)((double)scale * (mu * dmu - p * D));
+        }
+    }
+}
+
+// ------------------------------------------------------------------------- cosine decoder
+// pair e: a = z[e], b = z[n_pairs + e]; logits[e] = <a/max(|a|,eps), b/max(|b|,eps)>
+__global__ void __launch_bounds__(128)
+k_cosine_fwd(const float* __restrict__ z, int64_t ldz, int P, int n_pairs, float* __restrict__ logits,
+             float* __restrict__ norms) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_pairs) return;
+    const float* a = z + (int64_t)warp * ldz;
+    const float* b = z + (int64_t)(n_pairs + warp) * ldz;
+    float aa = 0.f, bb = 0.f, ab = 0.f;
+    for (int k = lane; k < P; k += 32) {
+        const float u = a[k], v = b[k];
+        aa += u * u; bb += v * v; ab += u * v;
+    }
+    aa = warp_sum(aa); bb = warp_sum(bb); ab = warp_sum(ab);
+    if (lane == 0) {
+        const float na = fmaxf(sqrtf(aa), 1e-8f), nb = fmaxf(sqrtf(bb), 1e-8f);
+        logits[warp] = ab / (na * nb);
+        norms[warp] = sqrtf(aa);
+        norms[n_pairs + warp] = sqrtf(bb);
+    }
+}
+
+__global__ void __launch_bounds__(128)
+k_cosine_bwd(const float* __restrict__ z, int64_t ldz, int P, int n_pairs, const float* __restrict__ logits,
+             const float* __restrict__ norms, const float* __restrict__ dlogits, float* __restrict__ dz, int64_t lddz) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= n_pairs) return;
+    const float* a = z + (int64_t)warp * ldz;
+    const float* b = z + (int64_t)(n_pairs + warp) * ldz;
+    float* da = dz + (int64_t)warp * lddz;
+    float* db = dz + (int64_t)(n_pairs + warp) * lddz;
+    const float ra = norms[warp], rb = norms[n_pairs + warp];
+    const float na = fmaxf(ra, 1e-8f), nb = fmaxf(rb, 1e-8f);
+    const float g = dlogits[warp], cs = logits[warp];
+    // a_hat = a / na.  If |a| > eps: d cos/da = (b_hat - cos * a_hat) / na, else b_hat / na.
+    const bool ca = ra > 1e-8f, cb = rb > 1e-8f;
+    for (int k = lane; k < P; k += 32) {
+        const float ah = a[k] / na, bh = b[k] / nb;
+        da[k] = g * (bh - (ca ? cs * ah : 0.f)) / na;
+        db[k] = g * (ah - (cb ? cs * bh : 0.f)) / nb;
+    }
+}
+
+// ------------------------------------------------------------------------- weighted BCE
+// Single CTA.  incl == NULL -> all included.  loss = mean_incl( pw*y*softplus(-x) + (1-y)*softplus(x) ),
+// pw = #neg/#pos.  dlogits = scale * d loss / d logits (0 for excluded).
+__device__ __forceinline__ float softplusf(float v) { return fmaxf(v, 0.f) + log1pf(expf(-fabsf(v))); }
+
+__global__ void __launch_bounds__(1024)
+k_bce(const float* __restrict__ logits, const float* __restrict__ labels, const uint8_t* __restrict__ incl,
+      int n, float scale, float* __restrict__ loss_out, float* __restrict__ dlogits) {
+    __shared__ float red[32];
+    const int tid = threadIdx.x;
+    float np = 0.f, nn = 0.f;
+    for (int e = tid; e < n; e += 1024) {
+        if (incl && !incl[e]) continue;
+        if (labels[e] == 1.f) np += 1.f;
+        else if (labels[e] == 0.f) nn += 1.f;
+    }
+    np = block_sum(np, red);
+    nn = block_sum(nn, red);
+    float cnt = 0.f;
+    for (int e = tid; e < n; e += 1024) cnt += (incl && !incl[e]) ? 0.f : 1.f;
+    cnt = block_sum(cnt, red);
+    const float pw = nn / np;
+    float acc = 0.f;
+    for (int e = tid; e < n; e += 1024) {
+        const bool in = !(incl && !incl[e]);
+        const float xv = logits[e], y = labels[e];
+        float d = 0.f;
+        if (in) {
+            acc += pw * y * softplusf(-xv) + (1.f - y) * softplusf(xv);
+            const float sg = 1.f / (1.f + expf(-xv));
+            d = (-(pw * y) * (1.f - sg) + (1.f - y) * sg) / cnt;
+        }
+        if (dlogits) dlogits[e] = scale * d;
+    }
+    acc = block_sum(acc, red);
+    if (tid == 0) *loss_out = acc / cnt;
+}
+
+// ------------------------------------------------------------------------- KL
+// kl = -0.5 * mean_rows sum_cols (1 + 2 ls - mu^2 - exp(ls)^2); grads scaled by `scale`.
+__global__ void __launch_bounds__(256)
+k_kl(const float* __restrict__ mu, int64_t ldmu, const float* __restrict__ ls, int64_t ldls, int R, int P,
+     float scale, double* __restrict__ sum_out, float* __restrict__ dmu, int64_t lddmu, float* __restrict__ dls,
+     int64_t lddls) {
+    __shared__ double redd[32];
+    const int64_t total = (int64_t)R * P;
+    double acc = 0.0;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / P), c = (int)(q % P);
+        const float m = mu[(int64_t)r * ldmu + c], l = ls[(int64_t)r * ldls + c];
+        const float e2 = expf(l) * expf(l);
+        acc += (double)(1.f + 2.f * l - m * m - e2);
+        if (dmu) {
+            dmu[(int64_t)r * lddmu + c] = scale * m / (float)R;
+            dls[(int64_t)r * lddls + c] = scale * (e2 - 1.f) / (float)R;
+        }
+    }
+    acc = block_sum_d(acc, redd);
+    if (threadIdx.x == 0) atomicAdd(sum_out, -0.5 * acc / (double)R);
+}
+
+}  // namespace
+
+extern "C" int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x, int64_t ldx, const uint8_t* sel,
+                                const float* theta_param, int32_t n_rows, int32_t F, float scale, float* means,
+                                int64_t ldm, double* loss_sum, float* dlogits, int64_t lddl, float* dtheta,
+                                void* stream) {
+    NC_REQUIRE(n_rows >= 0 && F > 0 && ldl >= F && ldx >= F, NC_ESHAPE, "nc_nb_loss_fused: bad shape rows=%d F=%d", n_rows, F);
+    if (n_rows == 0) return NC_OK;
+    k_nb_fused<<<n_rows, NB_T, 0, (cudaStream_t)stream>>>(logits, ldl, x, ldx, sel, theta_param, F, scale, means, ldm,
+                                                         loss_sum, dlogits, lddl, dtheta);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_nb_loss_fused");
+    return NC_OK;
+}
+
+extern "C" int nc_cosine_fwd(const float* z, int64_t ldz, int32_t P, int32_t n_pairs, float* logits, float* norms,
+                             void* stream) {
+    NC_REQUIRE(n_pairs >= 0 && P > 0 && ldz >= P, NC_ESHAPE, "nc_cosine_fwd: bad shape");
+    if (n_pairs == 0) return NC_OK;
+    k_cosine_fwd<<<(unsigned)nc_cdiv(n_pairs, 4), 128, 0, (cudaStream_t)stream>>>(z, ldz, P, n_pairs, logits, norms);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_cosine_fwd");
+    return NC_OK;
+}
+
+extern "C" int nc_cosine_bwd(const float* z, int64_t ldz, int32_t P, int32_t n_pairs, const float* logits,
+                             const float* norms, const float* dlogits, float* dz, int64_t lddz, void* stream) {
+    NC_REQUIRE(n_pairs >= 0 && P > 0 && ldz >= P && lddz >= P, NC_ESHAPE, "nc_cosine_bwd: bad shape");
+    if (n_pairs == 0) return NC_OK;
+    k_cosine_bwd<<<(unsigned)nc_cdiv(n_pairs, 4), 128, 0, (cudaStream_t)stream>>>(z, ldz, P, n_pairs, logits, norms,
+                                                                                  dlogits, dz, lddz);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_cosine_bwd");
+    return NC_OK;
+}
+
+extern "C" int nc_bce_fwd_bwd(const float* logits, const float* labels, const uint8_t* incl, int32_t n, float scale,
+                              float* loss_out, float* dlogits, void* stream) {
+    NC_REQUIRE(n > 0, NC_ESHAPE, "nc_bce_fwd_bwd: empty input");
+    k_bce<<<1, 1024, 0, (cudaStream_t)stream>>>(logits, labels, incl, n, scale, loss_out, dlogits);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_bce_fwd_bwd");
+    return NC_OK;
+}
+
+extern "C" int nc_kl_fwd_bwd(const float* mu, int64_t ldmu, const float* logstd, int64_t ldls, int32_t R, int32_t P,
+                             float scale, double* sum_out, float* dmu, int64_t lddmu, float* dlogstd, int64_t lddls,
+                             void* stream) {
+    NC_REQUIRE(R > 0 && P > 0, NC_ESHAPE, "nc_kl_fwd_bwd: empty input");
+    const int64_t total = (int64_t)R * P;
+    int blocks = (int)std::min<int64_t>(nc_cdiv(total, 256), 4 * nc_num_sms());
+    k_kl<<<blocks, 256, 0, (cudaStream_t)stream>>>(mu, ldmu, logstd, ldls, R, P, scale, sum_out, dmu, lddmu, dlogstd, lddls);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_kl_fwd_bwd");
+    return NC_OK;
+}

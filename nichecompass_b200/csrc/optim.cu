@@ -1,0 +1,320 @@
+// Latent sampling, row gather/scatter, gene-program weight regularisers, active-GP statistics,
+// fused Adam and precision casts.  Reference: modules/vgaemodulemixin.py:34-41 (reparameterize),
+// modules/vgpgae.py:626-651 (batch_idx gather, z masking, |mu| EMA), modules/losses.py:215-252
+// (group lasso), :287-339 (L1), modules/vgpgae.py:1205-1334 (active-GP mask),
+// train/trainer.py:339-342,421 (torch.optim.Adam).
+#include <algorithm>
+
+#include "common.cuh"
+
+extern void nc_count_launch(int n);
+
+namespace {
+inline int grid_for(int64_t n, int t = 256) { return (int)std::min<int64_t>(std::max<int64_t>(nc_cdiv(n, t), 1), 8 * (int64_t)nc_num_sms()); }
+
+// ------------------------------------------------------------------------- gather / scatter rows
+__global__ void k_gather_rows_f32(const float* __restrict__ src, int64_t lds, const int32_t* __restrict__ idx,
+                                  int R, int C, float* __restrict__ dst, int64_t ldd) {
+    const int64_t total = (int64_t)R * C;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / C), c = (int)(q % C);
+        dst[(int64_t)r * ldd + c] = src[(int64_t)idx[r] * lds + c];
+    }
+}
+__global__ void k_scatter_add_rows_f32(const float* __restrict__ src, int64_t lds, const int32_t* __restrict__ idx,
+                                       int R, int C, float* __restrict__ dst, int64_t ldd) {
+    const int64_t total = (int64_t)R * C;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / C), c = (int)(q % C);
+        atomicAdd(dst + (int64_t)idx[r] * ldd + c, src[(int64_t)r * lds + c]);
+    }
+}
+
+// ------------------------------------------------------------------------- reparameterisation
+// z = (mu + eps * exp(logstd)) * active;  optional bf16 copy for the decoder GEMM
+__global__ void k_reparam_fwd(const float* __restrict__ mu, int64_t ldmu, const float* __restrict__ ls, int64_t ldls,
+                              const float* __restrict__ eps, int64_t ldeps, const uint8_t* __restrict__ active,
+                              int R, int P, float* __restrict__ z, int64_t ldz, __nv_bfloat16* __restrict__ zb,
+                              int64_t ldzb) {
+    const int64_t total = (int64_t)R * P;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / P), c = (int)(q % P);
+        float v = mu[(int64_t)r * ldmu + c];
+        if (eps) v += eps[(int64_t)r * ldeps + c] * expf(ls[(int64_t)r * ldls + c]);
+        if (active && !active[c]) v = 0.f;
+        z[(int64_t)r * ldz + c] = v;
+        if (zb) zb[(int64_t)r * ldzb + c] = __float2bfloat16_rn(v);
+    }
+}
+__global__ void k_reparam_bwd(const float* __restrict__ ls, int64_t ldls, const float* __restrict__ eps, int64_t ldeps,
+                              const uint8_t* __restrict__ active, int R, int P, const float* __restrict__ dz,
+                              int64_t lddz, float* __restrict__ dmu, int64_t lddmu, float* __restrict__ dls, int64_t lddls) {
+    const int64_t total = (int64_t)R * P;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / P), c = (int)(q % P);
+        float g = dz[(int64_t)r * lddz + c];
+        if (active && !active[c]) g = 0.f;
+        dmu[(int64_t)r * lddmu + c] = g;
+        dls[(int64_t)r * lddls + c] = eps ? g * eps[(int64_t)r * ldeps + c] * expf(ls[(int64_t)r * ldls + c]) : 0.f;
+    }
+}
+
+// ------------------------------------------------------------------------- |mu| EMA
+// ema[c] = momentum * mean_r |mu[r,c]| + (1 - momentum) * ema[c]; one warp per column block
+__global__ void k_abs_mean_ema(const float* __restrict__ mu, int64_t ldmu, int R, int P, float momentum,
+                               float* __restrict__ ema) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= P) return;
+    float s = 0.f;
+    for (int r = 0; r < R; ++r) s += fabsf(mu[(int64_t)r * ldmu + c]);
+    ema[c] = momentum * (s / (float)R) + (1.f - momentum) * ema[c];
+}
+
+// ------------------------------------------------------------------------- weight statistics
+// Per gene-program (column) statistics of a decoder weight W [F, P] (row-major, ld):
+//   abs_sum[c] += sum_f |W[f,c]| * (l1mask ? l1mask[f,c] : 1)
+//   sq_sum[c]  += sum_f W[f,c]^2        nnz[c] += #{W[f,c] != 0}     mask_cnt[c] += #{mask[f,c] != 0}
+// Any output may be NULL.  grid.x tiles columns (32 per CTA), grid.y tiles rows.
+__global__ void __launch_bounds__(256)
+k_col_stats(const float* __restrict__ W, int64_t ld, int F, int P, const uint8_t* __restrict__ l1mask,
+            const float* __restrict__ mask, int64_t ldmask, float* __restrict__ abs_sum, float* __restrict__ sq_sum,
+            float* __restrict__ nnz, float* __restrict__ mask_cnt) {
+    __shared__ float s[4][8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    float a = 0.f, q = 0.f, z = 0.f, mc = 0.f;
+    if (c < P) {
+        const int rows_per = (F + gridDim.y - 1) / gridDim.y;
+        const int f0 = blockIdx.y * rows_per, f1 = min(F, f0 + rows_per);
+        for (int f = f0 + ty; f < f1; f += 8) {
+            const float w = W[(int64_t)f * ld + c];
+            const float lm = l1mask ? (float)l1mask[(int64_t)f * P + c] : 1.f;
+            a += fabsf(w) * lm;
+            q += w * w;
+            z += (w != 0.f) ? 1.f : 0.f;
+            if (mask) mc += (mask[(int64_t)f * ldmask + c] != 0.f) ? 1.f : 0.f;
+        }
+    }
+    s[0][ty][tx] = a; s[1][ty][tx] = q; s[2][ty][tx] = z; s[3][ty][tx] = mc;
+    __syncthreads();
+    if (ty == 0 && c < P) {
+        float ra = 0.f, rq = 0.f, rz = 0.f, rm = 0.f;
+        for (int k = 0; k < 8; ++k) { ra += s[0][k][tx]; rq += s[1][k][tx]; rz += s[2][k][tx]; rm += s[3][k][tx]; }
+        if (abs_sum) atomicAdd(abs_sum + c, ra);
+        if (sq_sum) atomicAdd(sq_sum + c, rq);
+        if (nnz) atomicAdd(nnz + c, rz);
+        if (mask_cnt) atomicAdd(mask_cnt + c, rm);
+    }
+}
+
+// dW += l1_scale * sign(W) * l1mask + gl_coef[c] * W   (gl_coef[c] = lambda * sqrt(cnt_c) / ||W[:,c]||, 0 if norm 0)
+__global__ void k_reg_grad(const float* __restrict__ W, int64_t ld, int F, int P, float l1_scale,
+                           const uint8_t* __restrict__ l1mask, const float* __restrict__ gl_coef,
+                           float* __restrict__ dW, int64_t lddw) {
+    const int64_t total = (int64_t)F * P;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int f = (int)(q / P), c = (int)(q % P);
+        const float w = W[(int64_t)f * ld + c];
+        float g = 0.f;
+        if (l1_scale != 0.f && (!l1mask || l1mask[q])) g += l1_scale * (w > 0.f ? 1.f : (w < 0.f ? -1.f : 0.f));
+        if (gl_coef) g += gl_coef[c] * w;
+        dW[(int64_t)f * lddw + c] += g;
+    }
+}
+
+// ------------------------------------------------------------------------- Adam (torch semantics)
+__global__ void k_adam(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                       int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
+                       float clip, __nv_bfloat16* __restrict__ p_bf16) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float gi = g[i];
+        if (clip > 0.f) gi = fminf(fmaxf(gi, -clip), clip);
+        const float pi = p[i];
+        if (wd != 0.f) gi += wd * pi;
+        const float mi = b1 * m[i] + (1.f - b1) * gi;
+        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+        m[i] = mi;
+        v[i] = vi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        const float np = pi - (lr / bc1) * (mi / denom);
+        p[i] = np;
+        if (p_bf16) p_bf16[i] = __float2bfloat16_rn(np);
+    }
+}
+
+// fp32 -> bf16 cast (optionally multiplied by a mask of the same shape), 2-D with leading dims
+__global__ void k_cast_bf16(const float* __restrict__ src, int64_t lds, const float* __restrict__ mask, int64_t ldm,
+                            int R, int C, __nv_bfloat16* __restrict__ dst, int64_t ldd) {
+    const int64_t total = (int64_t)R * ldd;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / ldd), c = (int)(q % ldd);
+        float v = 0.f;
+        if (c < C) {
+            v = src[(int64_t)r * lds + c];
+            if (mask) v *= mask[(int64_t)r * ldm + c];
+        }
+        dst[q] = __float2bfloat16_rn(v);
+    }
+}
+}  // namespace
+
+extern "C" int nc_gather_rows_f32(const float* src, int64_t lds, const int32_t* idx, int32_t R, int32_t C, float* dst,
+                                  int64_t ldd, void* stream) {
+    NC_REQUIRE(R >= 0 && C > 0 && lds >= C && ldd >= C, NC_ESHAPE, "nc_gather_rows_f32: bad shape");
+    if (R == 0) return NC_OK;
+    k_gather_rows_f32<<<grid_for((int64_t)R * C), 256, 0, (cudaStream_t)stream>>>(src, lds, idx, R, C, dst, ldd);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_gather_rows_f32");
+    return NC_OK;
+}
+
+extern "C" int nc_scatter_add_rows_f32(const float* src, int64_t lds, const int32_t* idx, int32_t R, int32_t C,
+                                       float* dst, int64_t ldd, void* stream) {
+    NC_REQUIRE(R >= 0 && C > 0 && lds >= C && ldd >= C, NC_ESHAPE, "nc_scatter_add_rows_f32: bad shape");
+    if (R == 0) return NC_OK;
+    k_scatter_add_rows_f32<<<grid_for((int64_t)R * C), 256, 0, (cudaStream_t)stream>>>(src, lds, idx, R, C, dst, ldd);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_scatter_add_rows_f32");
+    return NC_OK;
+}
+
+extern "C" int nc_reparam_fwd(const float* mu, int64_t ldmu, const float* logstd, int64_t ldls, const float* eps,
+                              int64_t ldeps, const uint8_t* active, int32_t R, int32_t P, float* z, int64_t ldz,
+                              void* z_bf16, int64_t ldzb, void* stream) {
+    NC_REQUIRE(R >= 0 && P > 0, NC_ESHAPE, "nc_reparam_fwd: bad shape");
+    if (R == 0) return NC_OK;
+    k_reparam_fwd<<<grid_for((int64_t)R * P), 256, 0, (cudaStream_t)stream>>>(mu, ldmu, logstd, ldls, eps, ldeps, active,
+                                                                            R, P, z, ldz, (__nv_bfloat16*)z_bf16, ldzb);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_reparam_fwd");
+    return NC_OK;
+}
+
+extern "C" int nc_reparam_bwd(const float* logstd, int64_t ldls, const float* eps, int64_t ldeps, const uint8_t* active,
+                              int32_t R, int32_t P, const float* dz, int64_t lddz, float* dmu, int64_t lddmu,
+                              float* dlogstd, int64_t lddls, void* stream) {
+    NC_REQUIRE(R >= 0 && P > 0, NC_ESHAPE, "nc_reparam_bwd: bad shape");
+    if (R == 0) return NC_OK;
+    k_reparam_bwd<<<grid_for((int64_t)R * P), 256, 0, (cudaStream_t)stream>>>(logstd, ldls, eps, ldeps, active, R, P, dz,
+                                                                            lddz, dmu, lddmu, dlogstd, lddls);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_reparam_bwd");
+    return NC_OK;
+}
+
+extern "C" int nc_abs_mean_ema(const float* mu, int64_t ldmu, int32_t R, int32_t P, float momentum, float* ema,
+                               void* stream) {
+    NC_REQUIRE(R > 0 && P > 0, NC_ESHAPE, "nc_abs_mean_ema: bad shape");
+    k_abs_mean_ema<<<(unsigned)nc_cdiv(P, 128), 128, 0, (cudaStream_t)stream>>>(mu, ldmu, R, P, momentum, ema);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_abs_mean_ema");
+    return NC_OK;
+}
+
+extern "C" int nc_weight_col_stats(const float* W, int64_t ld, int32_t F, int32_t P, const uint8_t* l1mask,
+                                   const float* mask, int64_t ldmask, float* abs_sum, float* sq_sum, float* nnz,
+                                   float* mask_cnt, void* stream) {
+    NC_REQUIRE(F > 0 && P > 0 && ld >= P, NC_ESHAPE, "nc_weight_col_stats: bad shape");
+    dim3 grid((unsigned)nc_cdiv(P, 32), (unsigned)std::min<int64_t>(nc_cdiv(F, 64), 64));
+    k_col_stats<<<grid, 256, 0, (cudaStream_t)stream>>>(W, ld, F, P, l1mask, mask, ldmask, abs_sum, sq_sum, nnz, mask_cnt);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_weight_col_stats");
+    return NC_OK;
+}
+
+extern "C" int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t P, float l1_scale,
+                                  const uint8_t* l1mask, const float* gl_coef, float* dW, int64_t lddw, void* stream) {
+    NC_REQUIRE(F > 0 && P > 0 && ld >= P && lddw >= P, NC_ESHAPE, "nc_weight_reg_grad: bad shape");
+    k_reg_grad<<<grid_for((int64_t)F * P), 256, 0, (cudaStream_t)stream>>>(W, ld, F, P, l1_scale, l1mask, gl_coef, dW, lddw);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_weight_reg_grad");
+    return NC_OK;
+}
+
+extern "C" int nc_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                            float beta2, float eps, float weight_decay, int32_t step, float clip_value, void* p_bf16,
+                            void* stream) {
+    NC_REQUIRE(n >= 0 && step >= 1, NC_EINVAL, "nc_adam_step: need n >= 0 and step >= 1");
+    if (n == 0) return NC_OK;
+    const float bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+    const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
+    k_adam<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, bc1,
+                                                         bc2_sqrt, clip_value, (__nv_bfloat16*)p_bf16);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_adam_step");
+    return NC_OK;
+}
+
+extern "C" int nc_cast_bf16(const float* src, int64_t lds, const float* mask, int64_t ldmask, int32_t R, int32_t C,
+                            void* dst, int64_t ldd, void* stream) {
+    NC_REQUIRE(R >= 0 && C > 0 && lds >= C && ldd >= C, NC_ESHAPE, "nc_cast_bf16: bad shape");
+    if (R == 0) return NC_OK;
+    k_cast_bf16<<<grid_for((int64_t)R * ldd), 256, 0, (cudaStream_t)stream>>>(src, lds, mask, ldmask, R, C,
+                                                                             (__nv_bfloat16*)dst, ldd);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_cast_bf16");
+    return NC_OK;
+}
+
+// ------------------------------------------------------------------------- bias gradients / ReLU backward
+namespace {
+// out[c] (+)= sum_r x[r, c]; grid.x tiles columns (32), grid.y tiles rows, atomics across row tiles
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_col_sum(const T* __restrict__ x, int64_t ld, int R, int C, float* __restrict__ out) {
+    __shared__ float s[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + tx;
+    float a = 0.f;
+    if (c < C) {
+        const int rows_per = (R + gridDim.y - 1) / gridDim.y;
+        const int r0 = blockIdx.y * rows_per, r1 = min(R, r0 + rows_per);
+        for (int r = r0 + ty; r < r1; r += 8) a += Elem<T>::ld(x + (int64_t)r * ld + c);
+    }
+    s[ty][tx] = a;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+        float t = 0.f;
+        for (int k = 0; k < 8; ++k) t += s[k][tx];
+        atomicAdd(out + c, t);
+    }
+}
+
+// out = dh * (h > 0), cast to T; pad columns [C, ldo) are zeroed
+template <typename T>
+__global__ void k_relu_bwd(const float* __restrict__ dh, int64_t lddh, const T* __restrict__ h, int64_t ldh, int R,
+                           int C, T* __restrict__ out, int64_t ldo) {
+    const int64_t total = (int64_t)R * ldo;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / ldo), c = (int)(q % ldo);
+        float v = 0.f;
+        if (c < C && Elem<T>::ld(h + (int64_t)r * ldh + c) > 0.f) v = dh[(int64_t)r * lddh + c];
+        Elem<T>::st(out + q, v);
+    }
+}
+}  // namespace
+
+extern "C" int nc_col_sum(const void* x, int dtype, int64_t ld, int32_t R, int32_t C, float* out, void* stream) {
+    NC_REQUIRE(R >= 0 && C > 0 && ld >= C, NC_ESHAPE, "nc_col_sum: bad shape");
+    if (R == 0) return NC_OK;
+    dim3 grid((unsigned)nc_cdiv(C, 32), (unsigned)std::min<int64_t>(nc_cdiv(R, 64), 128));
+    if (dtype == NC_F32) k_col_sum<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, ld, R, C, out);
+    else if (dtype == NC_BF16) k_col_sum<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ld, R, C, out);
+    else NC_REQUIRE(false, NC_EINVAL, "nc_col_sum: bad dtype %d", dtype);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_col_sum");
+    return NC_OK;
+}
+
+extern "C" int nc_relu_bwd(const float* dh, int64_t lddh, const void* h, int dtype, int64_t ldh, int32_t R, int32_t C,
+                           void* out, int64_t ldo, void* stream) {
+    NC_REQUIRE(R >= 0 && C > 0 && lddh >= C && ldh >= C && ldo >= C, NC_ESHAPE, "nc_relu_bwd: bad shape");
+    if (R == 0) return NC_OK;
+    const int g = grid_for((int64_t)R * ldo);
+    if (dtype == NC_F32) k_relu_bwd<float><<<g, 256, 0, (cudaStream_t)stream>>>(dh, lddh, (const float*)h, ldh, R, C, (float*)out, ldo);
+    else if (dtype == NC_BF16) k_relu_bwd<__nv_bfloat16><<<g, 256, 0, (cudaStream_t)stream>>>(dh, lddh, (const __nv_bfloat16*)h, ldh, R, C, (__nv_bfloat16*)out, ldo);
+    else NC_REQUIRE(false, NC_EINVAL, "nc_relu_bwd: bad dtype %d", dtype);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_relu_bwd");
+    return NC_OK;
+}

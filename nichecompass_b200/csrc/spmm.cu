@@ -172,8 +172,8 @@ template <typename TX, typename TO, bool VEC>
 __global__ void __launch_bounds__(SPMM_T)
 k_spmm_csr(const TX* __restrict__ x, int64_t ldx, int32_t n_cols,
            const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
-           const float* __restrict__ w, const float* __restrict__ wself, int skip_self,
-           TO* __restrict__ out, int64_t ldo) {
+           const float* __restrict__ w, const float* __restrict__ wself, const float* __restrict__ bias,
+           int skip_self, TO* __restrict__ out, int64_t ldo) {
     __shared__ int32_t s_col[SPMM_STAGE];
     __shared__ float s_w[SPMM_STAGE];
     const int i = blockIdx.x;
@@ -231,6 +231,12 @@ k_spmm_csr(const TX* __restrict__ x, int64_t ldx, int32_t n_cols,
 #pragma unroll
     for (int v = 0; v < SPMM_VPT; ++v) {
         const int c = c_base + (v * SPMM_T + tid) * 4;
+        if (bias) {
+            if (c < n_cols) acc[v].x += __ldg(bias + c);
+            if (c + 1 < n_cols) acc[v].y += __ldg(bias + c + 1);
+            if (c + 2 < n_cols) acc[v].z += __ldg(bias + c + 2);
+            if (c + 3 < n_cols) acc[v].w += __ldg(bias + c + 3);
+        }
         if (VEC && c + 3 < n_cols) {
             Elem<TO>::st4(orow + c, acc[v]);
         } else {
@@ -244,36 +250,36 @@ k_spmm_csr(const TX* __restrict__ x, int64_t ldx, int32_t n_cols,
 
 template <typename TX, typename TO>
 static int launch_spmm(const void* x, int64_t ldx, int32_t n_cols, const int32_t* rowptr,
-                       const int32_t* col, const float* w, const float* wself, int skip_self,
+                       const int32_t* col, const float* w, const float* wself, const float* bias, int skip_self,
                        int32_t n_rows, void* out, int64_t ldo, cudaStream_t s) {
     const size_t ax = sizeof(TX) * 4, ao = sizeof(TO) * 4;
     const bool vec = (ldx % 4 == 0) && (ldo % 4 == 0) && ((uintptr_t)x % ax == 0) && ((uintptr_t)out % ao == 0);
     dim3 grid(n_rows, (unsigned)nc_cdiv(n_cols, SPMM_CHUNK));
     if (vec)
-        k_spmm_csr<TX, TO, true><<<grid, SPMM_T, 0, s>>>((const TX*)x, ldx, n_cols, rowptr, col, w, wself, skip_self, (TO*)out, ldo);
+        k_spmm_csr<TX, TO, true><<<grid, SPMM_T, 0, s>>>((const TX*)x, ldx, n_cols, rowptr, col, w, wself, bias, skip_self, (TO*)out, ldo);
     else
-        k_spmm_csr<TX, TO, false><<<grid, SPMM_T, 0, s>>>((const TX*)x, ldx, n_cols, rowptr, col, w, wself, skip_self, (TO*)out, ldo);
+        k_spmm_csr<TX, TO, false><<<grid, SPMM_T, 0, s>>>((const TX*)x, ldx, n_cols, rowptr, col, w, wself, bias, skip_self, (TO*)out, ldo);
     nc_count_launch(1);
     return 0;
 }
 
 extern "C" int nc_spmm_csr(const void* x, int x_dtype, int64_t ldx, int32_t n_cols,
                            const int32_t* rowptr, const int32_t* col, const float* w,
-                           const float* wself, int skip_self, int32_t n_rows, void* out,
-                           int out_dtype, int64_t ldo, void* stream) {
+                           const float* wself, const float* bias, int skip_self, int32_t n_rows,
+                           void* out, int out_dtype, int64_t ldo, void* stream) {
     NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldx >= n_cols && ldo >= n_cols, NC_ESHAPE,
                "nc_spmm_csr: bad shape n_rows=%d n_cols=%d ldx=%lld ldo=%lld", n_rows, n_cols,
                (long long)ldx, (long long)ldo);
     if (n_rows == 0) return NC_OK;
     cudaStream_t s = (cudaStream_t)stream;
     if (x_dtype == NC_F32 && out_dtype == NC_F32)
-        launch_spmm<float, float>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+        launch_spmm<float, float>(x, ldx, n_cols, rowptr, col, w, wself, bias, skip_self, n_rows, out, ldo, s);
     else if (x_dtype == NC_BF16 && out_dtype == NC_F32)
-        launch_spmm<__nv_bfloat16, float>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+        launch_spmm<__nv_bfloat16, float>(x, ldx, n_cols, rowptr, col, w, wself, bias, skip_self, n_rows, out, ldo, s);
     else if (x_dtype == NC_BF16 && out_dtype == NC_BF16)
-        launch_spmm<__nv_bfloat16, __nv_bfloat16>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+        launch_spmm<__nv_bfloat16, __nv_bfloat16>(x, ldx, n_cols, rowptr, col, w, wself, bias, skip_self, n_rows, out, ldo, s);
     else if (x_dtype == NC_F32 && out_dtype == NC_BF16)
-        launch_spmm<float, __nv_bfloat16>(x, ldx, n_cols, rowptr, col, w, wself, skip_self, n_rows, out, ldo, s);
+        launch_spmm<float, __nv_bfloat16>(x, ldx, n_cols, rowptr, col, w, wself, bias, skip_self, n_rows, out, ldo, s);
     else
         NC_REQUIRE(false, NC_EINVAL, "nc_spmm_csr: unknown dtype %d/%d", x_dtype, out_dtype);
     NC_CHECK_LAUNCH("nc_spmm_csr");

@@ -1,0 +1,538 @@
+"""
+Differentiable building blocks of the VGPGAE hot path: ``torch.autograd.Function``s whose
+forward and backward are calls into the C ABI (``nichecompass_b200/_lib.py``).  No tensor math is
+done by PyTorch here beyond allocation, views and scalar bookkeeping.
+
+Two precisions: ``torch.float32`` (SIMT GEMM, parity mode, 1e-5) and ``torch.bfloat16``
+(activations + weights in bf16, tcgen05 GEMMs, fp32 accumulation / losses, 1e-3).
+"""
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import ops
+from ._lib import HostPtr, call, dtype_code
+from .ops import pad8
+
+
+# --------------------------------------------------------------------------- graph container
+class SubgraphCSR:
+    """Induced subgraph in dst-CSR form (int32, device).  ``n_dst``: the leading rows whose
+    outputs are consumed (the seeds); ``max_deg``: upper bound of their row lengths."""
+
+    def __init__(self, rowptr, col, n_nodes: int, n_dst: Optional[int] = None, max_deg: Optional[int] = None):
+        self.rowptr, self.col, self.n_nodes = rowptr, col, int(n_nodes)
+        self.n_dst = self.n_nodes if n_dst is None else int(n_dst)
+        if max_deg is None:
+            max_deg = int((rowptr[1:] - rowptr[:-1]).max().item()) if self.n_nodes > 0 else 0
+        self.max_deg = int(max_deg)
+        self._rev = None
+        self._norm = {}
+
+    @classmethod
+    def from_edge_index(cls, edge_index: torch.Tensor, n_nodes: int, n_dst: Optional[int] = None):
+        rowptr, col = ops.coo_to_dst_csr(edge_index, n_nodes)
+        return cls(rowptr, col, n_nodes, n_dst)
+
+    @property
+    def n_slots(self) -> int:
+        """Upper bound of the attention slots of the first n_dst rows (entries + self edges)."""
+        return self.col.numel() + self.n_dst
+
+    def reverse(self):
+        if self._rev is None:
+            self._rev = ops.reverse_csr(self.rowptr, self.col, self.n_nodes, self.n_dst, True, self.n_slots)
+        return self._rev
+
+    def gcn_weights(self, use_out_degree: bool, n_rows: Optional[int] = None):
+        n_rows = self.n_dst if n_rows is None else n_rows
+        key = (use_out_degree, n_rows)
+        if key not in self._norm:
+            self._norm[key] = ops.gcn_norm_weights(self.rowptr, self.col, self.n_nodes, n_rows, use_out_degree)
+        return self._norm[key]
+
+
+# --------------------------------------------------------------------------- packed weights
+_PACK_CACHE = {}
+
+
+def _versions(ts: Sequence[Optional[torch.Tensor]]):
+    return tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
+
+
+def pack_rows(key, params: Sequence[torch.Tensor], dtype: torch.dtype, n_cols: int) -> torch.Tensor:
+    """Stack 2-D parameters [r_i, n_cols] row-wise into one [sum r_i, pad8(n_cols)] buffer of
+    ``dtype`` (bf16 shadow / fp32 packed copy); refreshed only when a parameter changed."""
+    ver = (_versions(params), dtype)
+    hit = _PACK_CACHE.get(key)
+    if hit is not None and hit[0] == ver:
+        return hit[1]
+    rows = sum(p.size(0) for p in params)
+    ld = pad8(n_cols)
+    buf = hit[1] if (hit is not None and hit[1].shape == (rows, ld) and hit[1].dtype == dtype) else \
+        torch.zeros(rows, ld, dtype=dtype, device=params[0].device)
+    r = 0
+    with torch.no_grad():
+        for p in params:
+            p2 = p.detach().reshape(p.size(0), -1)
+            if dtype == torch.bfloat16:
+                call("nc_cast_bf16", p2, p2.stride(0), None, 0, p2.size(0), p2.size(1), buf[r:], ld)
+            else:
+                buf[r:r + p2.size(0), :p2.size(1)].copy_(p2)
+            r += p2.size(0)
+    _PACK_CACHE[key] = (ver, buf)
+    return buf
+
+
+def pack_cols(key, params: Sequence[torch.Tensor], masks: Sequence[Optional[torch.Tensor]],
+              dtype: torch.dtype) -> torch.Tensor:
+    """Concatenate [F, c_i] parameters column-wise, each multiplied by its mask (MaskedLinear:
+    weight * mask [* dynamic mask], nn/layercomponents.py:74-79), into [F, pad8(sum c_i)]."""
+    ver = (_versions(params), _versions(masks), dtype)
+    hit = _PACK_CACHE.get(key)
+    if hit is not None and hit[0] == ver:
+        return hit[1]
+    F = params[0].size(0)
+    ld = pad8(sum(p.size(1) for p in params))
+    buf32 = torch.zeros(F, ld, dtype=torch.float32, device=params[0].device)
+    c = 0
+    with torch.no_grad():
+        for p, m in zip(params, masks):
+            dst = buf32[:, c:c + p.size(1)]
+            if m is None:
+                dst.copy_(p.detach())
+            else:
+                torch.mul(p.detach(), m, out=dst)
+            c += p.size(1)
+        if dtype == torch.bfloat16:
+            buf = torch.empty(F, ld, dtype=torch.bfloat16, device=buf32.device)
+            call("nc_cast_bf16", buf32, ld, None, 0, F, ld, buf, ld)
+        else:
+            buf = buf32
+    _PACK_CACHE[key] = (ver, buf)
+    return buf
+
+
+def _cat_f32(ts: Sequence[torch.Tensor], pad_to: Optional[int] = None) -> torch.Tensor:
+    flat = torch.cat([t.detach().reshape(-1).float() for t in ts])
+    if pad_to is not None and flat.numel() < pad_to:
+        flat = torch.cat([flat, flat.new_zeros(pad_to - flat.numel())])
+    return flat.contiguous()
+
+
+def _col_sum(x: torch.Tensor, n_cols: int) -> torch.Tensor:
+    out = torch.zeros(n_cols, dtype=torch.float32, device=x.device)
+    if x.size(0) > 0:
+        call("nc_col_sum", x, dtype_code(x.dtype), x.stride(0), x.size(0), n_cols, out)
+    return out
+
+
+# --------------------------------------------------------------------------- GATv2 encoder
+class EncoderGATv2Fn(torch.autograd.Function):
+    """fc_l1 + ReLU + the four GATv2Conv heads of nn/encoders.py:144-208 (n_fc_layers=1,
+    n_layers=1) for the first ``graph.n_dst`` nodes: returns [n_dst, 2P] = (mu | logstd) with
+    mu = conv_mu ++ addon_conv_mu and logstd = conv_logstd ++ addon_conv_logstd.
+
+    ``convs`` order in ``tensors``: for each of the NC convs (lin_l.weight, lin_l.bias,
+    lin_r.weight, lin_r.bias, att, bias); ``out_offsets[c]`` is the output column of conv c."""
+
+    @staticmethod
+    def forward(ctx, x_enc, graph: SubgraphCSR, n_feat: int, heads: int, out_offsets, out_width: int,
+                cache_key, W1, b1, *tensors):
+        NC = len(tensors) // 6
+        conv = [tensors[6 * c:6 * c + 6] for c in range(NC)]
+        act = x_enc.dtype
+        dev = x_enc.device
+        n_sub, n_dst = graph.n_nodes, graph.n_dst
+        assert x_enc.size(0) == n_sub
+        Hd = W1.size(0)
+        Cs = [cv[5].numel() for cv in conv]
+        widths = [heads * C for C in Cs]
+        offs = [sum(widths[:c]) for c in range(NC)]
+        NL = sum(widths)
+        ldl = pad8(NL)
+        seg_host = torch.tensor([[offs[c], Cs[c], out_offsets[c], 0] for c in range(NC)], dtype=torch.int32)
+        seg = seg_host.to(dev, non_blocking=True)
+        W1p = pack_rows((cache_key, "W1"), [W1], act, W1.size(1))
+        Wl = pack_rows((cache_key, "Wl"), [cv[0] for cv in conv], act, Hd)
+        Wr = pack_rows((cache_key, "Wr"), [cv[2] for cv in conv], act, Hd)
+        bl, br = _cat_f32([cv[1] for cv in conv]), _cat_f32([cv[3] for cv in conv])
+        att = _cat_f32([cv[4] for cv in conv], pad_to=ldl)
+        bias_out = torch.zeros(out_width, dtype=torch.float32, device=dev)
+        for c in range(NC):
+            bias_out[out_offsets[c]:out_offsets[c] + Cs[c]] = conv[c][5].detach()
+        ldh = pad8(Hd)
+        Hbuf = torch.zeros(n_sub, ldh, dtype=act, device=dev) if ldh != Hd else torch.empty(n_sub, ldh, dtype=act, device=dev)
+        ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
+        XL = torch.empty(n_sub, ldl, dtype=act, device=dev)
+        XR = torch.empty(max(n_dst, 1), ldl, dtype=act, device=dev)
+        ops.gemm(Hbuf, Wl, bias=bl, out=XL[:, :NL], M=n_sub, N=NL, K=Hd)
+        ops.gemm(Hbuf, Wr, bias=br, out=XR[:, :NL], M=n_dst, N=NL, K=Hd)
+        out = torch.empty(n_dst, out_width, dtype=torch.float32, device=dev)
+        alpha = torch.empty(max(graph.n_slots, 1) * NC * heads, dtype=torch.float32, device=dev)
+        call("nc_gatv2_fwd", XL, XR, dtype_code(act), ldl, att, bias_out, graph.rowptr, graph.col, n_dst,
+             seg, HostPtr(seg_host), NC, heads, graph.max_deg, 0.2, out, out.stride(0), alpha)
+        ctx.save_for_backward(x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr)
+        ctx.meta = (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
+                    [tuple(t.shape) for t in tensors], tuple(W1.shape))
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr = ctx.saved_tensors
+        (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
+         shapes, w1_shape) = ctx.meta
+        act, dev = x_enc.dtype, x_enc.device
+        n_sub, n_dst = graph.n_nodes, graph.n_dst
+        dout = dout.contiguous().float()
+        rptr, rdst, rslot = graph.reverse()
+        dXL = torch.empty(n_sub, ldl, dtype=act, device=dev)
+        dXR = torch.empty(max(n_dst, 1), ldl, dtype=act, device=dev)
+        if ldl != NL:
+            dXL[:, NL:].zero_()
+            dXR[:, NL:].zero_()
+        datt = torch.zeros(ldl, dtype=torch.float32, device=dev)
+        dbias = torch.zeros(out_width, dtype=torch.float32, device=dev)
+        ds = torch.empty_like(alpha)
+        call("nc_gatv2_bwd", XL, XR, dtype_code(act), ldl, att, graph.rowptr, graph.col, n_dst, n_sub,
+             rptr, rdst, rslot, seg, HostPtr(seg_host), NC, heads, graph.max_deg, 0.2, dout, dout.stride(0), alpha, ds,
+             dXL, dXR, datt, dbias)
+        # weight gradients of lin_l / lin_r (all convs in one GEMM each), bias gradients
+        dWl = ops.gemm(dXL, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=Hd, K=n_sub)
+        dWr = ops.gemm(dXR, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=Hd, K=n_dst) \
+            if n_dst > 0 else torch.zeros(NL, Hd, device=dev)
+        dbl = _col_sum(dXL, NL)
+        dbr = _col_sum(dXR[:n_dst], NL)
+        # dH = dXL @ Wl (+ dXR @ Wr on the seed rows)
+        dH = torch.empty(n_sub, pad8(Hd), dtype=torch.float32, device=dev)
+        ops.gemm(dXL, Wl, trans_b=True, out=dH[:, :Hd], M=n_sub, N=Hd, K=NL)
+        if n_dst > 0:
+            ops.gemm(dXR, Wr, trans_b=True, out=dH[:n_dst, :Hd], accumulate=True, M=n_dst, N=Hd, K=NL)
+        dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
+        call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
+        dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
+        db1 = _col_sum(dHp, Hd)
+        grads: List[Optional[torch.Tensor]] = []
+        for c in range(NC):
+            sl = slice(offs[c], offs[c] + widths[c])
+            grads += [dWl[sl].reshape(shapes[6 * c]), dbl[sl], dWr[sl].reshape(shapes[6 * c + 2]), dbr[sl],
+                      datt[sl].reshape(shapes[6 * c + 4]),
+                      dbias[out_offsets[c]:out_offsets[c] + Cs[c]]]
+        dW1 = dW1 if dW1.shape == w1_shape else dW1.contiguous()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            # only the trailing (embedding) columns of the encoder input can require grad
+            dxf = ops.gemm(dHp, W1p, trans_b=True, out_dtype=torch.float32, M=n_sub, N=n_feat, K=Hd)
+            dx = torch.zeros_like(x_enc, dtype=torch.float32)
+            dx[:, :n_feat] = dxf
+            dx = dx.to(x_enc.dtype)
+        return (dx, None, None, None, None, None, None, dW1, db1, *grads)
+
+
+# --------------------------------------------------------------------------- latent plumbing
+class GatherRowsFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, src, idx):
+        src = src.contiguous()
+        out = torch.empty(idx.numel(), src.size(1), dtype=torch.float32, device=src.device)
+        call("nc_gather_rows_f32", src, src.stride(0), idx, idx.numel(), src.size(1), out, out.stride(0))
+        ctx.save_for_backward(idx)
+        ctx.n_src = src.size(0)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (idx,) = ctx.saved_tensors
+        dout = dout.contiguous()
+        dsrc = torch.zeros(ctx.n_src, dout.size(1), dtype=torch.float32, device=dout.device)
+        call("nc_scatter_add_rows_f32", dout, dout.stride(0), idx, idx.numel(), dout.size(1), dsrc, dsrc.stride(0))
+        return dsrc, None
+
+
+class ReparamFn(torch.autograd.Function):
+    """z = (mu + eps * exp(logstd)) with inactive gene programs zeroed
+    (modules/vgaemodulemixin.py:34-41, modules/vgpgae.py:632-637)."""
+
+    @staticmethod
+    def forward(ctx, mu, logstd, eps, active):
+        R, P = mu.shape
+        z = torch.empty(R, P, dtype=torch.float32, device=mu.device)
+        call("nc_reparam_fwd", mu, mu.stride(0), logstd, logstd.stride(0), eps, eps.stride(0) if eps is not None else 0,
+             active, R, P, z, z.stride(0), None, 0)
+        ctx.save_for_backward(logstd, eps, active)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        logstd, eps, active = ctx.saved_tensors
+        dz = dz.contiguous()
+        R, P = dz.shape
+        dmu = torch.empty_like(dz)
+        dls = torch.empty_like(dz)
+        call("nc_reparam_bwd", logstd, logstd.stride(0), eps, eps.stride(0) if eps is not None else 0, active, R, P,
+             dz, dz.stride(0), dmu, dmu.stride(0), dls, dls.stride(0))
+        return dmu, dls, None, None
+
+
+class KLFn(torch.autograd.Function):
+    """modules/losses.py:255-284."""
+
+    @staticmethod
+    def forward(ctx, mu, logstd):
+        R, P = mu.shape
+        acc = torch.zeros(1, dtype=torch.float64, device=mu.device)
+        dmu = torch.empty(R, P, dtype=torch.float32, device=mu.device)
+        dls = torch.empty(R, P, dtype=torch.float32, device=mu.device)
+        call("nc_kl_fwd_bwd", mu, mu.stride(0), logstd, logstd.stride(0), R, P, 1.0, acc, dmu, P, dls, P)
+        ctx.save_for_backward(dmu, dls)
+        return acc.float().reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        dmu, dls = ctx.saved_tensors
+        return dmu * g, dls * g
+
+
+class CosineFn(torch.autograd.Function):
+    """nn/decoders.py:56-62 + nn/utils.py:8-36: rows [0, n) of z against rows [n, 2n)."""
+
+    @staticmethod
+    def forward(ctx, z):
+        z = z.contiguous()
+        n = z.size(0) // 2
+        logits = torch.empty(n, dtype=torch.float32, device=z.device)
+        norms = torch.empty(2 * n, dtype=torch.float32, device=z.device)
+        call("nc_cosine_fwd", z, z.stride(0), z.size(1), n, logits, norms)
+        ctx.save_for_backward(z, logits, norms)
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        z, logits, norms = ctx.saved_tensors
+        n = z.size(0) // 2
+        dz = torch.zeros_like(z)
+        call("nc_cosine_bwd", z, z.stride(0), z.size(1), n, logits, norms, dlogits.contiguous(), dz, dz.stride(0))
+        return dz
+
+
+class BCEFn(torch.autograd.Function):
+    """modules/losses.py:123-166 (pos_weight = #neg / #pos over the included edges)."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, incl):
+        n = logits.numel()
+        loss = torch.empty(1, dtype=torch.float32, device=logits.device)
+        dlog = torch.empty(n, dtype=torch.float32, device=logits.device)
+        call("nc_bce_fwd_bwd", logits.contiguous(), labels.contiguous().float(), incl, n, 1.0, loss, dlog)
+        ctx.save_for_backward(dlog)
+        return loss.reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        (dlog,) = ctx.saved_tensors
+        return dlog * g, None, None
+
+
+# --------------------------------------------------------------------------- masked decoder
+class MaskedDecoderFn(torch.autograd.Function):
+    """logits = cat(z, embed) @ (W * mask)^T for the packed decoder weight
+    [F, P_prior | P_addon | n_embed] (nn/layers.py:83-142, nn/layercomponents.py:53-81).
+    The GP mask is re-applied to the weight gradient in the GEMM epilogue."""
+
+    @staticmethod
+    def forward(ctx, zcat, act_dtype, cache_key, dyn_masks, *params_and_masks):
+        n = len(params_and_masks) // 2
+        params, masks = params_and_masks[:n], params_and_masks[n:]
+        eff_masks = []
+        for m, d in zip(masks, dyn_masks):
+            if m is not None and d is not None:
+                m = m * d
+            elif d is not None:
+                m = d
+            eff_masks.append(m)
+        Wp = pack_cols(cache_key, params, eff_masks, act_dtype)
+        K = sum(p.size(1) for p in params)
+        F = params[0].size(0)
+        nb = zcat.size(0)
+        za = torch.zeros(nb, pad8(K), dtype=act_dtype, device=zcat.device)
+        za[:, :K] = zcat.detach()
+        logits = ops.gemm(za, Wp, out_dtype=torch.float32, M=nb, N=F, K=K)
+        ctx.save_for_backward(za, Wp, *[m for m in eff_masks if m is not None])
+        ctx.meta = (K, F, [p.size(1) for p in params], [m is not None for m in eff_masks], act_dtype)
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        za, Wp = ctx.saved_tensors[:2]
+        saved_masks = list(ctx.saved_tensors[2:])
+        K, F, widths, has_mask, act = ctx.meta
+        nb = za.size(0)
+        dl = torch.zeros(nb, pad8(F), dtype=act, device=za.device)
+        dl[:, :F] = dlogits
+        if any(has_mask):
+            mfull = torch.ones(F, pad8(K), dtype=torch.float32, device=za.device)
+            c = 0
+            for w, hm in zip(widths, has_mask):
+                if hm:
+                    mfull[:, c:c + w] = saved_masks.pop(0)
+                c += w
+        else:
+            mfull = None
+        dW = ops.gemm(dl, za, trans_a=True, trans_b=True, out_dtype=torch.float32, mask=mfull, M=F, N=K, K=nb)
+        dz = ops.gemm(dl, Wp, trans_b=True, out_dtype=torch.float32, M=nb, N=K, K=F)
+        grads, c = [], 0
+        for w in widths:
+            grads.append(dW[:, c:c + w])
+            c += w
+        return (dz, None, None, None, *grads, *([None] * len(widths)))
+
+
+class NBLossFusedFn(torch.autograd.Function):
+    """softmax over all features -> exp(log_lib) * softmax -> reconstructed-column select ->
+    mean NB negative log-likelihood, value and gradients in one kernel
+    (nn/layers.py:143, nn/decoders.py:168, modules/vgpgae.py:714-749, modules/losses.py:169-212)."""
+
+    @staticmethod
+    def forward(ctx, logits, theta_param, x_full, sel):
+        nb, F = logits.shape
+        dev = logits.device
+        acc = torch.zeros(1, dtype=torch.float64, device=dev)
+        dlog = torch.empty(nb, F, dtype=torch.float32, device=dev)
+        dth = torch.zeros(F, dtype=torch.float32, device=dev)
+        means = torch.empty(nb, F, dtype=torch.float32, device=dev)
+        logits = logits.contiguous()
+        call("nc_nb_loss_fused", logits, logits.stride(0), x_full, x_full.stride(0), sel, theta_param.detach(),
+             nb, F, 1.0 / nb, means, F, acc, dlog, F, dth)
+        ctx.save_for_backward(dlog, dth)
+        ctx.mark_non_differentiable(means)
+        return (acc / nb).float().reshape(()), means
+
+    @staticmethod
+    def backward(ctx, g, _gm):
+        dlog, dth = ctx.saved_tensors
+        return dlog * g, dth * g, None, None
+
+
+# --------------------------------------------------------------------------- weight regularisers
+class WeightRegFn(torch.autograd.Function):
+    """sum over the given decoder weights of  l1 * sum |W * l1mask|  +  gl * sum_c sqrt(cnt_c) ||W[:,c]||_2
+    (modules/losses.py:287-339 and :215-252).  ``l1masks[i]``: uint8 [F, P] or None (all);
+    ``gl_masks[i]``: the MaskedLinear mask buffer [F, P] (count of non-masked weights) or None."""
+
+    @staticmethod
+    def forward(ctx, l1_scale, gl_scale, l1masks, gl_masks, *weights):
+        total = torch.zeros((), dtype=torch.float32, device=weights[0].device)
+        coefs = []
+        for W, lm, gm in zip(weights, l1masks, gl_masks):
+            F, P = W.shape
+            dev = W.device
+            abs_sum = torch.zeros(P, dtype=torch.float32, device=dev) if l1_scale != 0 else None
+            sq = torch.zeros(P, dtype=torch.float32, device=dev) if gl_scale != 0 else None
+            cnt = torch.zeros(P, dtype=torch.float32, device=dev) if gl_scale != 0 else None
+            Wd = W.detach()
+            call("nc_weight_col_stats", Wd, Wd.stride(0), F, P, lm, gm if gl_scale != 0 else None,
+                 gm.stride(0) if (gm is not None and gl_scale != 0) else 0, abs_sum, sq, None, cnt)
+            coef = None
+            if l1_scale != 0:
+                total = total + l1_scale * abs_sum.sum()
+            if gl_scale != 0:
+                norm = sq.sqrt()
+                root = cnt.sqrt()
+                total = total + gl_scale * (root * norm).sum()
+                coef = torch.where(norm > 0, gl_scale * root / norm.clamp_min(1e-30), torch.zeros_like(norm))
+            coefs.append(coef)
+        ctx.l1_scale = l1_scale
+        ctx.l1masks = l1masks
+        ctx.coefs = coefs
+        ctx.save_for_backward(*weights)
+        return total
+
+    @staticmethod
+    def backward(ctx, g):
+        grads = []
+        for W, lm, coef in zip(ctx.saved_tensors, ctx.l1masks, ctx.coefs):
+            dW = torch.zeros_like(W, dtype=torch.float32)
+            Wd = W.detach()
+            call("nc_weight_reg_grad", Wd, Wd.stride(0), W.size(0), W.size(1), float(ctx.l1_scale), lm, coef,
+                 dW, dW.stride(0))
+            grads.append(dW * g)
+        return (None, None, None, None, *grads)
+
+
+# --------------------------------------------------------------------------- attention aggregator
+class AttentionAggregatorFn(torch.autograd.Function):
+    """nn/aggregators.py:113-156.  Not covered by the round-1 kernels:
+    fails loudly instead of falling back to a framework implementation."""
+
+    @staticmethod
+    def forward(ctx, x, graph, heads, slope, act_dtype, cache_key, w_l, w_r, attn):
+        raise NotImplementedError("node_label_method='one-hop-attention' has no CUDA kernel yet "
+                                  "(DESIGN.md 'not yet covered'); use 'one-hop-norm' or 'one-hop-sum'")
+
+
+# --------------------------------------------------------------------------- GCN encoder
+class EncoderGCNFn(torch.autograd.Function):
+    """fc_l1 + ReLU + the GCNConv heads of nn/encoders.py:105-117: one
+    packed GEMM for the four ``lin`` weights, then the symmetric-normalised CSR SpMM with
+    subgraph-local degrees and exactly one self loop per node.  ``tensors``: (lin.weight, bias)
+    per conv in output-column order."""
+
+    @staticmethod
+    def forward(ctx, x_enc, graph: SubgraphCSR, n_feat: int, out_offsets, out_width: int, cache_key, W1, b1,
+                *tensors):
+        NC = len(tensors) // 2
+        Ws, bs = [tensors[2 * c] for c in range(NC)], [tensors[2 * c + 1] for c in range(NC)]
+        act, dev = x_enc.dtype, x_enc.device
+        n_sub, n_dst = graph.n_nodes, graph.n_dst
+        Hd = W1.size(0)
+        Cs = [w.size(0) for w in Ws]
+        assert list(out_offsets) == [sum(Cs[:c]) for c in range(NC)] and sum(Cs) == out_width
+        W1p = pack_rows((cache_key, "W1"), [W1], act, W1.size(1))
+        Wall = pack_rows((cache_key, "Wgcn"), Ws, act, Hd)
+        bias_out = _cat_f32(bs)
+        ldh = pad8(Hd)
+        Hbuf = torch.zeros(n_sub, ldh, dtype=act, device=dev)
+        ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
+        ldw = pad8(out_width)
+        XW = torch.zeros(n_sub, ldw, dtype=act, device=dev)
+        ops.gemm(Hbuf, Wall, out=XW[:, :out_width], M=n_sub, N=out_width, K=Hd)
+        w, wself = graph.gcn_weights(use_out_degree=False)
+        out = ops.spmm_csr(XW, graph.rowptr, graph.col, w, wself, True, n_dst, bias=bias_out, n_cols=out_width)
+        ctx.save_for_backward(x_enc, Hbuf, W1p, Wall, w, wself)
+        ctx.meta = (graph, n_feat, out_width, NC, Cs, Hd, [tuple(t.shape) for t in tensors])
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x_enc, Hbuf, W1p, Wall, w, wself = ctx.saved_tensors
+        graph, n_feat, out_width, NC, Cs, Hd, shapes = ctx.meta
+        act, dev = x_enc.dtype, x_enc.device
+        n_sub, n_dst = graph.n_nodes, graph.n_dst
+        dout = dout.contiguous().float()
+        rptr, rdst, rslot = graph.reverse()
+        rd = rdst.long()
+        is_self = rslot == (graph.rowptr[rd + 1] + rdst)
+        e_idx = (rslot - rdst).long().clamp_(0, max(w.numel() - 1, 0))
+        rw = torch.where(is_self, wself[rd.clamp_(0, max(n_dst - 1, 0))], w[e_idx]).contiguous()
+        ldw = pad8(out_width)
+        dXW = torch.zeros(n_sub, ldw, dtype=act, device=dev)
+        ops.spmm_csr(dout, rptr, rdst, rw, None, False, n_sub, out=dXW[:, :out_width], n_cols=out_width)
+        dbias = _col_sum(dout, out_width)
+        dWall = ops.gemm(dXW, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=out_width, N=Hd, K=n_sub)
+        dH = torch.empty(n_sub, pad8(Hd), dtype=torch.float32, device=dev)
+        ops.gemm(dXW, Wall, trans_b=True, out=dH[:, :Hd], M=n_sub, N=Hd, K=out_width)
+        dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
+        call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
+        dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
+        db1 = _col_sum(dHp, Hd)
+        grads, r = [], 0
+        for c in range(NC):
+            grads += [dWall[r:r + Cs[c]], dbias[r:r + Cs[c]]]
+            r += Cs[c]
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dxf = ops.gemm(dHp, W1p, trans_b=True, out_dtype=torch.float32, M=n_sub, N=n_feat, K=Hd)
+            dx = torch.zeros_like(x_enc, dtype=torch.float32)
+            dx[:, :n_feat] = dxf
+            dx = dx.to(x_enc.dtype)
+        return (dx, None, None, None, None, None, dW1, db1, *grads)

@@ -1,0 +1,127 @@
+"""
+Encoder of the VGPGAE (reference: nn/encoders.py:12-208).  Same constructor, parameters and
+state_dict keys; the arithmetic is one fused autograd Function over hand-written kernels
+(tcgen05 / SIMT GEMMs + the fused GATv2 edge kernels or the CSR SpMM for GCN).
+"""
+from typing import Literal, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..functional import EncoderGATv2Fn, EncoderGCNFn, SubgraphCSR
+from ..ops import pad8
+from .conv import GATv2Conv, GCNConv
+
+
+class Encoder(nn.Module):
+    """fc layer -> ReLU -> message passing heads producing ``mu`` and ``logstd`` of the latent
+    normal (prior gene programs ++ add-on gene programs).
+
+    Parameters are those of the reference ``Encoder``; ``use_bn`` is accepted and unused
+    exactly as there (nn/encoders.py:52-53 documents it, the body never reads it).
+    Round-1 kernel coverage: ``n_fc_layers == 1``, ``n_layers == 1``, ``dropout_rate == 0``.
+    """
+
+    def __init__(self,
+                 n_input: int,
+                 n_cat_covariates_embed_input: int,
+                 n_hidden: int,
+                 n_latent: int,
+                 n_addon_latent: int = 100,
+                 n_fc_layers: int = 1,
+                 conv_layer: Literal["gcnconv", "gatv2conv"] = "gatv2conv",
+                 n_layers: int = 1,
+                 cat_covariates_embed_mode: Literal["input", "hidden"] = "input",
+                 n_attention_heads: int = 4,
+                 dropout_rate: float = 0.,
+                 activation=torch.relu,
+                 use_bn: bool = True):
+        super().__init__()
+        print("ENCODER -> "
+              f"n_input: {n_input}, n_cat_covariates_embed_input: {n_cat_covariates_embed_input}, "
+              f"n_hidden: {n_hidden}, n_latent: {n_latent}, n_addon_latent: {n_addon_latent}, "
+              f"n_fc_layers: {n_fc_layers}, n_layers: {n_layers}, conv_layer: {conv_layer}, "
+              f"n_attention_heads: {n_attention_heads if conv_layer == 'gatv2conv' else '0'}, "
+              f"dropout_rate: {dropout_rate}, ")
+        if n_fc_layers != 1 or n_layers != 1:
+            raise NotImplementedError("nichecompass_b200 kernels cover n_fc_layers=1, n_layers=1 "
+                                      "(the reference defaults); see DESIGN.md 'not yet covered'")
+        if dropout_rate != 0.:
+            raise NotImplementedError("dropout in the encoder is not implemented in the CUDA path")
+        if cat_covariates_embed_mode != "input" and n_cat_covariates_embed_input != 0:
+            raise NotImplementedError("cat_covariates_embed_mode='hidden' is not implemented")
+        self.n_latent = n_latent
+        self.n_addon_latent = n_addon_latent
+        self.n_layers = n_layers
+        self.n_fc_layers = n_fc_layers
+        self.conv_layer = conv_layer
+        self.n_attention_heads = n_attention_heads
+        self.cat_covariates_embed_mode = cat_covariates_embed_mode
+        self.n_input = n_input + n_cat_covariates_embed_input
+        self.fc_l1 = nn.Linear(self.n_input, n_hidden)
+        conv = (lambda c: GATv2Conv(n_hidden, c, heads=n_attention_heads)) if conv_layer == "gatv2conv" \
+            else (lambda c: GCNConv(n_hidden, c))
+        if conv_layer not in ("gatv2conv", "gcnconv"):
+            raise ValueError(f"unknown conv_layer {conv_layer}")
+        self.conv_mu = conv(n_latent)
+        self.conv_logstd = conv(n_latent)
+        if n_addon_latent != 0:
+            self.addon_conv_mu = conv(n_addon_latent)
+            self.addon_conv_logstd = conv(n_addon_latent)
+        self.compute_dtype = torch.float32
+        self._key = id(self)
+
+    # ------------------------------------------------------------------ fused path
+    @property
+    def n_gps(self) -> int:
+        return self.n_latent + self.n_addon_latent
+
+    def _convs(self):
+        """Convs in output order with their output column offsets in the (mu | logstd) matrix."""
+        P = self.n_gps
+        convs = [(self.conv_mu, 0)]
+        if self.n_addon_latent != 0:
+            convs.append((self.addon_conv_mu, self.n_latent))
+        convs.append((self.conv_logstd, P))
+        if self.n_addon_latent != 0:
+            convs.append((self.addon_conv_logstd, P + self.n_latent))
+        return convs
+
+    def encode(self, x_enc: torch.Tensor, graph: SubgraphCSR) -> torch.Tensor:
+        """``x_enc``: [n_sub, pad8(n_input)] in ``compute_dtype`` (log1p counts ++ optional
+        embedding, zero padded).  Returns (mu | logstd) [graph.n_dst, 2 * n_gps] fp32."""
+        convs = self._convs()
+        offs = [o for _, o in convs]
+        if self.conv_layer == "gatv2conv":
+            tensors = [t for c, _ in convs for t in c.param_tuple()]
+            return EncoderGATv2Fn.apply(x_enc, graph, self.n_input, self.n_attention_heads, offs,
+                                        2 * self.n_gps, self._key, self.fc_l1.weight, self.fc_l1.bias,
+                                        *tensors)
+        tensors = [t for c, _ in convs for t in (c.lin.weight, c.bias)]
+        return EncoderGCNFn.apply(x_enc, graph, self.n_input, offs, 2 * self.n_gps, self._key,
+                                  self.fc_l1.weight, self.fc_l1.bias, *tensors)
+
+    def pack_input(self, x: torch.Tensor, cat_covariates_embed: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Dense fp32 [n, F] (already log-transformed) (+ embedding) -> padded compute-dtype tile."""
+        n = x.size(0)
+        buf = torch.zeros(n, pad8(self.n_input), dtype=self.compute_dtype, device=x.device)
+        buf[:, :x.size(1)] = x
+        if cat_covariates_embed is not None and self.cat_covariates_embed_mode == "input":
+            if cat_covariates_embed.requires_grad:
+                full = torch.cat((x, cat_covariates_embed), dim=1).to(self.compute_dtype)
+                return torch.nn.functional.pad(full, (0, buf.size(1) - full.size(1)))
+            buf[:, x.size(1):x.size(1) + cat_covariates_embed.size(1)] = cat_covariates_embed
+        return buf
+
+    # ------------------------------------------------------------------ reference signature
+    def forward(self,
+                x: torch.Tensor,
+                edge_index: torch.Tensor,
+                cat_covariates_embed: Optional[torch.Tensor] = None
+                ) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Reference call signature (nn/encoders.py:144-208): returns ``mu`` and ``logstd`` for
+        ALL nodes of the batch."""
+        graph = SubgraphCSR.from_edge_index(edge_index, x.size(0))
+        ml = self.encode(self.pack_input(x, cat_covariates_embed), graph)
+        P = self.n_gps
+        return ml[:, :P], ml[:, P:]

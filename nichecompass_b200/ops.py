@@ -49,8 +49,9 @@ def reverse_csr(rowptr, col, n_nodes: int, n_rows: int, add_self: bool, n_entrie
     if n_entries is None:
         n_entries = col.numel() + (n_rows if add_self else 0)
     rptr = torch.empty(n_nodes + 1, dtype=torch.int32, device=dev)
-    rdst = torch.empty(max(n_entries, 1), dtype=torch.int32, device=dev)
-    rslot = torch.empty(max(n_entries, 1), dtype=torch.int32, device=dev)
+    # zero-filled: entries past rptr[n_nodes] (the buffers are sized by an upper bound) stay valid ids
+    rdst = torch.zeros(max(n_entries, 1), dtype=torch.int32, device=dev)
+    rslot = torch.zeros(max(n_entries, 1), dtype=torch.int32, device=dev)
     cursor = torch.empty(max(n_nodes, 1), dtype=torch.int32, device=dev)
     call("nc_reverse_csr", rowptr, col, n_nodes, n_rows, int(add_self), rptr, rdst, rslot, cursor)
     return rptr, rdst, rslot
@@ -58,12 +59,13 @@ def reverse_csr(rowptr, col, n_nodes: int, n_rows: int, add_self: bool, n_entrie
 
 # --------------------------------------------------------------------------- SpMM / gathers
 def spmm_csr(x: torch.Tensor, rowptr, col, w, wself, skip_self: bool, n_rows: int,
-             out_dtype: torch.dtype = torch.float32, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+             out_dtype: torch.dtype = torch.float32, out: Optional[torch.Tensor] = None,
+             bias: Optional[torch.Tensor] = None, n_cols: Optional[int] = None) -> torch.Tensor:
     assert x.dim() == 2 and x.stride(1) == 1
-    n_cols = x.size(1)
+    n_cols = x.size(1) if n_cols is None else n_cols
     if out is None:
         out = torch.empty(n_rows, n_cols, dtype=out_dtype, device=x.device)
-    call("nc_spmm_csr", x, dtype_code(x.dtype), x.stride(0), n_cols, rowptr, col, w, wself,
+    call("nc_spmm_csr", x, dtype_code(x.dtype), x.stride(0), n_cols, rowptr, col, w, wself, bias,
          int(skip_self), n_rows, out, dtype_code(out.dtype), out.stride(0))
     return out
 

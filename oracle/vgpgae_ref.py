@@ -253,6 +253,11 @@ class VGPGAERef:
             active = self.get_active_gp_mask()
             z = z.clone()
             z[:, ~active] = 0
+            if not self.training:
+                # in eval mode the reference's z IS self.mu (vgaemodulemixin.py:39-41), so the
+                # in-place zeroing at vgpgae.py:637 also lands in output["mu"]
+                mu = z
+                out["mu"] = z
         if decoder == "graph":
             out["edge_recon_labels"] = batch.edge_label
             n_cov = len(c.get("cat_covariates_embeds_nums", []))

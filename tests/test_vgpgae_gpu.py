@@ -1,0 +1,153 @@
+"""
+Tier-2 parity (GPU box): the CUDA VGPGAE module against the CPU oracle on identical weights,
+sampled batches and injected reparameterisation noise.
+Tolerances (BASELINE.json north_star): fp32 mode 1e-5 relative; bf16 mode 1e-3 relative on
+per-batch losses (element-wise tensors in bf16 mode are checked at the bf16 rounding level).
+"""
+import copy
+import io
+import contextlib
+
+import pytest
+import torch
+
+from oracle import sampler_ref as R
+from oracle.vgpgae_ref import VGPGAERef, init_params
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+LAM = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lambda_l1_addon=30.,
+           lambda_group_lasso=2., lambda_gene_expr_recon=300., lambda_edge_recon=500000.)
+
+
+def build_module(cfg, params, conv_layer, node_label_method):
+    from nichecompass_b200.modules import VGPGAE
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+                   n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"],
+                   n_addon_gp=cfg["n_addon_gp"], cat_covariates_embeds_nums=[],
+                   n_output_genes=cfg["n_output_genes"],
+                   target_rna_decoder_mask=cfg["target_rna_mask"],
+                   source_rna_decoder_mask=cfg["source_rna_mask"],
+                   features_idx_dict=copy.deepcopy(cfg["features_idx_dict"]),
+                   features_scale_factors=torch.ones(2 * cfg["n_output_genes"]),
+                   conv_layer_encoder=conv_layer, encoder_n_attention_heads=cfg["heads"],
+                   node_label_method=node_label_method, active_gp_thresh_ratio=0.01,
+                   include_cat_covariates_contrastive_loss=False)
+    missing, unexpected = m.load_state_dict({k: v.float() for k, v in params.items()}, strict=True)
+    return m.to(DEV)
+
+
+def make_batches(adata, edge_bs=16, node_bs=8):
+    torch.manual_seed(0)
+    x = H.dense_x(adata, torch.float64)
+    n = adata.n_obs
+    ei = R.adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
+    splits = R.edge_level_split(ei, n, 0.1)
+    train_mask, _ = R.node_level_split_mask(n, 0.1)
+    nl = R.NodeLoaderRef(x, ei, n, train_mask, node_bs)
+    ll = R.LinkLoaderRef(x, splits["train"].edge_index, n, splits["train"].edge_label_index, edge_bs)
+    return next(iter(nl)), next(iter(ll))
+
+
+def run_pair(conv_layer, node_label_method, n_addon, dtype, n_genes=40, use_only_active=False, train=True):
+    adata = H.tiny_problem(n_cells=150, n_genes=n_genes, n_prior_gp=12)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=n_addon, conv_layer=conv_layer,
+                                  node_label_method=node_label_method)
+    p32 = init_params(cfg, seed=3)
+    if use_only_active:
+        p32["running_mean_abs_mu"] = torch.rand(cfg["n_prior_gp"] + n_addon) ** 6
+    p64 = {k: v.double().clone().requires_grad_(v.is_floating_point() and not k.endswith(("mask", "abs_mu")))
+           for k, v in p32.items()}
+    orc = VGPGAERef(cfg, p64)
+    orc.training = train
+    mod = build_module(cfg, p32, conv_layer, node_label_method).set_compute_dtype(dtype)
+    mod.train(train)
+    node_b, edge_b = make_batches(adata)
+    P = cfg["n_prior_gp"] + n_addon
+    g = torch.Generator().manual_seed(5)
+    eps_n = torch.randn(node_b.batch_size, P, generator=g, dtype=torch.float64)
+    eps_e = torch.randn(2 * edge_b.edge_label_index.size(1), P, generator=g, dtype=torch.float64)
+    on = orc.forward(node_b, "omics", use_only_active_gps=use_only_active, eps=eps_n)
+    oe = orc.forward(edge_b, "graph", use_only_active_gps=use_only_active, eps=eps_e)
+    ol = orc.loss(oe, on, **LAM)
+    if train:
+        ol["optim_loss"].backward()
+    mod._eps_queue = [eps_n, eps_e]
+    nb_cuda = H.batch_to(node_b, torch.float32, DEV)
+    eb_cuda = H.batch_to(edge_b, torch.float32, DEV)
+    with torch.set_grad_enabled(train):
+        cn = mod(nb_cuda, "omics", use_only_active_gps=use_only_active)
+        ce = mod(eb_cuda, "graph", use_only_active_gps=use_only_active)
+        cl = mod.loss(ce, cn, **LAM)
+    if train:
+        cl["optim_loss"].backward()
+    return orc, mod, (on, oe, ol), (cn, ce, cl), p64
+
+
+@pytest.mark.parametrize("conv_layer,node_label_method,n_addon,n_genes", [
+    ("gatv2conv", "one-hop-norm", 4, 40),
+    ("gatv2conv", "one-hop-sum", 0, 43),
+    ("gcnconv", "one-hop-norm", 4, 40),
+    ("gatv2conv", "one-hop-norm", 3, 41),     # C % 4 != 0 -> scalar kernel paths
+])
+def test_fp32_forward_loss_grads(conv_layer, node_label_method, n_addon, n_genes):
+    orc, mod, (on, oe, ol), (cn, ce, cl), p64 = run_pair(conv_layer, node_label_method, n_addon,
+                                                         torch.float32, n_genes)
+    tol = 1e-5
+    for k in ("mu", "logstd", "target_rna_nb_means", "source_rna_nb_means"):
+        assert H.rel_err(cn[k], on[k]) < tol, k
+    for k in ("target_rna", "source_rna"):
+        assert H.rel_err(cn["node_labels"][k], on["node_labels"][k]) < 1e-6, k
+    for k in ("mu", "logstd", "edge_recon_logits"):
+        assert H.rel_err(ce[k], oe[k]) < tol, k
+    for k, v in ol.items():
+        assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(v)) < tol, k
+    assert H.rel_err(mod.running_mean_abs_mu, orc.running_mean_abs_mu) < tol
+    checked = 0
+    for k, p in mod.named_parameters():
+        ref = p64[k].grad
+        if ref is None:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+            continue
+        assert p.grad is not None, k
+        assert H.rel_err(p.grad, ref) < 2e-5, k
+        checked += 1
+    assert checked >= 8
+
+
+def test_bf16_losses_and_grads():
+    orc, mod, (on, oe, ol), (cn, ce, cl), p64 = run_pair("gatv2conv", "one-hop-norm", 4, torch.bfloat16)
+    for k in ("global_loss", "optim_loss", "edge_recon_loss", "gene_expr_recon_loss", "kl_reg_loss"):
+        assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(ol[k])) < 2e-3, k
+    assert H.rel_err(cn["mu"], on["mu"]) < 2e-2
+    errs = {k: H.rel_err(p.grad, p64[k].grad) for k, p in mod.named_parameters() if p64[k].grad is not None}
+    print({k: f"{v:.2e}" for k, v in errs.items()})
+    worst = max(errs.values())
+    assert worst < 6e-2, errs
+
+
+@pytest.mark.parametrize("train", [True, False])
+def test_only_active_gps(train):
+    orc, mod, (on, oe, ol), (cn, ce, cl), _ = run_pair("gatv2conv", "one-hop-norm", 4, torch.float32,
+                                                       use_only_active=True, train=train)
+    assert torch.equal(mod.get_active_gp_mask().cpu(), orc.get_active_gp_mask())
+    assert cn["target_rna_nb_means"].shape == on["target_rna_nb_means"].shape
+    for k in ("mu", "target_rna_nb_means", "source_rna_nb_means"):
+        assert H.rel_err(cn[k], on[k]) < 1e-5, k
+    for k, v in ol.items():
+        assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(v)) < 1e-5, k
+    assert H.rel_err(mod.running_mean_abs_mu, orc.running_mean_abs_mu) < 1e-5
+
+
+def test_latent_representation_eval():
+    orc, mod, _, _, _ = run_pair("gatv2conv", "one-hop-norm", 4, torch.float32, train=False)
+    adata = H.tiny_problem(n_cells=150, n_genes=40, n_prior_gp=12)
+    node_b, _ = make_batches(adata)
+    mu_o, std_o = orc.get_latent_representation(node_b, only_active_gps=True, return_mu_std=True)
+    with torch.no_grad():
+        mu_c, std_c = mod.get_latent_representation(H.batch_to(node_b, torch.float32, DEV),
+                                                    only_active_gps=True, return_mu_std=True)
+    assert H.rel_err(mu_c, mu_o) < 1e-5 and H.rel_err(std_c, std_o) < 1e-5
