@@ -223,6 +223,27 @@ int nc_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float 
 int nc_cast_bf16(const float* src, int64_t lds, const float* mask, int64_t ldmask, int32_t R,
                  int32_t C, void* dst, int64_t ldd, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * GPU CSR neighbourhood sampler (PyG NeighborLoader / LinkNeighborLoader + pyg-lib
+ * neighbor_sample + induced subgraph: data/dataloaders.py:64-100).
+ * g_rowptr/g_col: CSC of the message-passing graph (incoming neighbours sorted by source id).
+ * seeds: unique global node ids.  n_hops >= 1; k_neighbors < 0 keeps all neighbours, otherwise
+ * the k slots with the smallest splitmix64(rng_seed, batch_id, node, slot) keys.
+ * slot_ws: int32[n_graph_nodes] persistent workspace that must hold INT32_MAX everywhere on
+ * entry and is restored on exit (nc_fill_i32 once).  Outputs: n_id[cap_nodes] (local -> global,
+ * seeds first, then discovery order), local dst-CSR rowptr[cap_nodes+1] / col[cap_edges].
+ * cand_ws: int32[2*cap_nodes + 3*cap_cand + 2] scratch.  counts: int32[8] on the device =
+ * {n_sub, E_sub, overflow flag, longest row, ...}; nothing is read back by the library.      */
+int nc_sample_subgraph(const int32_t* g_rowptr, const int32_t* g_col, const int32_t* seeds,
+                       int32_t n_seed, int32_t n_hops, int32_t k_neighbors, int64_t rng_seed,
+                       int64_t batch_id, int32_t* slot_ws, int32_t* n_id, int32_t cap_nodes,
+                       int32_t* rowptr, int32_t* col, int32_t cap_edges, int32_t* cand_ws,
+                       int32_t cap_cand, int32_t* counts, void* stream);
+/* torch.unique(ids, return_inverse=True) for the link-batch seeds (sorted ascending), n <= 16384. */
+int nc_unique_sorted_i32(const int32_t* ids, int32_t n, int32_t* uniq, int32_t* inverse,
+                         int32_t* n_unique, void* stream);
+int nc_fill_i32(int32_t* p, int64_t n, int32_t value, void* stream);
+
 /* Bias gradients and ReLU backward of the encoder linears (autograd of nn/encoders.py:179):
  * out[c] += sum_r x[r, c];   out = dh * (h > 0) cast to the activation dtype.              */
 int nc_col_sum(const void* x, int dtype, int64_t ld, int32_t R, int32_t C, float* out,
