@@ -98,7 +98,8 @@ def dtype_code(t: torch.dtype) -> int:
 def ptr(t: Optional[torch.Tensor]):
     if t is None:
         return None
-    if not t.is_cuda:
+    if not t.is_cuda and not t.is_pinned():
+        # pinned host memory is device-addressable under UVA (host-resident count store)
         raise NicheCompassCudaError("nichecompass_b200 kernels need CUDA tensors (no CPU fallback)")
     return ctypes.c_void_p(t.data_ptr())
 

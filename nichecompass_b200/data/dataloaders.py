@@ -42,9 +42,19 @@ class NodeLoader:
         self.rng_seed = rng_seed
         self._batch_counter = 0
         self._input_dev = None
+        self.rank, self.world_size = 0, 1
+
+    def set_shard(self, rank: int, world_size: int):
+        """Data parallelism: this process yields batches rank, rank + W, ... of the common
+        permutation (wrapping around so that every rank yields the same number of batches)."""
+        self.rank, self.world_size = int(rank), int(world_size)
+
+    @property
+    def n_batches_total(self) -> int:
+        return math.ceil(self.input_nodes.numel() / self.batch_size)
 
     def __len__(self) -> int:
-        return math.ceil(self.input_nodes.numel() / self.batch_size)
+        return math.ceil(self.n_batches_total / self.world_size)
 
     def __iter__(self) -> Iterator[SampledBatch]:
         g = self.data.device_graph()
@@ -53,13 +63,14 @@ class NodeLoader:
             self._input_dev = self.input_nodes.to(dev, torch.int32)
         order = _epoch_permutation(self.input_nodes.numel(), self.shuffle).to(dev)
         cats = self.data.cats_device()
-        for b in range(len(self)):
+        for i in range(len(self)):
+            b = (i * self.world_size + self.rank) % self.n_batches_total
+            batch_id = self._batch_counter + self.rank
+            self._batch_counter += self.world_size
             idx = order[b * self.batch_size:(b + 1) * self.batch_size]
             seeds = self._input_dev[idx].contiguous()
             n_seed = seeds.numel()
-            n_id, graph = sample_subgraph(g, seeds, n_seed, self.num_neighbors, self.rng_seed,
-                                          self._batch_counter)
-            self._batch_counter += 1
+            n_id, graph = sample_subgraph(g, seeds, n_seed, self.num_neighbors, self.rng_seed, batch_id)
             batch = SampledBatch(self.data.store, n_id, graph, n_seed, cats)
             batch.batch_size = n_seed
             batch.input_id = idx
@@ -82,9 +93,19 @@ class LinkLoader:
         self.rng_seed = rng_seed
         self._batch_counter = 0
         self._pos_dev = None
+        self.rank, self.world_size = 0, 1
+
+    def set_shard(self, rank: int, world_size: int):
+        """See ``NodeLoader.set_shard``.  Every rank draws the negatives of ALL batches so that the
+        host generators of the ranks stay in lock-step."""
+        self.rank, self.world_size = int(rank), int(world_size)
+
+    @property
+    def n_batches_total(self) -> int:
+        return math.ceil(self.pos.size(1) / self.batch_size)
 
     def __len__(self) -> int:
-        return math.ceil(self.pos.size(1) / self.batch_size)
+        return math.ceil(self.n_batches_total / self.world_size)
 
     def __iter__(self) -> Iterator[SampledBatch]:
         g = self.data.device_graph()
@@ -94,22 +115,29 @@ class LinkLoader:
         order = _epoch_permutation(self.pos.size(1), self.shuffle).to(dev)
         cats = self.data.cats_device()
         n_nodes = self.data.num_nodes
-        for b in range(len(self)):
-            idx = order[b * self.batch_size:(b + 1) * self.batch_size]
-            pos = self._pos_dev[:, idx]
-            num_pos = pos.size(1)
-            num_neg = math.ceil(num_pos * self.ratio)
+        n_total = self.n_batches_total
+        n_round = len(self) * self.world_size
+        for q in range(n_round):
+            b = q % n_total
+            n_pos_b = min(self.batch_size, self.pos.size(1) - b * self.batch_size)
+            num_neg = math.ceil(n_pos_b * self.ratio)
             # same two draws, same order, as PyG's binary negative sampling
             src_neg = torch.randint(n_nodes, (num_neg,))
             dst_neg = torch.randint(n_nodes, (num_neg,))
+            batch_id = self._batch_counter
+            self._batch_counter += 1
+            if q % self.world_size != self.rank:
+                continue
+            idx = order[b * self.batch_size:(b + 1) * self.batch_size]
+            pos = self._pos_dev[:, idx]
+            num_pos = pos.size(1)
             neg = torch.stack((src_neg, dst_neg)).to(torch.int32)
             if dev.type == "cuda":
                 neg = neg.pin_memory().to(dev, non_blocking=True)
             ids = torch.cat((pos[0], neg[0], pos[1], neg[1])).contiguous()
             seeds, inv, n_seed = unique_sorted(ids)
             n_id, graph = sample_subgraph(g, seeds.contiguous(), n_seed, self.num_neighbors, self.rng_seed,
-                                          self._batch_counter)
-            self._batch_counter += 1
+                                          batch_id)
             batch = SampledBatch(self.data.store, n_id, graph, n_seed, cats)
             batch.edge_label_index = inv.view(2, -1)
             batch.edge_label = torch.cat((torch.ones(num_pos, device=dev), torch.zeros(num_neg, device=dev)))

@@ -115,13 +115,15 @@ def prepare_data(adata,
                  edge_test_ratio: float = 0.,
                  node_val_ratio: float = 0.1,
                  node_test_ratio: float = 0.,
-                 device=None) -> dict:
+                 device=None,
+                 store_location: str = "device") -> dict:
     """Dictionary with ``edge_train_data``, ``edge_val_data``, ``edge_test_data`` and
     ``node_masked_data`` exactly as the reference's ``prepare_data``; all splits share one HBM
     count store."""
     dataset = SpatialAnnTorchDataset(adata=adata, adata_atac=adata_atac, counts_key=counts_key, adj_key=adj_key,
                                      cat_covariates_keys=cat_covariates_keys,
-                                     cat_covariates_label_encoders=cat_covariates_label_encoders, device=device)
+                                     cat_covariates_label_encoders=cat_covariates_label_encoders, device=device,
+                                     store_location=store_location)
     data = GraphData(dataset, dataset.edge_index)
     train, val, test = edge_level_split(data, dataset.edge_label_adj, val_ratio=edge_val_ratio,
                                         test_ratio=edge_test_ratio)

@@ -44,7 +44,8 @@ class SpatialAnnTorchDataset:
                  edge_label_adj_key: str = "edge_label_spatial_connectivities",
                  self_loops: bool = True,
                  cat_covariates_keys: Optional[List[str]] = None,
-                 device: Optional[torch.device] = None):
+                 device: Optional[torch.device] = None,
+                 store_location: str = "device"):
         device = torch.device(device) if device is not None else torch.device(
             "cuda" if torch.cuda.is_available() else "cpu")
         x = adata.X if counts_key is None else adata.layers[counts_key]
@@ -52,6 +53,7 @@ class SpatialAnnTorchDataset:
         self.n_obs = x.shape[0]
         self.n_node_features = x.shape[1] + (self._x_atac.shape[1] if self._x_atac is not None else 0)
         self.device = device
+        self.store_location = store_location
         self._store = None
         adj = adata.obsp[adj_key]
         adj = adj if sp.issparse(adj) else sp.csr_matrix(adj)
@@ -73,7 +75,7 @@ class SpatialAnnTorchDataset:
     @property
     def store(self) -> CSRFeatureStore:
         if self._store is None:
-            self._store = CSRFeatureStore.from_scipy(self._x_rna, self.device, self._x_atac)
+            self._store = CSRFeatureStore.from_scipy(self._x_rna, self.device, self._x_atac, self.store_location)
         return self._store
 
     @property

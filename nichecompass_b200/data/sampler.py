@@ -76,6 +76,14 @@ class SampledBatch:
     def to(self, device):
         return self
 
+    def tensors(self):
+        """Every device tensor of the batch (stream bookkeeping of the prefetcher)."""
+        out = [self.n_id, self.graph.rowptr, self.graph.col]
+        for t in (self.cat_covariates_cats, self.edge_label_index, self.edge_label, self.input_id):
+            if t is not None and t.is_cuda:
+                out.append(t)
+        return out
+
 
 def unique_sorted(ids: torch.Tensor):
     """(unique sorted ids, inverse, n_unique) of an int32 device vector -- one kernel, one sync."""

@@ -20,6 +20,13 @@ class CSRFeatureStore:
         self.rowptr, self.col, self.val, self.n_cols = rowptr, col, val, int(n_cols)
 
     @property
+    def location(self) -> str:
+        """"device": non-zeros in HBM.  "host": non-zeros in pinned host memory, read by the
+        gather / SpMM kernels straight over the host link (zero-copy) -- for count matrices larger
+        than HBM and for the end-to-end leg of bench.py (every step pulls its inputs from the host)."""
+        return "device" if self.val.is_cuda else "host"
+
+    @property
     def n_rows(self) -> int:
         return self.rowptr.numel() - 1
 
@@ -29,23 +36,28 @@ class CSRFeatureStore:
 
     @property
     def device(self):
-        return self.val.device
+        return self.rowptr.device
 
     @classmethod
-    def from_scipy(cls, x, device, x2=None) -> "CSRFeatureStore":
+    def from_scipy(cls, x, device, x2=None, location: str = "device") -> "CSRFeatureStore":
         """``x`` (and optionally ``x2`` appended column-wise, the RNA ++ ATAC layout of
         data/datasets.py:65-71): scipy sparse or ndarray."""
+        if location not in ("device", "host"):
+            raise ValueError(f"unknown store location {location}")
         x = sp.csr_matrix(x)
         if x2 is not None:
             x = sp.hstack([x, sp.csr_matrix(x2)], format="csr")
         x.sort_indices()
         pin = torch.cuda.is_available()
-        def up(a, dt):
+
+        def up(a, dt, keep_on_host=False):
             t = torch.from_numpy(np.ascontiguousarray(a.astype(dt, copy=False)))
             if pin:
                 t = t.pin_memory()
-            return t.to(device, non_blocking=True)
-        return cls(up(x.indptr, np.int64), up(x.indices, np.int32), up(x.data, np.float32), x.shape[1])
+            return t if keep_on_host else t.to(device, non_blocking=True)
+        host = location == "host"
+        return cls(up(x.indptr, np.int64), up(x.indices, np.int32, host), up(x.data, np.float32, host),
+                   x.shape[1])
 
     def to_dense(self, rows: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Debug / compatibility helper (torch index plumbing, not a hot path)."""
@@ -53,5 +65,5 @@ class CSRFeatureStore:
         counts = (self.rowptr[1:] - self.rowptr[:-1])
         r = torch.repeat_interleave(torch.arange(n, device=self.device), counts)
         d = torch.zeros(n, self.n_cols, dtype=torch.float32, device=self.device)
-        d[r, self.col.long()] = self.val
+        d[r, self.col.to(self.device).long()] = self.val.to(self.device)
         return d if rows is None else d[rows]

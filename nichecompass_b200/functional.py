@@ -54,10 +54,18 @@ class SubgraphCSR:
 
 # --------------------------------------------------------------------------- packed weights
 _PACK_CACHE = {}
+_PARAM_EPOCH = 0
+
+
+def bump_param_epoch():
+    """Called by code that updates parameters through raw pointers (the fused Adam kernel),
+    which autograd's version counters cannot see: invalidates every packed weight copy."""
+    global _PARAM_EPOCH
+    _PARAM_EPOCH += 1
 
 
 def _versions(ts: Sequence[Optional[torch.Tensor]]):
-    return tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
+    return (_PARAM_EPOCH,) + tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
 
 
 def pack_rows(key, params: Sequence[torch.Tensor], dtype: torch.dtype, n_cols: int) -> torch.Tensor:

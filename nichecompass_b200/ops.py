@@ -79,7 +79,7 @@ def spmm_csr_store(store, n_id, rowptr, col, w, wself, skip_self: bool, n_rows: 
 
 def csr_gather_rows(store, n_id, n_rows: int, log1p: bool, dtype: torch.dtype, ld: Optional[int] = None):
     ld = store.n_cols if ld is None else ld
-    out = torch.empty(n_rows, ld, dtype=dtype, device=store.val.device)
+    out = torch.empty(n_rows, ld, dtype=dtype, device=store.device)
     call("nc_csr_gather_rows", store.rowptr, store.col, store.val, store.n_cols, n_id, n_rows,
          int(log1p), out, dtype_code(dtype), ld)
     return out

@@ -1,0 +1,485 @@
+"""
+Trainer of the NicheCompass model (reference: train/trainer.py:28-706).
+
+Same constructor / ``train`` signature, hyper-parameter semantics, epoch schedule (all gene
+programs for ``n_epochs_all_gps`` epochs, optional warm-up without edge reconstruction /
+contrastive loss), joint iteration over the edge loader and the cycled node loader, per-epoch
+validation, early stopping with learning-rate reduction and best-state reload.
+
+What runs differently (and why it is result-preserving):
+  * batches are index sets sampled on the GPU from the HBM-resident graph + count store
+    (``nichecompass_b200.data``); the sampler of batch i+1 runs on a side stream while batch i
+    trains, so its one host read-back (the sub-graph size) does not stall the compute stream;
+  * Adam is one kernel over a flat parameter buffer (``FlatAdam``); in data-parallel runs
+    (``torch.distributed`` initialised, one process per GPU) rank r trains on batches
+    r, r + W, ... of the common permutation and the flat gradient buffer is all-reduced (mean)
+    once per step, as is the running |mu| statistic that drives gene-program pruning;
+  * losses are accumulated on the device and read back once per epoch instead of a blocking
+    ``.item()`` per iteration (train/trainer.py:404-411).
+"""
+import copy
+import math
+import time
+import warnings
+from collections import defaultdict
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from ..data import initialize_dataloaders, prepare_data
+from .basetrainermixin import BaseTrainerMixin
+from .metrics import eval_metrics
+from .optim import FlatAdam
+from .utils import EarlyStopping, _cycle_iterable, print_progress
+
+
+def _dist_info():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+class _Prefetcher:
+    """Runs a loader's sampling kernels on a side stream.  The loader's one host read-back per batch
+    (the sub-graph size written by ``nc_sample_subgraph``) then waits for the side stream only, while
+    the compute stream keeps executing the previous training step; the host therefore queues step
+    i + 1 while the device still runs step i.  Batches are drawn strictly on demand, so the host
+    random generators are consumed in the reference's order."""
+
+    def __init__(self, loader, stream: Optional[torch.cuda.Stream]):
+        self.loader, self.stream = loader, stream
+
+    def __len__(self):
+        return len(self.loader)
+
+    def __iter__(self):
+        if self.stream is None:
+            yield from self.loader
+            return
+        main = torch.cuda.current_stream()
+        self.stream.wait_stream(main)            # one-off: uploads made on the compute stream
+        it = iter(self.loader)
+        while True:
+            with torch.cuda.stream(self.stream):
+                batch = next(it, None)
+                if batch is None:
+                    return
+                ev = torch.cuda.Event()
+                ev.record(self.stream)
+            for t in batch.tensors():
+                t.record_stream(main)
+            main.wait_event(ev)
+            yield batch
+
+
+class Trainer(BaseTrainerMixin):
+    def __init__(self,
+                 adata,
+                 model: nn.Module,
+                 adata_atac=None,
+                 counts_key: Optional[str] = "counts",
+                 adj_key: str = "spatial_connectivities",
+                 cat_covariates_keys: Optional[List[str]] = None,
+                 gp_targets_mask_key: str = "nichecompass_gp_targets",
+                 gp_sources_mask_key: str = "nichecompass_gp_sources",
+                 edge_val_ratio: float = 0.1,
+                 node_val_ratio: float = 0.1,
+                 edge_batch_size: int = 512,
+                 node_batch_size: Optional[int] = None,
+                 n_sampled_neighbors: int = -1,
+                 use_early_stopping: bool = True,
+                 reload_best_model: bool = True,
+                 early_stopping_kwargs: Optional[dict] = None,
+                 use_cuda_if_available: bool = True,
+                 seed: int = 0,
+                 monitor: bool = True,
+                 verbose: bool = False,
+                 **kwargs):
+        self.adata = adata
+        self.adata_atac = adata_atac
+        self.model = model
+        self.counts_key = counts_key
+        self.adj_key = adj_key
+        self.cat_covariates_keys = cat_covariates_keys
+        self.n_cat_covariates = 0 if cat_covariates_keys is None else len(cat_covariates_keys)
+        self.gp_targets_mask_key = gp_targets_mask_key
+        self.gp_sources_mask_key = gp_sources_mask_key
+        self.edge_train_ratio_ = 1 - edge_val_ratio
+        self.edge_val_ratio_ = edge_val_ratio
+        self.node_train_ratio_ = 1 - node_val_ratio
+        self.node_val_ratio_ = node_val_ratio
+        self.edge_batch_size_ = edge_batch_size
+        self.node_batch_size_ = node_batch_size
+        self.n_sampled_neighbors_ = n_sampled_neighbors
+        self.use_early_stopping_ = use_early_stopping
+        self.reload_best_model_ = reload_best_model
+        self.early_stopping_kwargs_ = early_stopping_kwargs if early_stopping_kwargs else {}
+        if "early_stopping_metric" not in self.early_stopping_kwargs_:
+            self.early_stopping_kwargs_["early_stopping_metric"] = (
+                "val_global_loss" if (edge_val_ratio > 0 and node_val_ratio > 0) else "train_global_loss")
+        self.early_stopping = EarlyStopping(**self.early_stopping_kwargs_)
+        self.seed_ = seed
+        self.monitor_ = monitor
+        self.verbose_ = verbose
+        self.loaders_n_hops_ = kwargs.pop("loaders_n_hops", 1)
+        self.grad_clip_value_ = kwargs.pop("grad_clip_value", 0.)
+        # extensions of this build (not in the reference signature)
+        self.compute_dtype_ = kwargs.pop("compute_dtype", None)
+        self.store_location_ = kwargs.pop("store_location", "device")
+        self.prefetch_ = kwargs.pop("prefetch", True)
+        kwargs.pop("latent_dtype", None)          # forwarded by NicheCompass.train, unused here (as in the reference)
+        self.epoch = -1
+        self.training_time = 0
+        self.optimizer = None
+        self.best_epoch = None
+        self.best_model_state_dict = None
+        self.rank_, self.world_size_ = _dist_info()
+
+        print("\n--- INITIALIZING TRAINER ---")
+        np.random.seed(self.seed_)
+        if not (use_cuda_if_available and torch.cuda.is_available()):
+            raise RuntimeError("nichecompass_b200 has no CPU training path: a CUDA device is required")
+        torch.cuda.manual_seed(self.seed_)
+        torch.manual_seed(self.seed_)
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.model.to(self.device)
+        if self.compute_dtype_ is not None:
+            self.model.set_compute_dtype(self.compute_dtype_)
+
+        data_dict = prepare_data(
+            adata=adata,
+            cat_covariates_label_encoders=self.model.cat_covariates_label_encoders_,
+            adata_atac=adata_atac,
+            counts_key=self.counts_key,
+            adj_key=self.adj_key,
+            cat_covariates_keys=self.cat_covariates_keys,
+            edge_val_ratio=self.edge_val_ratio_,
+            edge_test_ratio=0.,
+            node_val_ratio=self.node_val_ratio_,
+            node_test_ratio=0.,
+            device=self.device,
+            store_location=self.store_location_)
+        self.node_masked_data = data_dict["node_masked_data"]
+        self.edge_train_data = data_dict["edge_train_data"]
+        self.edge_val_data = data_dict["edge_val_data"]
+        self.n_nodes_train = self.node_masked_data.train_mask.sum().item()
+        self.n_nodes_val = self.node_masked_data.val_mask.sum().item()
+        self.n_edges_train = self.edge_train_data.edge_label_index.size(1)
+        self.n_edges_val = self.edge_val_data.edge_label_index.size(1)
+        print(f"Number of training nodes: {self.n_nodes_train}")
+        print(f"Number of validation nodes: {self.n_nodes_val}")
+        print(f"Number of training edges: {self.n_edges_train}")
+        print(f"Number of validation edges: {self.n_edges_val}")
+
+        if self.node_batch_size_ is None:
+            self.node_batch_size_ = int(self.edge_batch_size_ / math.floor(
+                self.n_edges_train / self.n_nodes_train))
+        print(f"Edge batch size: {edge_batch_size}")
+        print(f"Node batch size: {node_batch_size}")
+
+        loader_dict = initialize_dataloaders(
+            node_masked_data=self.node_masked_data,
+            edge_train_data=self.edge_train_data,
+            edge_val_data=self.edge_val_data,
+            edge_batch_size=self.edge_batch_size_,
+            node_batch_size=self.node_batch_size_,
+            n_direct_neighbors=self.n_sampled_neighbors_,
+            n_hops=self.loaders_n_hops_,
+            edges_directed=False,
+            neg_edge_sampling_ratio=1.)
+        self.edge_train_loader = loader_dict["edge_train_loader"]
+        self.edge_val_loader = loader_dict.pop("edge_val_loader", None)
+        self.node_train_loader = loader_dict["node_train_loader"]
+        self.node_val_loader = loader_dict.pop("node_val_loader", None)
+        # data parallelism: the training loaders are strided over the ranks; validation is replicated
+        for ld in (self.edge_train_loader, self.node_train_loader):
+            ld.set_shard(self.rank_, self.world_size_)
+        self._side_streams = ([torch.cuda.Stream(), torch.cuda.Stream()] if self.prefetch_ else [None, None])
+
+    # ------------------------------------------------------------------ one iteration
+    def _loss_kwargs(self):
+        return dict(lambda_edge_recon=self.lambda_edge_recon_,
+                    lambda_gene_expr_recon=self.lambda_gene_expr_recon_,
+                    lambda_chrom_access_recon=self.lambda_chrom_access_recon_,
+                    lambda_cat_covariates_contrastive=self.lambda_cat_covariates_contrastive_,
+                    contrastive_logits_pos_ratio=self.contrastive_logits_pos_ratio_,
+                    contrastive_logits_neg_ratio=self.contrastive_logits_neg_ratio_,
+                    lambda_group_lasso=self.lambda_group_lasso_,
+                    lambda_l1_masked=self.lambda_l1_masked_,
+                    l1_targets_mask=self.l1_targets_mask,
+                    l1_sources_mask=self.l1_sources_mask,
+                    lambda_l1_addon=self.lambda_l1_addon_)
+
+    def train_iteration(self, edge_batch, node_batch) -> dict:
+        """train/trainer.py:368-421: two forwards, loss, zero_grad, backward, clip, Adam step.
+        Returns the loss dictionary (device scalars; nothing is read back here)."""
+        node_out = self.model(data_batch=node_batch.to(self.device), decoder="omics",
+                              use_only_active_gps=self.use_only_active_gps)
+        edge_out = self.model(data_batch=edge_batch.to(self.device), decoder="graph",
+                              use_only_active_gps=self.use_only_active_gps)
+        loss_dict = self.model.loss(
+            edge_model_output=edge_out, node_model_output=node_out, **self._loss_kwargs(),
+            edge_recon_active=self.edge_recon_active,
+            cat_covariates_contrastive_active=self.cat_covariates_contrastive_active)
+        self.optimizer.zero_grad()
+        loss_dict["optim_loss"].backward()
+        if self.world_size_ > 1:
+            self.optimizer.all_reduce_grads()
+            self._sync_running_stats()
+        self.optimizer.step(clip_value=self.grad_clip_value_)
+        return loss_dict
+
+    def _sync_running_stats(self):
+        """Ranks see different node batches: average the |mu| EMA so that every rank prunes the
+        same gene programs (modules/vgpgae.py:641-651 is per-process state in the reference)."""
+        import torch.distributed as dist
+        buf = self.model.running_mean_abs_mu
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM)
+        buf.div_(self.world_size_)
+
+    def _set_epoch_flags(self):
+        self.edge_recon_active = not (self.epoch < self.n_epochs_no_edge_recon_)
+        self.use_only_active_gps = not (self.epoch < self.n_epochs_all_gps_)
+        self.cat_covariates_contrastive_active = not (self.epoch < self.n_epochs_no_cat_covariates_contrastive_)
+
+    def _accumulate(self, acc: dict, prefix: str, loss_dict: dict):
+        keys = loss_dict.keys() if self.verbose_ else ("global_loss", "optim_loss")
+        for k in keys:
+            v = loss_dict[k].detach()
+            name = f"{prefix}_{k}"
+            acc[name] = v.clone() if name not in acc else acc[name].add_(v)
+
+    def joint_batches(self, edge_loader, node_loader):
+        """zip(edge loader, cycled node loader) with both samplers running one batch ahead."""
+        e = _Prefetcher(edge_loader, self._side_streams[0])
+        n = _Prefetcher(node_loader, self._side_streams[1])
+        return zip(e, _cycle_iterable(n))
+
+    # ------------------------------------------------------------------ training
+    def train(self,
+              n_epochs: int = 100,
+              n_epochs_all_gps: int = 25,
+              n_epochs_no_edge_recon: int = 0,
+              n_epochs_no_cat_covariates_contrastive: int = 5,
+              lr: float = 0.001,
+              weight_decay: float = 0.,
+              lambda_edge_recon: Optional[float] = 500000.,
+              lambda_cat_covariates_contrastive: Optional[float] = 0.,
+              contrastive_logits_pos_ratio: Optional[float] = 0.125,
+              contrastive_logits_neg_ratio: Optional[float] = 0.125,
+              lambda_gene_expr_recon: float = 100.,
+              lambda_chrom_access_recon: float = 10.,
+              lambda_group_lasso: float = 0.,
+              lambda_l1_masked: float = 0.,
+              l1_targets_mask: Optional[torch.Tensor] = None,
+              l1_sources_mask: Optional[torch.Tensor] = None,
+              lambda_l1_addon: float = 0.,
+              mlflow_experiment_id: Optional[str] = None,
+              max_iters_per_epoch: Optional[int] = None):
+        self.setup_training(n_epochs, n_epochs_all_gps, n_epochs_no_edge_recon,
+                            n_epochs_no_cat_covariates_contrastive, lr, weight_decay, lambda_edge_recon,
+                            lambda_cat_covariates_contrastive, contrastive_logits_pos_ratio,
+                            contrastive_logits_neg_ratio, lambda_gene_expr_recon, lambda_chrom_access_recon,
+                            lambda_group_lasso, lambda_l1_masked, l1_targets_mask, l1_sources_mask,
+                            lambda_l1_addon, mlflow_experiment_id)
+        print("\n--- MODEL TRAINING ---")
+        start_time = time.time()
+        for self.epoch in range(n_epochs):
+            self._set_epoch_flags()
+            self.iter_logs = defaultdict(list)
+            self.iter_logs["n_train_iter"] = 0
+            self.iter_logs["n_val_iter"] = 0
+            acc = {}
+            for edge_batch, node_batch in self.joint_batches(self.edge_train_loader, self.node_train_loader):
+                loss_dict = self.train_iteration(edge_batch, node_batch)
+                self._accumulate(acc, "train", loss_dict)
+                self.iter_logs["n_train_iter"] += 1
+                if max_iters_per_epoch is not None and self.iter_logs["n_train_iter"] >= max_iters_per_epoch:
+                    break
+
+            if self.edge_val_loader is not None and self.node_val_loader is not None:
+                self.eval_epoch(acc)
+            elif self.edge_val_loader is None and self.node_val_loader is not None:
+                warnings.warn("You have specified a node validation set but no edge validation set. "
+                              "Skipping validation...")
+            elif self.edge_val_loader is not None and self.node_val_loader is None:
+                warnings.warn("You have specified an edge validation set but no node validation set. "
+                              "Skipping validation...")
+
+            self._epoch_logs_from(acc)
+            if self.monitor_ and self.rank_ == 0:
+                print_progress(self.epoch, self.epoch_logs, self.n_epochs_)
+            if self.use_early_stopping_ and self.is_early_stopping():
+                break
+
+        self.training_time += (time.time() - start_time)
+        minutes, seconds = divmod(self.training_time, 60)
+        print(f"Model training finished after {int(minutes)} min {int(seconds)} sec.")
+        if self.best_model_state_dict is not None and self.reload_best_model_:
+            print(f"Using best model state, which was in epoch {self.best_epoch + 1}.")
+            self.model.load_state_dict(self.best_model_state_dict)
+        self.model.eval()
+        if self.edge_val_loader is not None:
+            self.eval_end()
+
+    def setup_training(self, n_epochs=100, n_epochs_all_gps=25, n_epochs_no_edge_recon=0,
+                       n_epochs_no_cat_covariates_contrastive=5, lr=0.001, weight_decay=0.,
+                       lambda_edge_recon=500000., lambda_cat_covariates_contrastive=0.,
+                       contrastive_logits_pos_ratio=0.125, contrastive_logits_neg_ratio=0.125,
+                       lambda_gene_expr_recon=100., lambda_chrom_access_recon=10., lambda_group_lasso=0.,
+                       lambda_l1_masked=0., l1_targets_mask=None, l1_sources_mask=None, lambda_l1_addon=0.,
+                       mlflow_experiment_id=None):
+        """Hyper-parameter bookkeeping + optimiser construction of ``train`` (train/trainer.py:310-342),
+        split out so that single iterations can be driven from outside (bench, tests)."""
+        self.n_epochs_ = n_epochs
+        self.n_epochs_all_gps_ = n_epochs_all_gps
+        self.n_epochs_no_edge_recon_ = n_epochs_no_edge_recon
+        self.n_epochs_no_cat_covariates_contrastive_ = n_epochs_no_cat_covariates_contrastive
+        self.lr_ = lr
+        self.weight_decay_ = weight_decay
+        self.lambda_edge_recon_ = lambda_edge_recon
+        self.lambda_gene_expr_recon_ = lambda_gene_expr_recon
+        self.lambda_chrom_access_recon_ = lambda_chrom_access_recon
+        self.lambda_cat_covariates_contrastive_ = lambda_cat_covariates_contrastive
+        self.contrastive_logits_pos_ratio_ = contrastive_logits_pos_ratio
+        self.contrastive_logits_neg_ratio_ = contrastive_logits_neg_ratio
+        self.lambda_group_lasso_ = lambda_group_lasso
+        self.lambda_l1_masked_ = lambda_l1_masked
+        self.l1_targets_mask = l1_targets_mask
+        self.l1_sources_mask = l1_sources_mask
+        self.lambda_l1_addon_ = lambda_l1_addon
+        self.mlflow_experiment_id = mlflow_experiment_id     # mlflow logging is not part of this build
+        self.epoch_logs = defaultdict(list)
+        self.model.train()
+        self.model.materialize_outputs = False              # training consumes the fused losses only
+        params = [p for p in self.model.parameters() if p.requires_grad]
+        self.optimizer = FlatAdam(params, lr=lr, weight_decay=weight_decay)
+        self.epoch = 0
+        self._set_epoch_flags()
+
+    def _epoch_logs_from(self, acc: dict):
+        """Mean of the per-iteration losses (train/trainer.py:437-445); one read-back per epoch."""
+        if not acc:
+            return
+        names = sorted(acc.keys())
+        vals = torch.stack([acc[k].float() for k in names])
+        if self.world_size_ > 1:
+            import torch.distributed as dist
+            cnt = torch.tensor([float(self.iter_logs["n_train_iter"])], device=vals.device)
+            is_train = torch.tensor([1.0 if k.startswith("train") else 0.0 for k in names], device=vals.device)
+            tr = vals * is_train
+            dist.all_reduce(tr, op=dist.ReduceOp.SUM)
+            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+            vals = torch.where(is_train.bool(), tr, vals)
+            n_train = float(cnt.item())
+        else:
+            n_train = float(self.iter_logs["n_train_iter"])
+        vals = vals.cpu().tolist()
+        for k, v in zip(names, vals):
+            n = n_train if k.startswith("train") else float(self.iter_logs["n_val_iter"])
+            self.epoch_logs[k].append(v / max(n, 1.0))
+
+    # ------------------------------------------------------------------ evaluation
+    def _collect_edge_outputs(self, store: dict, edge_out: dict):
+        store["probs"].append(torch.sigmoid(edge_out["edge_recon_logits"]).detach())
+        store["labels"].append(edge_out["edge_recon_labels"].detach())
+        if edge_out["edge_same_cat_covariates_cat"] is not None:
+            for i, s in enumerate(edge_out["edge_same_cat_covariates_cat"]):
+                store["same"][i].append(s.detach())
+        if edge_out["edge_incl"] is not None:
+            store["incl"].append(edge_out["edge_incl"].detach())
+
+    def _edge_store(self):
+        return {"probs": [], "labels": [], "same": [[] for _ in range(self.n_cat_covariates)], "incl": []}
+
+    @staticmethod
+    def _cat_np(ts):
+        return torch.cat(ts).cpu().numpy() if len(ts) > 0 else None
+
+    def _edge_metrics(self, store: dict, omics_pred_dict: Optional[dict] = None) -> dict:
+        incl = self._cat_np(store["incl"])
+        same = [self._cat_np(s) for s in store["same"]] if incl is not None else None
+        return eval_metrics(edge_recon_probs=self._cat_np(store["probs"]),
+                            edge_labels=self._cat_np(store["labels"]),
+                            edge_same_cat_covariates_cat=same, edge_incl=incl,
+                            omics_pred_dict=omics_pred_dict)
+
+    @torch.no_grad()
+    def eval_epoch(self, acc: Optional[dict] = None):
+        """Per-epoch validation (train/trainer.py:492-589)."""
+        acc = {} if acc is None else acc
+        self.model.eval()
+        store = self._edge_store()
+        for edge_batch, node_batch in self.joint_batches(self.edge_val_loader, self.node_val_loader):
+            node_out = self.model(data_batch=node_batch.to(self.device), decoder="omics",
+                                  use_only_active_gps=self.use_only_active_gps)
+            edge_out = self.model(data_batch=edge_batch.to(self.device), decoder="graph",
+                                  use_only_active_gps=self.use_only_active_gps)
+            loss_dict = self.model.loss(edge_model_output=edge_out, node_model_output=node_out,
+                                        **self._loss_kwargs(), edge_recon_active=True)
+            self._accumulate(acc, "val", loss_dict)
+            self.iter_logs["n_val_iter"] += 1
+            self._collect_edge_outputs(store, edge_out)
+        val_eval_dict = self._edge_metrics(store)
+        if self.verbose_:
+            for k in ("auroc_score", "auprc_score", "best_acc_score", "best_f1_score"):
+                self.epoch_logs[f"val_{k}"].append(val_eval_dict[k])
+        self.model.train()
+        return val_eval_dict
+
+    @torch.no_grad()
+    def eval_end(self):
+        """End-of-training validation metrics (train/trainer.py:591-683)."""
+        self.model.eval()
+        prev = self.model.materialize_outputs
+        self.model.materialize_outputs = True
+        store = self._edge_store()
+        for edge_batch in _Prefetcher(self.edge_val_loader, self._side_streams[0]):
+            edge_out = self.model(data_batch=edge_batch.to(self.device), decoder="graph", use_only_active_gps=True)
+            self._collect_edge_outputs(store, edge_out)
+        preds = defaultdict(list)
+        if self.node_val_loader is not None:
+            for node_batch in _Prefetcher(self.node_val_loader, self._side_streams[1]):
+                node_out = self.model(data_batch=node_batch.to(self.device), decoder="omics",
+                                      use_only_active_gps=True)
+                for mod in self.model.modalities_:
+                    for ent in ("target", "source"):
+                        preds[f"{ent}_{mod}_preds"].append(node_out[f"{ent}_{mod}_nb_means"].reshape(-1))
+                        preds[f"{ent}_{mod}"].append(node_out["node_labels"][f"{ent}_{mod}"].reshape(-1))
+        omics = {k: torch.cat(v).cpu().numpy() for k, v in preds.items()} if preds else None
+        self.model.materialize_outputs = prev
+        val_eval_dict = self._edge_metrics(store, omics)
+        self.val_eval_dict_ = val_eval_dict
+        if self.rank_ == 0:
+            print("\n--- MODEL EVALUATION ---")
+            print(f"val AUROC score: {val_eval_dict['auroc_score']:.4f}")
+            print(f"val AUPRC score: {val_eval_dict['auprc_score']:.4f}")
+            print(f"val best accuracy score: {val_eval_dict['best_acc_score']:.4f}")
+            print(f"val best F1 score: {val_eval_dict['best_f1_score']:.4f}")
+            if omics is not None:
+                for mod in self.model.modalities_:
+                    for ent in ("target", "source"):
+                        print(f"val {ent} {mod} MSE score: {val_eval_dict[f'{ent}_{mod}_mse_score']:.4f}")
+            for i in range(self.n_cat_covariates):
+                if f"cat_covariate{i}_mean_sim_diff" in val_eval_dict:
+                    print(f"Val cat covariate{i} mean sim diff: "
+                          f"{val_eval_dict[f'cat_covariate{i}_mean_sim_diff']:.4f}")
+        return val_eval_dict
+
+    def is_early_stopping(self) -> bool:
+        """train/trainer.py:685-706: snapshot the best state, reduce the learning rate on plateau,
+        answer whether to stop."""
+        metric = self.early_stopping.early_stopping_metric
+        current = self.epoch_logs[metric][-1]
+        if self.early_stopping.update_state(current):
+            self.best_model_state_dict = copy.deepcopy(self.model.state_dict())
+            self.best_epoch = self.epoch
+        continue_training, reduce_lr = self.early_stopping.step(current)
+        if reduce_lr:
+            for param_group in self.optimizer.param_groups:
+                param_group["lr"] *= self.early_stopping.lr_factor
+            print(f"New learning rate is {param_group['lr']}.\n")
+        return not continue_training
