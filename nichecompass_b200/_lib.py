@@ -116,13 +116,28 @@ def stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+_HOOK = None
+
+
+def set_call_hook(hook):
+    """``hook.before(name, args)`` / ``hook.after(name, args)`` around every C-ABI call (bench.py's
+    per-kernel CUDA-event timing); ``None`` removes it."""
+    global _HOOK
+    _HOOK = hook
+
+
 def call(name: str, *args):
     """Call ``name`` with torch tensors (-> device pointers), None (-> NULL) or scalars; the
     stream argument is appended automatically."""
     fn = getattr(_load(), name)
     conv = [ctypes.c_void_p(a.t.data_ptr()) if isinstance(a, HostPtr)
             else (ptr(a) if (a is None or torch.is_tensor(a)) else a) for a in args]
-    rc = fn(*conv, stream())
+    if _HOOK is not None:
+        _HOOK.before(name, args)
+        rc = fn(*conv, stream())
+        _HOOK.after(name, args)
+    else:
+        rc = fn(*conv, stream())
     if rc != 0:
         msg = _lib.nc_last_error().decode()
         if rc in (-1, -2):

@@ -122,3 +122,79 @@ def make_synthetic_adata(n_cells: int, n_genes: int, k: int, n_prior_gp: int, se
     tm, sm = random_gp_masks(rng, n_genes, n_prior_gp)
     add_gp_masks(adata, tm, sm)
     return adata
+
+
+def _poisson_counts_chunked(rng, n_cells, n_genes, cluster, prof, lib, device=None, chunk=16384):
+    """CSR counts with x[i, g] ~ Poisson(lib[i] * prof[cluster[i], g]) drawn chunk by chunk (on the
+    GPU when one is visible: 1M x 5k takes seconds), every cell guaranteed >= 1 count."""
+    import torch
+    dev = torch.device(device) if device is not None else torch.device(
+        "cuda" if torch.cuda.is_available() else "cpu")
+    g = torch.Generator(device=dev)
+    g.manual_seed(int(rng.integers(0, 2 ** 31 - 1)))
+    prof_t = torch.from_numpy(prof.astype(np.float32)).to(dev)
+    indptr = [np.zeros(1, dtype=np.int64)]
+    indices, data = [], []
+    base = 0
+    for lo in range(0, n_cells, chunk):
+        hi = min(lo + chunk, n_cells)
+        cl = torch.from_numpy(cluster[lo:hi]).to(dev)
+        lb = torch.from_numpy(lib[lo:hi].astype(np.float32)).to(dev)
+        rate = prof_t[cl] * lb[:, None]
+        x = torch.poisson(rate, generator=g)
+        empty = x.sum(1) == 0
+        if bool(empty.any()):
+            rows = empty.nonzero().flatten()
+            x[rows, (rows + lo) % n_genes] = 1.
+        nz = x.nonzero()
+        vals = x[nz[:, 0], nz[:, 1]]
+        counts = torch.bincount(nz[:, 0], minlength=hi - lo)
+        ptr = torch.cumsum(counts, 0).cpu().numpy().astype(np.int64) + base
+        base = int(ptr[-1])
+        indptr.append(ptr)
+        indices.append(nz[:, 1].to(torch.int32).cpu().numpy())
+        data.append(vals.cpu().numpy().astype(np.float32))
+    return sp.csr_matrix((np.concatenate(data), np.concatenate(indices), np.concatenate(indptr)),
+                         shape=(n_cells, n_genes))
+
+
+def make_synthetic_adata_large(n_cells: int, n_genes: int, k: int, n_prior_gp: int, seed: int = 0,
+                               n_samples: int = 1, lib_mean: float = 300., lib_sigma: float = 0.5,
+                               n_clusters: int = 8, counts_key: Optional[str] = "counts",
+                               adj_key: str = "spatial_connectivities", sample_key: str = "batch",
+                               device=None) -> AnnDataLite:
+    """Same construction as ``make_synthetic_adata`` at atlas scale (BASELINE.json configs 2-5):
+    Poisson counts around lib_i * profile[cluster_i] instead of explicit multinomial draws, obs
+    frame built without per-cell Python work."""
+    rng = np.random.default_rng(seed)
+    per = n_cells // n_samples
+    sizes = [per] * n_samples
+    sizes[-1] += n_cells - per * n_samples
+    coords, sample, blocks = [], [], []
+    for s, ns in enumerate(sizes):
+        c = rng.random((ns, 2))
+        coords.append(c + np.array([2.0 * s, 0.0]))
+        sample.append(np.full(ns, s))
+        blocks.append(knn_adjacency(c, k))
+    coords = np.concatenate(coords)
+    adj = (sp.block_diag(blocks, format="csr") if n_samples > 1 else blocks[0]).astype(np.float32)
+    adj.sort_indices()
+    local = coords - np.floor(coords / 2.0) * 2.0
+    cluster = ((np.minimum((local[:, 0] * 4).astype(int), 3)
+                + 4 * np.minimum((local[:, 1] * 2).astype(int), 1)) % n_clusters).astype(np.int64)
+    logits = rng.normal(0., 1.5, size=(n_clusters, n_genes))
+    prof = np.exp(logits - logits.max(1, keepdims=True))
+    prof /= prof.sum(1, keepdims=True)
+    lib = np.maximum(rng.lognormal(np.log(lib_mean), lib_sigma, n_cells), 1.0)
+    x = _poisson_counts_chunked(rng, n_cells, n_genes, cluster, prof, lib, device)
+    sample_ids = np.concatenate(sample)
+    obs = pd.DataFrame({sample_key: pd.Categorical.from_codes(sample_ids, [f"sample{s}" for s in range(n_samples)])},
+                       index=pd.RangeIndex(n_cells).astype(str))
+    adata = AnnDataLite(x, obs=obs)
+    if counts_key is not None:
+        adata.layers[counts_key] = x
+    adata.obsp[adj_key] = adj
+    adata.obsm["spatial"] = coords
+    tm, sm = random_gp_masks(rng, n_genes, n_prior_gp)
+    add_gp_masks(adata, tm, sm)
+    return adata

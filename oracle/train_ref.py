@@ -105,7 +105,7 @@ class TrainerRef:
             self.p[k].grad = None
         L["optim_loss"].backward()
         adam_step(self.p, self.keys, self.state, self.lr, self.weight_decay, clip_value=self.clip)
-        return {k: float(v) for k, v in L.items()}
+        return {k: float(v.detach()) for k, v in L.items()}
 
     def run(self, max_iters: Optional[int] = None) -> List[dict]:
         """One epoch (or ``max_iters`` iterations) of zip(edge loader, cycled node loader)."""

@@ -1,0 +1,134 @@
+"""
+GPU parity of the training loop and of the public model API: ``Trainer`` (CUDA) against
+``oracle.train_ref.TrainerRef`` (CPU restatement of train/trainer.py:339-454) on identical seeds,
+batches and injected reparameterisation noise; ``NicheCompass.train`` / ``get_latent_representation``
+/ ``save`` / ``load`` end to end.
+"""
+import contextlib
+import copy
+import io
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import train_ref as TR
+from oracle.vgpgae_ref import VGPGAERef, init_params
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+LAM = dict(lambda_l1_masked=0., lambda_l1_addon=30., lambda_group_lasso=1.5, lambda_gene_expr_recon=300.,
+           lambda_edge_recon=500000.)
+
+
+def _module(cfg, p32, conv="gatv2conv"):
+    from nichecompass_b200.modules import VGPGAE
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+                   n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"], n_addon_gp=cfg["n_addon_gp"],
+                   cat_covariates_embeds_nums=[], n_output_genes=cfg["n_output_genes"],
+                   target_rna_decoder_mask=cfg["target_rna_mask"], source_rna_decoder_mask=cfg["source_rna_mask"],
+                   features_idx_dict=copy.deepcopy(cfg["features_idx_dict"]),
+                   features_scale_factors=torch.ones(2 * cfg["n_output_genes"]),
+                   conv_layer_encoder=conv, encoder_n_attention_heads=cfg["heads"],
+                   node_label_method="one-hop-norm", active_gp_thresh_ratio=0.01,
+                   include_cat_covariates_contrastive_loss=False)
+    m.load_state_dict({k: v.float() for k, v in p32.items()}, strict=True)
+    return m
+
+
+def _cpu_run(adata, cfg, p32, n_iters, edge_bs, **kw):
+    torch.manual_seed(0)
+    p64 = {k: v.double().clone() for k, v in p32.items()}
+    ld = TR.build_loaders(H.dense_x(adata, torch.float64), adata.obsp["spatial_connectivities"], edge_bs)
+    ref = TR.TrainerRef(cfg, p64, ld.edge_loader, ld.node_loader, lr=1e-3, loss_kwargs=LAM, **kw)
+    return ref, ref.run(max_iters=n_iters), p64
+
+
+def _gpu_run(adata, cfg, p32, eps, n_iters, edge_bs, conv="gatv2conv", dtype=torch.float32, **tkw):
+    from nichecompass_b200.train import Trainer
+    with contextlib.redirect_stdout(io.StringIO()):
+        tr = Trainer(adata, _module(cfg, p32, conv), edge_batch_size=edge_bs, seed=0, monitor=False,
+                     compute_dtype=dtype, **tkw)
+        tr.setup_training(lr=1e-3, **LAM)
+    tr.model._eps_queue = [e.clone() for e in eps]
+    logs = []
+    for i, (eb, nb) in enumerate(tr.joint_batches(tr.edge_train_loader, tr.node_train_loader)):
+        L = tr.train_iteration(eb, nb)
+        logs.append({k: float(v) for k, v in L.items()})
+        if i + 1 == n_iters:
+            break
+    return tr, logs
+
+
+@pytest.mark.parametrize("conv", ["gatv2conv", "gcnconv"])
+def test_training_iterations_match_cpu_loop(conv):
+    adata = H.tiny_problem(n_cells=220, n_genes=44, n_prior_gp=12)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=4, conv_layer=conv)
+    p32 = init_params(cfg, seed=3)
+    ref, ref_logs, p64 = _cpu_run(adata, cfg, p32, 4, 24)
+    tr, logs = _gpu_run(adata, cfg, p32, ref.noise_log, 4, 24, conv)
+    assert tr.node_batch_size_ == ref.node_loader.batch_size
+    for it, (a, b) in enumerate(zip(logs, ref_logs)):
+        for k in b:
+            assert abs(a[k] - b[k]) <= 2e-5 * abs(b[k]) * (1 + it) + 1e-12, (it, k, a[k], b[k])
+    # parameters after 4 Adam steps (Adam normalises gradients: allow lr-sized slack on near-zero gradients)
+    sd = tr.model.state_dict()
+    close, total = 0, 0
+    for k in TR.trainable_keys(p64):
+        d = (sd[k].double().cpu() - p64[k].detach()).abs()
+        close += int((d <= 1e-5 + 1e-4 * p64[k].detach().abs()).sum())
+        total += d.numel()
+    assert close / total > 0.995, close / total
+    assert H.rel_err(tr.model.running_mean_abs_mu, ref.model.running_mean_abs_mu) < 1e-4
+
+
+def test_host_resident_store_gives_identical_losses():
+    adata = H.tiny_problem(n_cells=220, n_genes=44, n_prior_gp=12)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=4)
+    p32 = init_params(cfg, seed=3)
+    ref, _, _ = _cpu_run(adata, cfg, p32, 2, 24)
+    _, dev_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24)
+    _, host_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24, store_location="host")
+    assert dev_logs == host_logs
+
+
+def test_nichecompass_train_latent_save_load(tmp_path):
+    from nichecompass_b200.models import NicheCompass
+    adata = H.tiny_problem(n_cells=300, n_genes=48, n_prior_gp=12, lib_mean=80.)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = NicheCompass(adata, n_addon_gp=4, active_gp_thresh_ratio=0.01)
+        model.train(n_epochs=3, n_epochs_all_gps=1, edge_batch_size=64, lambda_group_lasso=1.0, verbose=True)
+    tr = model.trainer
+    assert len(tr.epoch_logs["train_global_loss"]) == 3 and len(tr.epoch_logs["val_global_loss"]) == 3
+    assert tr.epoch_logs["train_global_loss"][-1] < tr.epoch_logs["train_global_loss"][0]
+    assert 0.0 <= tr.val_eval_dict_["auroc_score"] <= 1.0
+    lat = adata.obsm["nichecompass_latent"]
+    n_active = len(adata.uns["nichecompass_active_gp_names"])
+    assert lat.shape == (300, n_active) and lat.dtype == np.float64 and np.isfinite(lat).all()
+
+    # latent inference: tiles of 8192 (product) == reference-sized batches evaluated by the CPU oracle
+    sd = {k: v.detach().double().cpu() for k, v in model.model.state_dict().items()}
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=4)
+    orc = VGPGAERef(cfg, sd)
+    orc.training = False
+    x = H.dense_x(adata, torch.float64)
+    ei = TR.R.adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
+    loader = TR.R.NodeLoaderRef(x, ei, 300, torch.ones(300, dtype=torch.bool), 64, shuffle=False)
+    mu_ref = torch.cat([orc.get_latent_representation(b, only_active_gps=True, return_mu_std=True)[0] for b in loader])
+    assert H.rel_err(torch.from_numpy(lat), mu_ref) < 2e-5
+
+    # save / load round trip with the reference's file layout; frozen weights after load
+    d = os.path.join(tmp_path, "model")
+    model.save(d, overwrite=True)
+    assert sorted(os.listdir(d)) == ["attr.pkl", "model_params.pt", "var_names.csv"]
+    with contextlib.redirect_stdout(io.StringIO()):
+        loaded = NicheCompass.load(d, adata=adata, use_cuda=True, unfreeze_addon_gp_weights=True)
+    assert loaded.is_trained_
+    for k, v in model.model.state_dict().items():
+        assert torch.equal(v.cpu(), loaded.model.state_dict()[k].cpu()), k
+    flags = {n: p.requires_grad for n, p in loaded.model.named_parameters()}
+    assert all(v == ("addon" in n or "theta" in n or "aggregator" in n) for n, v in flags.items())
+    lat2 = loaded.get_latent_representation(adata, only_active_gps=True, node_batch_size=64)
+    assert np.allclose(lat2, lat, rtol=1e-6, atol=1e-7)
