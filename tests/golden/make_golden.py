@@ -1,0 +1,140 @@
+"""
+Generates the golden vectors under tests/golden/ from the UNMODIFIED reference sources.
+
+Run in the builder container only (needs /root/reference):
+
+    python tests/golden/make_golden.py
+
+For every case it instantiates the reference ``nichecompass.modules.VGPGAE`` (loaded from
+/root/reference/src/nichecompass; the missing third-party imports torch_geometric / torch_sparse /
+mlflow are served by the pure-torch stand-ins in oracle/pyg_shim), runs one node batch through the
+omics decoders and one edge batch through the graph decoder in fp64 with injected
+reparameterisation noise, evaluates ``loss`` + ``backward``, the active gene-program mask and the
+latent representation, and writes inputs (weights, batches, noise) and outputs to
+``tests/golden/<case>.npz``.  tests/test_golden.py replays the inputs through the CPU oracle
+(not gpu) and through the CUDA module (gpu) -- neither needs /root/reference at test time.
+"""
+import copy
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+
+from oracle import sampler_ref as R                      # noqa: E402
+from tests import helpers as H                           # noqa: E402
+from tests.ref_harness import load_reference, quiet      # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+LAM = dict(lambda_l1_masked=3., lambda_l1_addon=30., lambda_group_lasso=2., lambda_gene_expr_recon=300.,
+           lambda_edge_recon=500000.)
+CASES = {
+    # name: (conv_layer, node_label_method, n_addon_gp, n_genes, use_only_active_gps)
+    "gatv2_norm_addon3": ("gatv2conv", "one-hop-norm", 3, 40, False),
+    "gcn_sum_addon3": ("gcnconv", "one-hop-sum", 3, 40, False),
+    "gatv2_attention_addon0": ("gatv2conv", "one-hop-attention", 0, 40, False),
+    "gatv2_norm_active_gps": ("gatv2conv", "one-hop-norm", 3, 41, True),
+}
+
+
+def batch_arrays(prefix, b, out):
+    out[f"{prefix}/x"] = b.x.numpy()
+    out[f"{prefix}/edge_index"] = b.edge_index.numpy()
+    if hasattr(b, "edge_label_index"):
+        out[f"{prefix}/edge_label_index"] = b.edge_label_index.numpy()
+        out[f"{prefix}/edge_label"] = b.edge_label.numpy()
+    else:
+        out[f"{prefix}/batch_size"] = np.int64(b.batch_size)
+
+
+def make_case(name, conv_layer, node_label_method, n_addon, n_genes, only_active):
+    ref = load_reference()
+    import torch_sparse
+    torch_sparse.DEFAULT_DTYPE = torch.float64
+    adata = H.tiny_problem(n_cells=120, n_genes=n_genes, n_prior_gp=10, seed=len(name))
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=n_addon, conv_layer=conv_layer,
+                                  node_label_method=node_label_method)
+    torch.manual_seed(1)
+    with quiet():
+        m = ref.modules.VGPGAE(
+            n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+            n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"], n_addon_gp=n_addon,
+            cat_covariates_embeds_nums=[], n_output_genes=cfg["n_output_genes"],
+            target_rna_decoder_mask=cfg["target_rna_mask"], source_rna_decoder_mask=cfg["source_rna_mask"],
+            features_idx_dict=copy.deepcopy(cfg["features_idx_dict"]),
+            features_scale_factors=torch.ones(2 * cfg["n_output_genes"]),
+            conv_layer_encoder=conv_layer, encoder_n_attention_heads=cfg["heads"],
+            node_label_method=node_label_method, active_gp_thresh_ratio=0.01,
+            include_cat_covariates_contrastive_loss=False).double()
+    m.train()
+    with torch.no_grad():
+        for k, p in m.named_parameters():
+            if k.endswith("bias"):
+                p.uniform_(-0.1, 0.1)           # PyG zero-initialises biases: make them count
+        if only_active:
+            m.running_mean_abs_mu.copy_(torch.rand(cfg["n_prior_gp"] + n_addon, dtype=torch.float64) ** 6)
+    out = {}
+    for k, v in m.state_dict().items():
+        out[f"state/{k}"] = v.detach().numpy().copy()
+    out["cfg/target_rna_mask"] = cfg["target_rna_mask"].numpy()
+    out["cfg/source_rna_mask"] = cfg["source_rna_mask"].numpy()
+    for k, v in cfg["features_idx_dict"].items():
+        out[f"cfg/features_idx/{k}"] = np.asarray(v, dtype=np.int64)
+    out["cfg/meta"] = np.array([conv_layer, node_label_method, str(n_addon), str(cfg["n_hidden"]),
+                                str(cfg["heads"]), str(int(only_active))])
+
+    torch.manual_seed(0)
+    x = H.dense_x(adata, torch.float64)
+    n = adata.n_obs
+    ei = R.adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
+    splits = R.edge_level_split(ei, n, 0.1)
+    train_mask, _ = R.node_level_split_mask(n, 0.1)
+    node_b = next(iter(R.NodeLoaderRef(x, ei, n, train_mask, 8)))
+    edge_b = next(iter(R.LinkLoaderRef(x, splits["train"].edge_index, n, splits["train"].edge_label_index, 16)))
+    batch_arrays("node_batch", node_b, out)
+    batch_arrays("edge_batch", edge_b, out)
+    P = cfg["n_prior_gp"] + n_addon
+    g = torch.Generator().manual_seed(5)
+    eps_n = torch.randn(node_b.batch_size, P, generator=g, dtype=torch.float64)
+    eps_e = torch.randn(2 * edge_b.edge_label_index.size(1), P, generator=g, dtype=torch.float64)
+    out["eps/node"], out["eps/edge"] = eps_n.numpy(), eps_e.numpy()
+
+    draws = [eps_n, eps_e]
+    real = torch.randn_like
+    torch.randn_like = lambda t, *a, **k: draws.pop(0)
+    try:
+        rn = m(data_batch=node_b, decoder="omics", use_only_active_gps=only_active)
+        re_ = m(data_batch=edge_b, decoder="graph", use_only_active_gps=only_active)
+    finally:
+        torch.randn_like = real
+    rl = m.loss(edge_model_output=re_, node_model_output=rn, l1_targets_mask=None, l1_sources_mask=None, **LAM)
+    rl["optim_loss"].backward()
+    for k in ("mu", "logstd", "target_rna_nb_means", "source_rna_nb_means"):
+        out[f"node_out/{k}"] = rn[k].detach().numpy()
+    for k in ("target_rna", "source_rna"):
+        out[f"node_out/node_labels/{k}"] = rn["node_labels"][k].detach().numpy()
+    for k in ("mu", "logstd", "edge_recon_logits"):
+        out[f"edge_out/{k}"] = re_[k].detach().numpy()
+    for k, v in rl.items():
+        out[f"loss/{k}"] = np.float64(float(v))
+    for k, p in m.named_parameters():
+        if p.grad is not None:
+            out[f"grad/{k}"] = p.grad.numpy().copy()
+    out["after/running_mean_abs_mu"] = m.running_mean_abs_mu.numpy().copy()
+    m.eval()
+    out["after/active_gp_mask"] = m.get_active_gp_mask().numpy()
+    with torch.no_grad():
+        mu, std = m.get_latent_representation(node_b, only_active_gps=True, return_mu_std=True)
+    out["latent/mu"], out["latent/std"] = mu.numpy(), std.numpy()
+    path = os.path.join(OUT, f"{name}.npz")
+    np.savez_compressed(path, **out)
+    print(f"{name}: {len(out)} arrays, {os.path.getsize(path) / 1024:.0f} KiB, "
+          f"global_loss {float(rl['global_loss']):.10g}")
+
+
+if __name__ == "__main__":
+    for name, args in CASES.items():
+        make_case(name, *args)

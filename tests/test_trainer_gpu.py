@@ -94,7 +94,12 @@ def test_host_resident_store_gives_identical_losses():
     ref, _, _ = _cpu_run(adata, cfg, p32, 2, 24)
     _, dev_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24)
     _, host_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24, store_location="host")
-    assert dev_logs == host_logs
+    # same kernels, same inputs: the first iteration is bit-identical; later ones may differ in the last
+    # ulp because a few gradients (att / bias / scatter-add) are accumulated with float atomics
+    assert dev_logs[0] == host_logs[0]
+    for a, b in zip(dev_logs, host_logs):
+        for k in a:
+            assert abs(a[k] - b[k]) <= 1e-6 * abs(b[k]), (k, a[k], b[k])
 
 
 def test_nichecompass_train_latent_save_load(tmp_path):
