@@ -26,6 +26,14 @@ shapes = [  # name, M, N, K, ta, tb, out dtype
     ("lin_l dX", 8704, 1600, 12800, False, True, torch.bfloat16),
     ("lin_l dW", 12800, 1600, 8704, True, True, torch.float32),
     ("fc_l1 dW", 1600, 5000, 8704, True, True, torch.float32),
+    ("lin_r fwd", 1024, 12800, 1600, False, False, torch.bfloat16),
+    ("lin_r dX", 1024, 1600, 12800, False, True, torch.float32),
+    ("lin_r dW", 12800, 1600, 1024, True, True, torch.float32),
+    ("fc_l1 fwd nb", 656, 1600, 5000, False, False, torch.bfloat16),
+    ("lin_l fwd nb", 656, 12800, 1600, False, False, torch.bfloat16),
+    ("lin_l dW nb", 12800, 1600, 656, True, True, torch.float32),
+    ("decoder fwd", 64, 5000, 1600, False, False, torch.float32),
+    ("decoder dW", 5000, 1600, 64, True, True, torch.float32),
     ("square 8k", 8192, 8192, 8192, False, False, torch.bfloat16),
 ]
 for name, M, N, K, ta, tb, od in shapes:
