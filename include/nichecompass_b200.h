@@ -214,14 +214,16 @@ int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t P, float l
 
 /* Fused Adam over a flat parameter segment with torch.optim.Adam semantics
  * (train/trainer.py:339-342,418-421): optional clip_grad_value_ (clip_value > 0), optional
- * refresh of the bf16 shadow copy used by the tensor-core GEMMs.                            */
-int nc_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+ * refresh of the bf16 shadow copy used by the tensor-core GEMMs; zero_grad != 0 clears g after
+ * it has been consumed (optimizer.zero_grad() of the next iteration, train/trainer.py:414).   */
+int nc_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
                  float beta2, float eps, float weight_decay, int32_t step, float clip_value,
-                 void* p_bf16, void* stream);
-/* fp32 [R, C] (lds) -> bf16 [R, ldd] (columns >= C zeroed), optionally multiplied by `mask`
- * (nn/layercomponents.py:77-80: weight * mask before the contraction).                      */
+                 void* p_bf16, int zero_grad, void* stream);
+/* fp32 [R, C] (lds) -> bf16 dst [R, fill_cols] (row pitch ldd; columns [C, fill_cols) zeroed;
+ * fill_cols <= 0 means ldd), optionally multiplied by `mask` (nn/layercomponents.py:77-80:
+ * weight * mask before the contraction).                                                    */
 int nc_cast_bf16(const float* src, int64_t lds, const float* mask, int64_t ldmask, int32_t R,
-                 int32_t C, void* dst, int64_t ldd, void* stream);
+                 int32_t C, void* dst, int64_t ldd, int32_t fill_cols, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * GPU CSR neighbourhood sampler (PyG NeighborLoader / LinkNeighborLoader + pyg-lib

@@ -1,8 +1,13 @@
 // bf16 GEMM on the 5th-gen tensor cores: TMA (cp.async.bulk.tensor) -> 128B-swizzled smem ring
 // -> tcgen05.mma (accumulators in TMEM, double buffered) -> tcgen05.ld epilogue with fused
-// bias / ReLU / gene-program mask / accumulate.  Persistent, one CTA per SM, warp-specialised:
+// bias / ReLU / gene-program mask -> 128B-swizzled smem staging -> TMA tensor store
+// (cp.async.bulk.tensor) or, for accumulate / split-K, TMA tensor reduce-add
+// (cp.reduce.async.bulk.tensor .add), so every global write is a full coalesced line and the
+// bounds are clipped by the tensor map.  Persistent, one CTA per SM, warp-specialised:
 //   warp 0 : TMA producer          warp 1 : TMEM allocator + MMA issuer (one elected lane)
-//   warps 2-5 : epilogue (TMEM lane quarter = warp_id % 4)
+//   warps 2-5 : epilogue (TMEM lane quarter = warp_id % 4), two 4 KB staging buffers each
+// Work item = (output tile, K split); small-tile-count / deep-K problems are split along K and
+// reduced in L2 by the TMA reduce-add.
 //   C[M,N] (+)= act(opA(A) * opB(B) + bias) (* mask)
 // A: [M,K] (K-major) or, trans_a, [K,M] (MN-major).  B: [N,K] (K-major) or, trans_b, [K,N].
 // Replaces the cuBLAS call sites nn/encoders.py:179 (fc_l1), PyG GATv2Conv lin_l/lin_r,
@@ -26,18 +31,20 @@ template <int BN> struct Cfg {
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     static constexpr int STAGES = (BN == 256) ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN;       // two accumulator stages (power of two)
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr int STAGING_BYTES = 4 /*warps*/ * 2 /*buffers*/ * 4096;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
 struct Epilogue {
-    void* C;
-    int64_t ldc;
     const float* bias;
     const float* mask;
     int64_t ldmask;
     int c_bf16;
     int relu;
-    int accumulate;
+    int reduce;        // TMA reduce-add instead of store (accumulate into C, or split-K partials)
+    int bias_vec;      // bias is 16-byte aligned
+    int mask_vec;      // mask rows are 16-byte aligned
+    int splits;        // K splits per output tile
 };
 
 // ------------------------------------------------------------------------- PTX wrappers
@@ -72,6 +79,21 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tm, ui
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(dst)), "l"((uint64_t)tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"((uint64_t)tm), "r"(smem_u32(src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, const void* src, int c0, int c1) {
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"((uint64_t)tm), "r"(smem_u32(src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void st_shared_v4(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -123,63 +145,51 @@ __host__ __device__ constexpr uint32_t make_idesc(int M, int N, bool a_mn, bool 
 }
 
 // ------------------------------------------------------------------------- epilogue helpers
-__device__ __forceinline__ void epi_store_chunk(const Epilogue& e, const uint32_t (&r)[32], int row, int col0,
-                                                int M, int N) {
-    if (row >= M) return;
-    const float* mrow = e.mask ? e.mask + (int64_t)row * e.ldmask : nullptr;
-    if (e.c_bf16) {
-        __nv_bfloat16* crow = (__nv_bfloat16*)e.C + (int64_t)row * e.ldc;
+// bias / ReLU / mask on the four accumulator values of columns [col, col+4) of one row.
+__device__ __forceinline__ void epi_apply4(const Epilogue& e, float (&v)[4], const float* mrow, int col, int N,
+                                           bool add_bias) {
+    if (e.bias && add_bias) {
+        if (e.bias_vec && col + 3 < N) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(e.bias + col));
+            v[0] += b.x; v[1] += b.y; v[2] += b.z; v[3] += b.w;
+        } else {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {          // 8 columns (16 B of bf16) per group
-            const int c = col0 + g * 8;
-            if (c >= N) break;
-            float v[8];
-#pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                v[t] = __uint_as_float(r[g * 8 + t]);
-                const int cc = c + t;
-                if (cc < N) {
-                    if (e.bias) v[t] += __ldg(e.bias + cc);
-                    if (e.relu) v[t] = fmaxf(v[t], 0.f);
-                    if (mrow) v[t] *= __ldg(mrow + cc);
-                    if (e.accumulate) v[t] += __bfloat162float(crow[cc]);
-                }
-            }
-            if (c + 7 < N) {
-                uint4 q;
-                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[0], v[1]), p1 = __floats2bfloat162_rn(v[2], v[3]);
-                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[4], v[5]), p3 = __floats2bfloat162_rn(v[6], v[7]);
-                q.x = *reinterpret_cast<uint32_t*>(&p0); q.y = *reinterpret_cast<uint32_t*>(&p1);
-                q.z = *reinterpret_cast<uint32_t*>(&p2); q.w = *reinterpret_cast<uint32_t*>(&p3);
-                *reinterpret_cast<uint4*>(crow + c) = q;
-            } else {
-                for (int t = 0; t < 8 && c + t < N; ++t) crow[c + t] = __float2bfloat16_rn(v[t]);
-            }
+            for (int t = 0; t < 4; ++t) if (col + t < N) v[t] += __ldg(e.bias + col + t);
         }
-    } else {
-        float* crow = (float*)e.C + (int64_t)row * e.ldc;
+    }
+    if (e.relu) {
 #pragma unroll
-        for (int g = 0; g < 8; ++g) {          // 4 columns (16 B of fp32) per group
-            const int c = col0 + g * 4;
-            if (c >= N) break;
-            float v[4];
+        for (int t = 0; t < 4; ++t) v[t] = fmaxf(v[t], 0.f);
+    }
+    if (mrow) {
+        if (e.mask_vec && col + 3 < N) {
+            const float4 m = __ldg(reinterpret_cast<const float4*>(mrow + col));
+            v[0] *= m.x; v[1] *= m.y; v[2] *= m.z; v[3] *= m.w;
+        } else {
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                v[t] = __uint_as_float(r[g * 4 + t]);
-                const int cc = c + t;
-                if (cc < N) {
-                    if (e.bias) v[t] += __ldg(e.bias + cc);
-                    if (e.relu) v[t] = fmaxf(v[t], 0.f);
-                    if (mrow) v[t] *= __ldg(mrow + cc);
-                    if (e.accumulate) v[t] += crow[cc];
-                }
-            }
-            if (c + 3 < N) {
-                *reinterpret_cast<float4*>(crow + c) = make_float4(v[0], v[1], v[2], v[3]);
-            } else {
-                for (int t = 0; t < 4 && c + t < N; ++t) crow[c + t] = v[t];
-            }
+            for (int t = 0; t < 4; ++t) if (col + t < N) v[t] *= __ldg(mrow + col + t);
         }
+    }
+}
+
+// One warp moves its 32 accumulator rows x (32 fp32 | 64 bf16) columns: registers -> 128B-swizzled
+// staging buffer (row = lane; 16-byte unit j of a row lives at unit j ^ (row & 7), the layout a
+// SWIZZLE_128B tensor map expects, and conflict-free for st.shared.v4) -> TMA store / reduce-add.
+__device__ __forceinline__ void epi_flush(const Epilogue& e, const CUtensorMap* tmC, uint8_t* buf, int lane,
+                                          const uint32_t (&packed)[32], int col0, int row0) {
+    if (lane == 0) bulk_wait_read_1();           // the store issued from this buffer two chunks ago has read it
+    __syncwarp();
+    uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        st_shared_v4(rowp + ((j ^ (lane & 7)) << 4), packed[4 * j], packed[4 * j + 1], packed[4 * j + 2],
+                     packed[4 * j + 3]);
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+        if (e.reduce) tma_reduce_add_2d(tmC, buf, col0, row0);
+        else tma_store_2d(tmC, buf, col0, row0);
+        bulk_commit();
     }
 }
 
@@ -187,13 +197,14 @@ __device__ __forceinline__ void epi_store_chunk(const Epilogue& e, const uint32_
 template <int BN, bool TA, bool TB>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const Epilogue epi, int M, int N, int K) {
+            const __grid_constant__ CUtensorMap tmC, const Epilogue epi, int M, int N, int K) {
     using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + C::STAGES * A_STAGE_BYTES;
-    uint64_t* bars = (uint64_t*)(smem + C::STAGES * C::STAGE_BYTES);
+    uint8_t* smem_stage = smem + C::STAGES * C::STAGE_BYTES;               // 1024-aligned (stage sizes are)
+    uint64_t* bars = (uint64_t*)(smem_stage + C::STAGING_BYTES);
     uint64_t* full_bar = bars;
     uint64_t* empty_bar = bars + C::STAGES;
     uint64_t* tmem_full = bars + 2 * C::STAGES;
@@ -202,12 +213,15 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN;
-    const int num_tiles = num_m * num_n;
     const int num_kb = (K + BK - 1) / BK;
+    const int splits = epi.splits;
+    const int num_items = num_m * num_n * splits;       // item = tile * splits + split
+    const int kb_per = (num_kb + splits - 1) / splits;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmA) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmB) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)&tmC) : "memory");
         for (int s = 0; s < C::STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -234,9 +248,11 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                const int tile = item / splits, split = item - tile * splits;
                 const int m0 = (tile % num_m) * BM, n0 = (tile / num_m) * BN;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                const int kb0 = split * kb_per, kb1 = min(num_kb, kb0 + kb_per);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
@@ -268,11 +284,13 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                const int split = item % splits;
+                const int kb0 = split * kb_per, kb1 = min(num_kb, kb0 + kb_per);
                 mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 tcgen05_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tcgen05_fence_after();
                     const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
@@ -286,7 +304,7 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                                   : make_desc(sa + k * 32, 16, 1024);
                         const uint64_t bdesc = TB ? make_desc(sb + k * 2048, BK * 128, 1024)
                                                   : make_desc(sb + k * 32, 16, 1024);
-                        umma_bf16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0);
+                        umma_bf16(d_tmem, adesc, bdesc, idesc, ((kb - kb0) | k) != 0);
                     }
                     umma_commit(&empty_bar[stage]);          // frees the smem slot when the MMAs retire
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
@@ -298,25 +316,67 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     } else {
         // ===================================================== epilogue (warps 2..5)
         const int q = warp & 3;                              // TMEM lane quarter of this warp
+        uint8_t* my_stage = smem_stage + q * 8192;
+        int buf = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+            const int tile = item / splits, split = item - tile * splits;
             const int m0 = (tile % num_m) * BM, n0 = (tile / num_m) * BN;
+            const bool has_k = split * kb_per < num_kb;      // trailing splits can be empty
             mbar_wait(&tmem_full[acc], acc_phase);
             tcgen05_fence_after();
-            const int row = m0 + q * 32 + lane;
+            const int row0 = m0 + q * 32, row = row0 + lane;
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+            const float* mrow = (epi.mask && row < M) ? epi.mask + (int64_t)row * epi.ldmask : nullptr;
+            const bool add_bias = split == 0;
+            if (row0 < M && has_k) {
+                if (epi.c_bf16) {
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
-                if (n0 + c >= N) break;                      // warp-uniform
-                uint32_t r[32];
-                tmem_ld32(t_row + (uint32_t)c, r);
-                epi_store_chunk(epi, r, row, n0 + c, M, N);
+                    for (int c = 0; c < BN; c += 64) {
+                        if (n0 + c >= N) break;              // warp-uniform
+                        uint32_t r0[32], r1[32], packed[32];
+                        tmem_ld32(t_row + (uint32_t)c, r0);
+                        tmem_ld32(t_row + (uint32_t)(c + 32), r1);
+#pragma unroll
+                        for (int g = 0; g < 16; ++g) {
+                            float v[4];
+#pragma unroll
+                            for (int t = 0; t < 4; ++t)
+                                v[t] = __uint_as_float(g < 8 ? r0[(g & 7) * 4 + t] : r1[(g & 7) * 4 + t]);
+                            epi_apply4(epi, v, mrow, n0 + c + g * 4, N, add_bias);
+                            __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+                            packed[g * 2] = *reinterpret_cast<uint32_t*>(&lo);
+                            packed[g * 2 + 1] = *reinterpret_cast<uint32_t*>(&hi);
+                        }
+                        epi_flush(epi, &tmC, my_stage + buf * 4096, lane, packed, n0 + c, row0);
+                        buf ^= 1;
+                    }
+                } else {
+#pragma unroll 1
+                    for (int c = 0; c < BN; c += 32) {
+                        if (n0 + c >= N) break;              // warp-uniform
+                        uint32_t r[32];
+                        tmem_ld32(t_row + (uint32_t)c, r);
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) {
+                            float v[4];
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) v[t] = __uint_as_float(r[g * 4 + t]);
+                            epi_apply4(epi, v, mrow, n0 + c + g * 4, N, add_bias);
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) r[g * 4 + t] = __float_as_uint(v[t]);
+                        }
+                        epi_flush(epi, &tmC, my_stage + buf * 4096, lane, r, n0 + c, row0);
+                        buf ^= 1;
+                    }
+                }
             }
             tcgen05_fence_before();
             mbar_arrive(&tmem_empty[acc]);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (lane == 0) bulk_wait_all();                      // staging buffers must outlive the bulk reads
     }
     tcgen05_fence_before();
     __syncthreads();
@@ -345,14 +405,15 @@ PFN_encodeTiled get_encode_fn() {
 }
 
 // 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements.
-int make_tmap(CUtensorMap* tm, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer) {
+int make_tmap(CUtensorMap* tm, const void* ptr, int64_t inner, int64_t outer, int64_t ld, int box_inner, int box_outer,
+              bool f32 = false) {
     PFN_encodeTiled fn = get_encode_fn();
     if (!fn) { nc_set_error("nc_gemm_bf16: cuTensorMapEncodeTiled unavailable (no CUDA driver?)"); return NC_ECUDA; }
     cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * (f32 ? 4 : 2)};
     cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+    CUresult r = fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -364,7 +425,8 @@ int make_tmap(CUtensorMap* tm, const void* ptr, int64_t inner, int64_t outer, in
 }
 
 template <int BN, bool TA, bool TB>
-int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epilogue& epi, int M, int N, int K, cudaStream_t s) {
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Epilogue& epi, int M, int N,
+           int K, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_gemm_bf16<BN, TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -372,9 +434,9 @@ int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epilogue& epi, 
         if (e != cudaSuccess) { nc_set_error("nc_gemm_bf16: cannot opt in to %d B smem: %s", Cfg<BN>::SMEM_BYTES, cudaGetErrorString(e)); return NC_ECUDA; }
         attr_set = true;
     }
-    const int tiles = (int)(nc_cdiv(M, BM) * nc_cdiv(N, BN));
-    const int grid = tiles < nc_num_sms() ? tiles : nc_num_sms();
-    k_gemm_bf16<BN, TA, TB><<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, s>>>(tmA, tmB, epi, M, N, K);
+    const int items = (int)(nc_cdiv(M, BM) * nc_cdiv(N, BN)) * epi.splits;
+    const int grid = items < nc_num_sms() ? items : nc_num_sms();
+    k_gemm_bf16<BN, TA, TB><<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, s>>>(tmA, tmB, tmC, epi, M, N, K);
     nc_count_launch(1);
     return NC_OK;
 }
@@ -407,14 +469,37 @@ extern "C" int nc_gemm_bf16(const void* A, int64_t lda, int trans_a, const void*
     if (trans_b) rc = make_tmap(&tmB, B, N, K, ldb, 64, BK);
     else         rc = make_tmap(&tmB, B, K, N, ldb, BK, BNsel);
     if (rc) return rc;
-    Epilogue epi{Cp, ldc, bias, mask, ldmask, c_dtype == NC_BF16, relu, accumulate};
+    // split K when the tiles alone cannot fill the machine and the reduction is deep (fp32 C, no ReLU):
+    // the partial tiles are summed in L2 by the TMA reduce-add.
+    const int num_kb = (int)nc_cdiv(K, BK);
+    const int64_t tiles = nc_cdiv(M, BM) * nc_cdiv(N, BNsel);
+    int splits = 1;
+    if (c_dtype == NC_F32 && !relu && tiles * 2 <= nc_num_sms() && num_kb >= 8) {
+        int want = (int)(nc_num_sms() / tiles);
+        if (want > num_kb / 4) want = num_kb / 4;
+        if (want > 16) want = 16;
+        if (want > 1) {
+            const int kb_per = (num_kb + want - 1) / want;
+            splits = (num_kb + kb_per - 1) / kb_per;         // no empty split
+        }
+    }
     cudaStream_t s = (cudaStream_t)stream;
-#define DISPATCH(BN)                                                                       \
-    do {                                                                                   \
-        if (trans_a && trans_b) rc = launch<BN, true, true>(tmA, tmB, epi, M, N, K, s);    \
-        else if (trans_a) rc = launch<BN, true, false>(tmA, tmB, epi, M, N, K, s);         \
-        else if (trans_b) rc = launch<BN, false, true>(tmA, tmB, epi, M, N, K, s);         \
-        else rc = launch<BN, false, false>(tmA, tmB, epi, M, N, K, s);                     \
+    if (splits > 1 && !accumulate) {
+        cudaError_t e = cudaMemset2DAsync(Cp, (size_t)ldc * 4, 0, (size_t)N * 4, (size_t)M, s);
+        if (e != cudaSuccess) { nc_set_error("nc_gemm_bf16: memset failed: %s", cudaGetErrorString(e)); return NC_ECUDA; }
+    }
+    CUtensorMap tmC;
+    rc = make_tmap(&tmC, Cp, N, M, ldc, c_dtype == NC_BF16 ? 64 : 32, 32, c_dtype == NC_F32);
+    if (rc) return rc;
+    Epilogue epi{bias, mask, ldmask, c_dtype == NC_BF16, relu, (accumulate || splits > 1) ? 1 : 0,
+                 ((uintptr_t)bias % 16 == 0) ? 1 : 0, (mask && (uintptr_t)mask % 16 == 0 && ldmask % 4 == 0) ? 1 : 0,
+                 splits};
+#define DISPATCH(BN)                                                                            \
+    do {                                                                                        \
+        if (trans_a && trans_b) rc = launch<BN, true, true>(tmA, tmB, tmC, epi, M, N, K, s);    \
+        else if (trans_a) rc = launch<BN, true, false>(tmA, tmB, tmC, epi, M, N, K, s);         \
+        else if (trans_b) rc = launch<BN, false, true>(tmA, tmB, tmC, epi, M, N, K, s);         \
+        else rc = launch<BN, false, false>(tmA, tmB, tmC, epi, M, N, K, s);                     \
     } while (0)
     if (BNsel == 256) DISPATCH(256); else DISPATCH(128);
 #undef DISPATCH

@@ -123,37 +123,67 @@ __global__ void k_reg_grad(const float* __restrict__ W, int64_t ld, int F, int P
 }
 
 // ------------------------------------------------------------------------- Adam (torch semantics)
-__global__ void k_adam(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
-                       int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
-                       float clip, __nv_bfloat16* __restrict__ p_bf16) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        float gi = g[i];
-        if (clip > 0.f) gi = fminf(fmaxf(gi, -clip), clip);
-        const float pi = p[i];
-        if (wd != 0.f) gi += wd * pi;
-        const float mi = b1 * m[i] + (1.f - b1) * gi;
-        const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
-        m[i] = mi;
-        v[i] = vi;
-        const float denom = sqrtf(vi) / bc2_sqrt + eps;
-        const float np = pi - (lr / bc1) * (mi / denom);
-        p[i] = np;
+__device__ __forceinline__ float adam_elem(float pi, float gi, float& mi, float& vi, float lr_bc1, float b1, float b2,
+                                           float eps, float wd, float bc2_sqrt, float clip) {
+    if (clip > 0.f) gi = fminf(fmaxf(gi, -clip), clip);
+    if (wd != 0.f) gi += wd * pi;
+    mi = b1 * mi + (1.f - b1) * gi;
+    vi = b2 * vi + (1.f - b2) * gi * gi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    return pi - lr_bc1 * (mi / denom);
+}
+
+// 128-bit accesses over the 4-aligned body, scalar tail.  zero_g: the gradient buffer is cleared
+// after it has been consumed (saves the separate memset of optimizer.zero_grad()).
+__global__ void __launch_bounds__(256)
+k_adam(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+       int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
+       float clip, __nv_bfloat16* __restrict__ p_bf16, int zero_g) {
+    const float lr_bc1 = lr / bc1;
+    const int64_t n4 = n >> 2;
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = t0; i < n4; i += nt) {
+        float4 pp = reinterpret_cast<float4*>(p)[i];
+        const float4 gg = reinterpret_cast<const float4*>(g)[i];
+        float4 mm = reinterpret_cast<float4*>(m)[i];
+        float4 vv = reinterpret_cast<float4*>(v)[i];
+        pp.x = adam_elem(pp.x, gg.x, mm.x, vv.x, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        pp.y = adam_elem(pp.y, gg.y, mm.y, vv.y, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        pp.z = adam_elem(pp.z, gg.z, mm.z, vv.z, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        pp.w = adam_elem(pp.w, gg.w, mm.w, vv.w, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        reinterpret_cast<float4*>(p)[i] = pp;
+        reinterpret_cast<float4*>(m)[i] = mm;
+        reinterpret_cast<float4*>(v)[i] = vv;
+        if (zero_g) reinterpret_cast<float4*>(g)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p_bf16) {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y), hi = __floats2bfloat162_rn(pp.z, pp.w);
+            uint2 q;
+            q.x = *reinterpret_cast<uint32_t*>(&lo);
+            q.y = *reinterpret_cast<uint32_t*>(&hi);
+            reinterpret_cast<uint2*>(p_bf16)[i] = q;
+        }
+    }
+    for (int64_t i = (n4 << 2) + t0; i < n; i += nt) {
+        float mi = m[i], vi = v[i];
+        const float np = adam_elem(p[i], g[i], mi, vi, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        p[i] = np; m[i] = mi; v[i] = vi;
+        if (zero_g) g[i] = 0.f;
         if (p_bf16) p_bf16[i] = __float2bfloat16_rn(np);
     }
 }
 
 // fp32 -> bf16 cast (optionally multiplied by a mask of the same shape), 2-D with leading dims
 __global__ void k_cast_bf16(const float* __restrict__ src, int64_t lds, const float* __restrict__ mask, int64_t ldm,
-                            int R, int C, __nv_bfloat16* __restrict__ dst, int64_t ldd) {
-    const int64_t total = (int64_t)R * ldd;
+                            int R, int C, __nv_bfloat16* __restrict__ dst, int64_t ldd, int W) {
+    const int64_t total = (int64_t)R * W;
     for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
-        const int r = (int)(q / ldd), c = (int)(q % ldd);
+        const int r = (int)(q / W), c = (int)(q % W);
         float v = 0.f;
         if (c < C) {
             v = src[(int64_t)r * lds + c];
             if (mask) v *= mask[(int64_t)r * ldm + c];
         }
-        dst[q] = __float2bfloat16_rn(v);
+        dst[(int64_t)r * ldd + c] = __float2bfloat16_rn(v);
     }
 }
 }  // namespace
@@ -231,26 +261,30 @@ extern "C" int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t
     return NC_OK;
 }
 
-extern "C" int nc_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+extern "C" int nc_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
                             float beta2, float eps, float weight_decay, int32_t step, float clip_value, void* p_bf16,
-                            void* stream) {
+                            int zero_grad, void* stream) {
     NC_REQUIRE(n >= 0 && step >= 1, NC_EINVAL, "nc_adam_step: need n >= 0 and step >= 1");
     if (n == 0) return NC_OK;
     const float bc1 = (float)(1.0 - pow((double)beta1, (double)step));
     const float bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
-    k_adam<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, bc1,
-                                                         bc2_sqrt, clip_value, (__nv_bfloat16*)p_bf16);
+    NC_REQUIRE(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0 && (uintptr_t)p_bf16 % 8 == 0,
+               NC_EINVAL, "nc_adam_step: buffers must be 16-byte aligned");
+    k_adam<<<grid_for((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, weight_decay,
+                                                                   bc1, bc2_sqrt, clip_value, (__nv_bfloat16*)p_bf16,
+                                                                   zero_grad);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_adam_step");
     return NC_OK;
 }
 
 extern "C" int nc_cast_bf16(const float* src, int64_t lds, const float* mask, int64_t ldmask, int32_t R, int32_t C,
-                            void* dst, int64_t ldd, void* stream) {
-    NC_REQUIRE(R >= 0 && C > 0 && lds >= C && ldd >= C, NC_ESHAPE, "nc_cast_bf16: bad shape");
+                            void* dst, int64_t ldd, int32_t fill_cols, void* stream) {
+    if (fill_cols <= 0) fill_cols = (int32_t)ldd;
+    NC_REQUIRE(R >= 0 && C > 0 && lds >= C && fill_cols >= C && ldd >= fill_cols, NC_ESHAPE, "nc_cast_bf16: bad shape");
     if (R == 0) return NC_OK;
-    k_cast_bf16<<<grid_for((int64_t)R * ldd), 256, 0, (cudaStream_t)stream>>>(src, lds, mask, ldmask, R, C,
-                                                                             (__nv_bfloat16*)dst, ldd);
+    k_cast_bf16<<<grid_for((int64_t)R * fill_cols), 256, 0, (cudaStream_t)stream>>>(src, lds, mask, ldmask, R, C,
+                                                                                   (__nv_bfloat16*)dst, ldd, fill_cols);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_cast_bf16");
     return NC_OK;

@@ -55,6 +55,15 @@ class SubgraphCSR:
 # --------------------------------------------------------------------------- packed weights
 _PACK_CACHE = {}
 _PARAM_EPOCH = 0
+_KEY_COUNTER = [0]
+
+
+def new_cache_key() -> int:
+    """Process-unique token for a module's packed-weight cache entries (``id()`` values are
+    recycled after garbage collection and would let a new module hit a dead module's entry)."""
+    _KEY_COUNTER[0] += 1
+    return _KEY_COUNTER[0]
+
 
 
 def bump_param_epoch():
@@ -68,9 +77,53 @@ def _versions(ts: Sequence[Optional[torch.Tensor]]):
     return (_PARAM_EPOCH,) + tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
 
 
+def arena_view(params: Sequence[Optional[torch.Tensor]], kind: str) -> Optional[torch.Tensor]:
+    """1-D view over ``params`` inside a ``FlatAdam`` arena when they lie back to back there
+    (``FlatAdam(groups=...)``): kind 'p' = fp32 parameters, 'g' = gradients (zeroed before every
+    backward, kernels ACCUMULATE into it), 'b' = bf16 shadow kept current by the Adam kernel.
+    ``None`` when the parameters are not arena residents (plain modules, frozen weights)."""
+    if not params or params[0] is None:
+        return None
+    first = getattr(params[0], "_nc_arena", None)
+    if first is None:
+        return None
+    opt, off = first
+    if off % 8 != 0:
+        return None
+    o = off
+    base_p, base_g = opt.flat_p.data_ptr(), opt.flat_g.data_ptr()
+    for t in params:
+        a = getattr(t, "_nc_arena", None) if t is not None else None
+        if a is None or a[0] is not opt or a[1] != o or not t.requires_grad or t.data_ptr() != base_p + 4 * o:
+            return None
+        if kind == "g" and (t.grad is None or t.grad.data_ptr() != base_g + 4 * o):
+            return None
+        o += t.numel()
+    if kind == "p":
+        return opt.flat_p[off:o]
+    if kind == "g":
+        return opt.flat_g[off:o]
+    if opt.flat_bf16 is None:
+        return None
+    if not opt.shadow_is_current():
+        opt.refresh_shadow()
+    return opt.flat_bf16[off:o]
+
+
+def grad_view(params: Sequence[Optional[torch.Tensor]], needs: Sequence[bool]) -> Optional[torch.Tensor]:
+    """Gradient arena view for a group of parameters that all need a gradient, else ``None``."""
+    if not all(needs):
+        return None
+    return arena_view(params, "g")
+
+
 def pack_rows(key, params: Sequence[torch.Tensor], dtype: torch.dtype, n_cols: int) -> torch.Tensor:
     """Stack 2-D parameters [r_i, n_cols] row-wise into one [sum r_i, pad8(n_cols)] buffer of
     ``dtype`` (bf16 shadow / fp32 packed copy); refreshed only when a parameter changed."""
+    if n_cols % 8 == 0 and all(p.dim() == 2 and p.size(1) == n_cols for p in params):
+        v = arena_view(params, "b" if dtype == torch.bfloat16 else "p")
+        if v is not None:
+            return v.view(-1, n_cols)
     ver = (_versions(params), dtype)
     hit = _PACK_CACHE.get(key)
     if hit is not None and hit[0] == ver:
@@ -84,7 +137,7 @@ def pack_rows(key, params: Sequence[torch.Tensor], dtype: torch.dtype, n_cols: i
         for p in params:
             p2 = p.detach().reshape(p.size(0), -1)
             if dtype == torch.bfloat16:
-                call("nc_cast_bf16", p2, p2.stride(0), None, 0, p2.size(0), p2.size(1), buf[r:], ld)
+                call("nc_cast_bf16", p2, p2.stride(0), None, 0, p2.size(0), p2.size(1), buf[r:], ld, 0)
             else:
                 buf[r:r + p2.size(0), :p2.size(1)].copy_(p2)
             r += p2.size(0)
@@ -114,7 +167,7 @@ def pack_cols(key, params: Sequence[torch.Tensor], masks: Sequence[Optional[torc
             c += p.size(1)
         if dtype == torch.bfloat16:
             buf = torch.empty(F, ld, dtype=torch.bfloat16, device=buf32.device)
-            call("nc_cast_bf16", buf32, ld, None, 0, F, ld, buf, ld)
+            call("nc_cast_bf16", buf32, ld, None, 0, F, ld, buf, ld, 0)
         else:
             buf = buf32
     _PACK_CACHE[key] = (ver, buf)
@@ -122,14 +175,19 @@ def pack_cols(key, params: Sequence[torch.Tensor], masks: Sequence[Optional[torc
 
 
 def _cat_f32(ts: Sequence[torch.Tensor], pad_to: Optional[int] = None) -> torch.Tensor:
+    v = arena_view(ts, "p")
+    if v is not None:
+        return v
     flat = torch.cat([t.detach().reshape(-1).float() for t in ts])
     if pad_to is not None and flat.numel() < pad_to:
         flat = torch.cat([flat, flat.new_zeros(pad_to - flat.numel())])
     return flat.contiguous()
 
 
-def _col_sum(x: torch.Tensor, n_cols: int) -> torch.Tensor:
-    out = torch.zeros(n_cols, dtype=torch.float32, device=x.device)
+def _col_sum(x: torch.Tensor, n_cols: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[c] += sum_r x[r, c] (``out`` given: accumulate into it, e.g. a gradient arena view)."""
+    if out is None:
+        out = torch.zeros(n_cols, dtype=torch.float32, device=x.device)
     if x.size(0) > 0:
         call("nc_col_sum", x, dtype_code(x.dtype), x.stride(0), x.size(0), n_cols, out)
     return out
@@ -166,9 +224,12 @@ class EncoderGATv2Fn(torch.autograd.Function):
         Wr = pack_rows((cache_key, "Wr"), [cv[2] for cv in conv], act, Hd)
         bl, br = _cat_f32([cv[1] for cv in conv]), _cat_f32([cv[3] for cv in conv])
         att = _cat_f32([cv[4] for cv in conv], pad_to=ldl)
-        bias_out = torch.zeros(out_width, dtype=torch.float32, device=dev)
-        for c in range(NC):
-            bias_out[out_offsets[c]:out_offsets[c] + Cs[c]] = conv[c][5].detach()
+        tight = list(out_offsets) == [sum(Cs[:c]) for c in range(NC)] and sum(Cs) == out_width
+        bias_out = arena_view([cv[5] for cv in conv], "p") if tight else None
+        if bias_out is None:
+            bias_out = torch.zeros(out_width, dtype=torch.float32, device=dev)
+            for c in range(NC):
+                bias_out[out_offsets[c]:out_offsets[c] + Cs[c]] = conv[c][5].detach()
         ldh = pad8(Hd)
         Hbuf = torch.zeros(n_sub, ldh, dtype=act, device=dev) if ldh != Hd else torch.empty(n_sub, ldh, dtype=act, device=dev)
         ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
@@ -183,6 +244,7 @@ class EncoderGATv2Fn(torch.autograd.Function):
         ctx.save_for_backward(x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr)
         ctx.meta = (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
                     [tuple(t.shape) for t in tensors], tuple(W1.shape))
+        ctx.params = (W1, b1, conv, tight)          # arena residents receive their gradients in place
         return out
 
     @staticmethod
@@ -199,18 +261,39 @@ class EncoderGATv2Fn(torch.autograd.Function):
         if ldl != NL:
             dXL[:, NL:].zero_()
             dXR[:, NL:].zero_()
-        datt = torch.zeros(ldl, dtype=torch.float32, device=dev)
-        dbias = torch.zeros(out_width, dtype=torch.float32, device=dev)
+        W1, b1, conv, tight = ctx.params
+        need = ctx.needs_input_grad          # (x_enc, graph, n_feat, heads, offs, width, key, W1, b1, *tensors)
+        need_c = [need[9 + 6 * c:15 + 6 * c] for c in range(NC)]
+
+        def gv(slot):
+            return grad_view([cv[slot] for cv in conv], [nc[slot] for nc in need_c])
+        g_bl, g_br, g_att = gv(1), gv(3), gv(4)
+        g_Wl, g_Wr = (gv(0), gv(2)) if Hd % 4 == 0 else (None, None)       # GEMM C rows must stay 16-byte aligned
+        g_bias = gv(5) if tight else None
+        g_W1 = grad_view([W1], [need[7]]) if (n_feat == W1.size(1) and n_feat % 4 == 0) else None
+        g_b1 = grad_view([b1], [need[8]])
+        datt = g_att if g_att is not None else torch.zeros(ldl, dtype=torch.float32, device=dev)
+        dbias = g_bias if g_bias is not None else torch.zeros(out_width, dtype=torch.float32, device=dev)
         ds = torch.empty_like(alpha)
         call("nc_gatv2_bwd", XL, XR, dtype_code(act), ldl, att, graph.rowptr, graph.col, n_dst, n_sub,
              rptr, rdst, rslot, seg, HostPtr(seg_host), NC, heads, graph.max_deg, 0.2, dout, dout.stride(0), alpha, ds,
              dXL, dXR, datt, dbias)
         # weight gradients of lin_l / lin_r (all convs in one GEMM each), bias gradients
-        dWl = ops.gemm(dXL, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=Hd, K=n_sub)
-        dWr = ops.gemm(dXR, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=Hd, K=n_dst) \
-            if n_dst > 0 else torch.zeros(NL, Hd, device=dev)
-        dbl = _col_sum(dXL, NL)
-        dbr = _col_sum(dXR[:n_dst], NL)
+        if g_Wl is not None:
+            ops.gemm(dXL, Hbuf, trans_a=True, trans_b=True, out=g_Wl.view(NL, Hd), accumulate=True, M=NL, N=Hd, K=n_sub)
+            dWl = None
+        else:
+            dWl = ops.gemm(dXL, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=Hd, K=n_sub)
+        if g_Wr is not None:
+            if n_dst > 0:
+                ops.gemm(dXR, Hbuf, trans_a=True, trans_b=True, out=g_Wr.view(NL, Hd), accumulate=True,
+                         M=NL, N=Hd, K=n_dst)
+            dWr = None
+        else:
+            dWr = ops.gemm(dXR, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=Hd, K=n_dst) \
+                if n_dst > 0 else torch.zeros(NL, Hd, device=dev)
+        dbl = _col_sum(dXL, NL, out=g_bl)
+        dbr = _col_sum(dXR[:n_dst], NL, out=g_br)
         # dH = dXL @ Wl (+ dXR @ Wr on the seed rows)
         dH = torch.empty(n_sub, pad8(Hd), dtype=torch.float32, device=dev)
         ops.gemm(dXL, Wl, trans_b=True, out=dH[:, :Hd], M=n_sub, N=Hd, K=NL)
@@ -218,15 +301,26 @@ class EncoderGATv2Fn(torch.autograd.Function):
             ops.gemm(dXR, Wr, trans_b=True, out=dH[:n_dst, :Hd], accumulate=True, M=n_dst, N=Hd, K=NL)
         dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
         call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
-        dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
-        db1 = _col_sum(dHp, Hd)
+        if g_W1 is not None:
+            ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out=g_W1.view(Hd, n_feat), accumulate=True,
+                     M=Hd, N=n_feat, K=n_sub)
+            dW1 = None
+        else:
+            dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
+        db1 = _col_sum(dHp, Hd, out=g_b1)
         grads: List[Optional[torch.Tensor]] = []
         for c in range(NC):
             sl = slice(offs[c], offs[c] + widths[c])
-            grads += [dWl[sl].reshape(shapes[6 * c]), dbl[sl], dWr[sl].reshape(shapes[6 * c + 2]), dbr[sl],
-                      datt[sl].reshape(shapes[6 * c + 4]),
-                      dbias[out_offsets[c]:out_offsets[c] + Cs[c]]]
-        dW1 = dW1 if dW1.shape == w1_shape else dW1.contiguous()
+            grads += [None if g_Wl is not None else dWl[sl].reshape(shapes[6 * c]),
+                      None if g_bl is not None else dbl[sl],
+                      None if g_Wr is not None else dWr[sl].reshape(shapes[6 * c + 2]),
+                      None if g_br is not None else dbr[sl],
+                      None if g_att is not None else datt[sl].reshape(shapes[6 * c + 4]),
+                      None if g_bias is not None else dbias[out_offsets[c]:out_offsets[c] + Cs[c]]]
+        if g_b1 is not None:
+            db1 = None
+        if dW1 is not None and dW1.shape != w1_shape:
+            dW1 = dW1.contiguous()
         dx = None
         if ctx.needs_input_grad[0]:
             # only the trailing (embedding) columns of the encoder input can require grad
@@ -342,10 +436,46 @@ class BCEFn(torch.autograd.Function):
 
 
 # --------------------------------------------------------------------------- masked decoder
+def _block_layout(widths: Sequence[int]):
+    """Column offsets of the (prior | add-on | embedding) blocks in the packed operands: every
+    block starts on a multiple of 8 elements so that each is a legal TMA operand on its own."""
+    offs, c = [], 0
+    for w in widths:
+        offs.append(c)
+        c += pad8(w)
+    return offs, c
+
+
+def pack_decoder_weight(key, params, masks, dtype, offs, Kp) -> torch.Tensor:
+    """[F, Kp] packed ``weight * mask [* dynamic mask]`` (nn/layercomponents.py:74-79), refreshed
+    only when a parameter / mask changed."""
+    ver = (_versions(params), _versions(masks), dtype)
+    hit = _PACK_CACHE.get(key)
+    if hit is not None and hit[0] == ver:
+        return hit[1]
+    F = params[0].size(0)
+    buf = hit[1] if (hit is not None and hit[1].shape == (F, Kp) and hit[1].dtype == dtype) else \
+        torch.zeros(F, Kp, dtype=dtype, device=params[0].device)
+    with torch.no_grad():
+        for p_, m, o in zip(params, masks, offs):
+            w = p_.size(1)
+            pd = p_.detach()
+            if dtype == torch.bfloat16:
+                call("nc_cast_bf16", pd, pd.stride(0), m, m.stride(0) if m is not None else 0, F, w,
+                     buf[:, o:], Kp, pad8(w))
+            elif m is None:
+                buf[:, o:o + w].copy_(pd)
+            else:
+                torch.mul(pd, m, out=buf[:, o:o + w])
+    _PACK_CACHE[key] = (ver, buf)
+    return buf
+
+
 class MaskedDecoderFn(torch.autograd.Function):
-    """logits = cat(z, embed) @ (W * mask)^T for the packed decoder weight
-    [F, P_prior | P_addon | n_embed] (nn/layers.py:83-142, nn/layercomponents.py:53-81).
-    The GP mask is re-applied to the weight gradient in the GEMM epilogue."""
+    """logits = cat(z, embed) @ (W * mask)^T for the decoder weight blocks
+    [F, P_prior | P_addon | n_embed] (nn/layers.py:83-142, nn/layercomponents.py:53-81) as ONE
+    GEMM over the packed operands.  The GP mask is re-applied to each block's weight gradient in
+    the GEMM epilogue; arena-resident weights receive it in place."""
 
     @staticmethod
     def forward(ctx, zcat, act_dtype, cache_key, dyn_masks, *params_and_masks):
@@ -358,41 +488,52 @@ class MaskedDecoderFn(torch.autograd.Function):
             elif d is not None:
                 m = d
             eff_masks.append(m)
-        Wp = pack_cols(cache_key, params, eff_masks, act_dtype)
-        K = sum(p.size(1) for p in params)
+        widths = [p.size(1) for p in params]
+        offs, Kp = _block_layout(widths)
+        Wp = pack_decoder_weight(cache_key, params, eff_masks, act_dtype, offs, Kp)
         F = params[0].size(0)
         nb = zcat.size(0)
-        za = torch.zeros(nb, pad8(K), dtype=act_dtype, device=zcat.device)
-        za[:, :K] = zcat.detach()
-        logits = ops.gemm(za, Wp, out_dtype=torch.float32, M=nb, N=F, K=K)
+        za = torch.zeros(nb, Kp, dtype=act_dtype, device=zcat.device)
+        zd, c = zcat.detach(), 0
+        for w, o in zip(widths, offs):
+            za[:, o:o + w] = zd[:, c:c + w]
+            c += w
+        logits = ops.gemm(za, Wp, out_dtype=torch.float32, M=nb, N=F, K=Kp)
         ctx.save_for_backward(za, Wp, *[m for m in eff_masks if m is not None])
-        ctx.meta = (K, F, [p.size(1) for p in params], [m is not None for m in eff_masks], act_dtype)
+        ctx.meta = (F, widths, offs, Kp, [m is not None for m in eff_masks], act_dtype)
+        ctx.params = params
         return logits
 
     @staticmethod
     def backward(ctx, dlogits):
         za, Wp = ctx.saved_tensors[:2]
         saved_masks = list(ctx.saved_tensors[2:])
-        K, F, widths, has_mask, act = ctx.meta
+        F, widths, offs, Kp, has_mask, act = ctx.meta
         nb = za.size(0)
-        dl = torch.zeros(nb, pad8(F), dtype=act, device=za.device)
-        dl[:, :F] = dlogits
-        if any(has_mask):
-            mfull = torch.ones(F, pad8(K), dtype=torch.float32, device=za.device)
-            c = 0
-            for w, hm in zip(widths, has_mask):
-                if hm:
-                    mfull[:, c:c + w] = saved_masks.pop(0)
-                c += w
+        n = len(widths)
+        if act == torch.float32 and dlogits.stride(1) == 1 and dlogits.dtype == torch.float32:
+            dl = dlogits
         else:
-            mfull = None
-        dW = ops.gemm(dl, za, trans_a=True, trans_b=True, out_dtype=torch.float32, mask=mfull, M=F, N=K, K=nb)
-        dz = ops.gemm(dl, Wp, trans_b=True, out_dtype=torch.float32, M=nb, N=K, K=F)
-        grads, c = [], 0
-        for w in widths:
-            grads.append(dW[:, c:c + w])
-            c += w
-        return (dz, None, None, None, *grads, *([None] * len(widths)))
+            dl = torch.zeros(nb, pad8(F), dtype=act, device=za.device)
+            dl[:, :F] = dlogits
+        dzp = ops.gemm(dl, Wp, trans_b=True, out_dtype=torch.float32, M=nb, N=Kp, K=F)
+        dz = dzp[:, :widths[0]] if n == 1 else torch.cat([dzp[:, o:o + w] for w, o in zip(widths, offs)], dim=1)
+        grads = []
+        for i, (w, o) in enumerate(zip(widths, offs)):
+            m = saved_masks.pop(0) if has_mask[i] else None
+            if not ctx.needs_input_grad[4 + i]:
+                grads.append(None)
+                continue
+            ldm = m.stride(0) if m is not None else 0
+            zb = za[:, o:o + pad8(w)]
+            g = grad_view([ctx.params[i]], [True]) if w % 4 == 0 else None
+            if g is not None:
+                ops.gemm(dl, zb, trans_a=True, trans_b=True, out=g.view(F, w), mask=m, accumulate=True, M=F, N=w, K=nb)
+                grads.append(None)
+            else:
+                grads.append(ops.gemm(dl, zb, trans_a=True, trans_b=True, out_dtype=torch.float32, mask=m,
+                                      M=F, N=w, K=nb))
+        return (dz, None, None, None, *grads, *([None] * n))
 
 
 class NBLossFusedFn(torch.autograd.Function):

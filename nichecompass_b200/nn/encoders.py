@@ -8,7 +8,7 @@ from typing import Literal, Optional, Tuple
 import torch
 import torch.nn as nn
 
-from ..functional import EncoderGATv2Fn, EncoderGCNFn, SubgraphCSR
+from ..functional import EncoderGATv2Fn, EncoderGCNFn, SubgraphCSR, new_cache_key
 from ..ops import pad8
 from .conv import GATv2Conv, GCNConv
 
@@ -69,7 +69,7 @@ class Encoder(nn.Module):
             self.addon_conv_mu = conv(n_addon_latent)
             self.addon_conv_logstd = conv(n_addon_latent)
         self.compute_dtype = torch.float32
-        self._key = id(self)
+        self._key = new_cache_key()
 
     # ------------------------------------------------------------------ fused path
     @property
@@ -86,6 +86,16 @@ class Encoder(nn.Module):
         if self.n_addon_latent != 0:
             convs.append((self.addon_conv_logstd, P + self.n_latent))
         return convs
+
+    def arena_groups(self):
+        """Parameters the fused kernels consume stacked: laid out back to back by ``FlatAdam`` so
+        that the stacked matrices, their bf16 shadows and their gradients are views."""
+        convs = [c for c, _ in self._convs()]
+        if self.conv_layer == "gatv2conv":
+            return [[c.lin_l.weight for c in convs], [c.lin_r.weight for c in convs],
+                    [c.lin_l.bias for c in convs], [c.lin_r.bias for c in convs],
+                    [c.att for c in convs], [c.bias for c in convs], [self.fc_l1.weight], [self.fc_l1.bias]]
+        return [[c.lin.weight for c in convs], [c.bias for c in convs], [self.fc_l1.weight], [self.fc_l1.bias]]
 
     def encode(self, x_enc: torch.Tensor, graph: SubgraphCSR) -> torch.Tensor:
         """``x_enc``: [n_sub, pad8(n_input)] in ``compute_dtype`` (log1p counts ++ optional

@@ -6,7 +6,7 @@ from typing import Optional
 import torch
 import torch.nn as nn
 
-from ..functional import MaskedDecoderFn
+from ..functional import MaskedDecoderFn, new_cache_key
 
 
 class MaskedLinear(nn.Linear):
@@ -26,6 +26,7 @@ class MaskedLinear(nn.Linear):
         self.register_buffer("mask", mask.t().to(self.weight.dtype).contiguous())
         self.weight.data *= self.mask
         self.compute_dtype = torch.float32
+        self._key = new_cache_key()
 
     def apply_dynamic_mask_(self, dynamic_mask: torch.Tensor) -> torch.Tensor:
         """``weight.data *= dynamic_mask.t()`` -- the permanent side effect of the reference
@@ -37,4 +38,4 @@ class MaskedLinear(nn.Linear):
 
     def forward(self, input: torch.Tensor, dynamic_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
         dm = self.apply_dynamic_mask_(dynamic_mask) if dynamic_mask is not None else None
-        return MaskedDecoderFn.apply(input, self.compute_dtype, (id(self), "w"), [dm], self.weight, self.mask)
+        return MaskedDecoderFn.apply(input, self.compute_dtype, (self._key, "w"), [dm], self.weight, self.mask)

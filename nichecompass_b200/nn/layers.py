@@ -8,7 +8,7 @@ from typing import List, Optional
 import torch
 import torch.nn as nn
 
-from ..functional import MaskedDecoderFn
+from ..functional import MaskedDecoderFn, new_cache_key
 from .layercomponents import MaskedLinear
 
 
@@ -37,6 +37,7 @@ class AddOnMaskedLayer(nn.Module):
         self.activation = activation
         self.compute_dtype = torch.float32
         self._embed_mask = None
+        self._key = new_cache_key()
 
     def _embed_col_mask(self) -> Optional[torch.Tensor]:
         """Without add-on GPs the embedding only feeds the masked features (nn/layers.py:134-142)."""
@@ -64,7 +65,7 @@ class AddOnMaskedLayer(nn.Module):
             params.append(self.cat_covariates_embed_l.weight)
             masks.append(self._embed_col_mask())
             dyn.append(None)
-        return MaskedDecoderFn.apply(input, self.compute_dtype, (id(self), "packed"), dyn, *params, *masks)
+        return MaskedDecoderFn.apply(input, self.compute_dtype, (self._key, "packed"), dyn, *params, *masks)
 
     def forward(self, input: torch.Tensor, dynamic_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Reference signature.  The activation here is the module passed at construction

@@ -356,7 +356,10 @@ class Trainer(BaseTrainerMixin):
         self.model.train()
         self.model.materialize_outputs = False              # training consumes the fused losses only
         params = [p for p in self.model.parameters() if p.requires_grad]
-        self.optimizer = FlatAdam(params, lr=lr, weight_decay=weight_decay)
+        enc = getattr(self.model, "encoder", None)
+        groups = enc.arena_groups() if hasattr(enc, "arena_groups") else None
+        shadow = getattr(self.model, "compute_dtype", torch.float32) == torch.bfloat16
+        self.optimizer = FlatAdam(params, lr=lr, weight_decay=weight_decay, groups=groups, bf16_shadow=shadow)
         self.epoch = 0
         self._set_epoch_flags()
 

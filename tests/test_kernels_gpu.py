@@ -118,7 +118,8 @@ def test_gemm_f32(ta, tb):
 
 
 @pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
-@pytest.mark.parametrize("shape", [(128, 128, 64), (300, 200, 136), (1000, 1608, 520), (64, 5000, 1600)])
+@pytest.mark.parametrize("shape", [(128, 128, 64), (300, 200, 136), (1000, 1608, 520), (64, 5000, 1600),
+                                   (64, 1608, 5000), (5000, 1500, 72)])
 def test_gemm_bf16_tcgen05(ta, tb, shape):
     g = torch.Generator().manual_seed(1)
     M, N, K = shape

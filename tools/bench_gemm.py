@@ -1,5 +1,7 @@
 """Micro-benchmark of nc_gemm_bf16 on the hot-path GEMM shapes (CUDA events, L2 flushed)."""
+import os
 import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from nichecompass_b200 import ops
 
