@@ -3,6 +3,7 @@
 // KL regulariser.  Reference: nn/layers.py:143, nn/decoders.py:168, modules/vgpgae.py:714-749,
 // modules/losses.py:123-166 (BCE), :169-212 (NB), :255-284 (KL), nn/utils.py:8-36 (cosine).
 #include <algorithm>
+#include <cooperative_groups.h>
 
 #include "common.cuh"
 
@@ -18,37 +19,61 @@ __device__ double digamma_d(double x) {
     return r + log(x) - 0.5 / x - f * (1.0 / 12.0 - f * (1.0 / 120.0 - f * (1.0 / 252.0 - f * (1.0 / 240.0 - f * (1.0 / 132.0)))));
 }
 
-constexpr int NB_T = 256;
+constexpr int NB_T = 512;
+constexpr int NB_CL = 4;      // CTAs (one thread-block cluster) per row
 
-// One CTA per row.  logits: decoder pre-activations over ALL F features; sel[c] != 0 marks the
-// reconstructed columns (softmax is over all F, library size and loss over selected columns).
+// One 4-CTA cluster per row: each CTA owns a quarter of the columns, the row-wide reductions
+// (max, library size, softmax denominator, D) are exchanged through distributed shared memory.
+// logits: decoder pre-activations over ALL F features; sel[c] != 0 marks the reconstructed
+// columns (softmax is over all F, library size and loss over selected columns).
 __global__ void __launch_bounds__(NB_T)
 k_nb_fused(const float* __restrict__ logits, int64_t ldl, const float* __restrict__ x, int64_t ldx,
            const uint8_t* __restrict__ sel, const float* __restrict__ theta_param, int F, float scale,
            float* __restrict__ means, int64_t ldm, double* __restrict__ loss_sum,
            float* __restrict__ dlogits, int64_t lddl, float* __restrict__ dtheta) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
     __shared__ float red[32];
     __shared__ double redd[32];
-    const int r = blockIdx.x, tid = threadIdx.x;
+    __shared__ float xf[2][2];     // [phase parity][value] partials read by the other CTAs of the cluster
+    __shared__ double xd[1];
+    const int rank = (int)cluster.block_rank();
+    const int r = blockIdx.x / NB_CL, tid = threadIdx.x;
+    const int per = (F + NB_CL - 1) / NB_CL;
+    const int c0 = rank * per, c1 = min(F, c0 + per);
     const float* lr = logits + (int64_t)r * ldl;
     const float* xr = x + (int64_t)r * ldx;
     // row max, library size
     float m = -INFINITY, lib = 0.f;
-    for (int c = tid; c < F; c += NB_T) {
+    for (int c = c0 + tid; c < c1; c += NB_T) {
         m = fmaxf(m, lr[c]);
         if (sel[c]) lib += xr[c];
     }
     m = block_max(m, red);
     lib = block_sum(lib, red);
+    if (tid == 0) { xf[0][0] = m; xf[0][1] = lib; }
+    cluster.sync();
+    m = -INFINITY; lib = 0.f;
+#pragma unroll
+    for (int k = 0; k < NB_CL; ++k) {
+        const float* o = cluster.map_shared_rank(&xf[0][0], k);
+        m = fmaxf(m, o[0]);
+        lib += o[1];
+    }
     float se = 0.f;
-    for (int c = tid; c < F; c += NB_T) se += expf(lr[c] - m);
+    for (int c = c0 + tid; c < c1; c += NB_T) se += expf(lr[c] - m);
     se = block_sum(se, red);
+    if (tid == 0) xf[1][0] = se;
+    cluster.sync();
+    se = 0.f;
+#pragma unroll
+    for (int k = 0; k < NB_CL; ++k) se += *cluster.map_shared_rank(&xf[1][0], k);
     const double L = (double)lib;           // exp(log(library size))
     const double inv_se = 1.0 / (double)se;
     // loss and D = sum_c dmu_c * mu_c
     double loss = 0.0, D = 0.0;
     const double eps = 1e-8;
-    for (int c = tid; c < F; c += NB_T) {
+    for (int c = c0 + tid; c < c1; c += NB_T) {
         const double p = (double)expf(lr[c] - m) * inv_se;
         const double mu = L * p;
         if (means) means[(int64_t)r * ldm + c] = (float)mu;
@@ -69,10 +94,15 @@ k_nb_fused(const float* __restrict__ logits, int64_t ldl, const float* __restric
     }
     loss = block_sum_d(loss, redd);
     D = block_sum_d(D, redd);
-    if (tid == 0) atomicAdd(loss_sum, loss);
+    if (tid == 0) { atomicAdd(loss_sum, loss); xd[0] = D; }
+    cluster.sync();
+    D = 0.0;
+#pragma unroll
+    for (int k = 0; k < NB_CL; ++k) D += *cluster.map_shared_rank(&xd[0], k);
+    cluster.sync();                          // nobody leaves while its shared memory may still be read
     if (dlogits) {
         float* dr = dlogits + (int64_t)r * lddl;
-        for (int c = tid; c < F; c += NB_T) {
+        for (int c = c0 + tid; c < c1; c += NB_T) {
             const double p = (double)expf(lr[c] - m) * inv_se;
             const double mu = L * p;
             double dmu = 0.0;
@@ -199,8 +229,21 @@ extern "C" int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x
                                 void* stream) {
     NC_REQUIRE(n_rows >= 0 && F > 0 && ldl >= F && ldx >= F, NC_ESHAPE, "nc_nb_loss_fused: bad shape rows=%d F=%d", n_rows, F);
     if (n_rows == 0) return NC_OK;
-    k_nb_fused<<<n_rows, NB_T, 0, (cudaStream_t)stream>>>(logits, ldl, x, ldx, sel, theta_param, F, scale, means, ldm,
-                                                         loss_sum, dlogits, lddl, dtheta);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)n_rows * NB_CL);
+    cfg.blockDim = dim3(NB_T);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = NB_CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, k_nb_fused, logits, ldl, x, ldx, sel, theta_param, (int)F, scale, means,
+                                        ldm, loss_sum, dlogits, lddl, dtheta);
+    if (le != cudaSuccess) { nc_set_error("nc_nb_loss_fused: launch failed: %s", cudaGetErrorString(le)); return NC_ECUDA; }
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_nb_loss_fused");
     return NC_OK;
