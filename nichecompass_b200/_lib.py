@@ -112,11 +112,19 @@ class HostPtr:
         self.t = t
 
 
-def stream():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
+def stream() -> int:
+    """cudaStream_t of torch's current stream on the current device (as an integer handle)."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device())
+    return torch.cuda.current_stream().cuda_stream
 
 
 _HOOK = None
+_FN = {}
+_Tensor = torch.Tensor
 
 
 def set_call_hook(hook):
@@ -126,23 +134,44 @@ def set_call_hook(hook):
     _HOOK = hook
 
 
+def _fail(name: str, rc: int):
+    msg = _lib.nc_last_error().decode()
+    if rc in (-1, -2):
+        raise ValueError(f"{name}: {msg}")
+    raise NicheCompassCudaError(f"{name} failed ({rc}): {msg}")
+
+
 def call(name: str, *args):
     """Call ``name`` with torch tensors (-> device pointers), None (-> NULL) or scalars; the
-    stream argument is appended automatically."""
-    fn = getattr(_load(), name)
-    conv = [ctypes.c_void_p(a.t.data_ptr()) if isinstance(a, HostPtr)
-            else (ptr(a) if (a is None or torch.is_tensor(a)) else a) for a in args]
+    stream argument is appended automatically.  This is the hot host path (~70 calls per
+    training step): tensors are converted with one ``data_ptr()`` each, ctypes ``argtypes`` do
+    the rest."""
+    fn = _FN.get(name)
+    if fn is None:
+        fn = _FN[name] = getattr(_load(), name)
+    conv = []
+    for a in args:
+        if isinstance(a, _Tensor):
+            if not a.is_cuda and not a.is_pinned():
+                # pinned host memory is device-addressable under UVA (host-resident count store)
+                raise NicheCompassCudaError("nichecompass_b200 kernels need CUDA tensors (no CPU fallback)")
+            conv.append(a.data_ptr())
+        elif isinstance(a, HostPtr):
+            conv.append(a.t.data_ptr())
+        else:
+            conv.append(a)
+    if _raw_stream is not None:
+        st = _raw_stream(torch.cuda.current_device())
+    else:
+        st = torch.cuda.current_stream().cuda_stream
     if _HOOK is not None:
         _HOOK.before(name, args)
-        rc = fn(*conv, stream())
+        rc = fn(*conv, st)
         _HOOK.after(name, args)
     else:
-        rc = fn(*conv, stream())
+        rc = fn(*conv, st)
     if rc != 0:
-        msg = _lib.nc_last_error().decode()
-        if rc in (-1, -2):
-            raise ValueError(f"{name}: {msg}")
-        raise NicheCompassCudaError(f"{name} failed ({rc}): {msg}")
+        _fail(name, rc)
 
 
 def launch_count() -> int:

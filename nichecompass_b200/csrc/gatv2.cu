@@ -131,6 +131,175 @@ k_gatv2_fwd(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, cons
     }
 }
 
+// ------------------------------------------------------------------------- forward, streaming (bf16)
+// One CTA per (target, conv).  Every neighbour's x_l segment of this conv (H*C contiguous bf16) is
+// pulled ONCE from HBM by a bulk async copy (cp.async.bulk -> mbarrier) into a 4-deep shared-memory
+// ring and consumed from there: score (LeakyReLU + att dot, reduced over the NT/H threads of a head),
+// online softmax (running max / sum with rescaling of the accumulators), alpha-weighted sum.
+// Thread t works for head t / (NT/H) and owns NV 4-element vectors of that head's C columns.
+constexpr int FS_NT = 256;
+constexpr int FS_STAGES = 4;
+
+__device__ __forceinline__ uint32_t fs_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void fs_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(fs_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fs_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fs_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void fs_mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "FS_WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra.uni FS_WAIT_DONE;\n\t"
+        "bra.uni FS_WAIT_LOOP;\n\t"
+        "FS_WAIT_DONE:\n\t"
+        "}" ::"r"(fs_smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fs_bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(fs_smem_u32(dst)), "l"(src), "r"(bytes), "r"(fs_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ float4 bf4_to_f4(uint2 r) {
+    float4 o;
+    o.x = __uint_as_float(r.x << 16);
+    o.y = __uint_as_float(r.x & 0xffff0000u);
+    o.z = __uint_as_float(r.y << 16);
+    o.w = __uint_as_float(r.y & 0xffff0000u);
+    return o;
+}
+
+template <int NV>
+__global__ void __launch_bounds__(FS_NT, 2)
+k_gatv2_fwd_stream(const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __restrict__ xr, int64_t ld,
+                   const float* __restrict__ att, const float* __restrict__ bias, const int32_t* __restrict__ rowptr,
+                   const int32_t* __restrict__ col, const int32_t* __restrict__ seg, int n_conv, int H, int max_deg,
+                   int seg_stride, float slope, float* __restrict__ out, int64_t ldo, float* __restrict__ alpha) {
+    extern __shared__ __align__(128) uint8_t fs_smem[];
+    const int stride = max_deg + 1;
+    uint8_t* ring = fs_smem;                                              // FS_STAGES * seg_stride bytes
+    float* s_e = (float*)(ring + (size_t)FS_STAGES * seg_stride);         // [H][stride] raw scores
+    int* s_j = (int*)(s_e + H * stride);                                  // [stride] compacted source ids
+    int* s_t = s_j + stride;                                              // [stride] their entry index
+    float* s_red = (float*)(s_t + stride);                                // [2][FS_NT/32]
+    uint64_t* full = (uint64_t*)(((uintptr_t)(s_red + 2 * (FS_NT / 32)) + 7) & ~(uintptr_t)7);
+    __shared__ int s_nv;
+
+    const int i = blockIdx.x, c = blockIdx.y;
+    const Seg sg = load_seg(seg, c);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int TPH = FS_NT / H, h = tid / TPH, lt = tid - h * TPH;         // TPH is a multiple of 32
+    const int WPH = TPH / 32;                                             // warps per head
+    const int e0 = rowptr[i], e1 = rowptr[i + 1];
+    const int nE = e1 - e0 + 1;
+    const int NCH = n_conv * H;
+    const int C4 = sg.C >> 2;
+    const uint32_t seg_bytes = (uint32_t)(H * sg.C * 2);
+
+    if (tid == 0) {
+        int n = 0;
+        for (int t = 0; t < nE; ++t) {
+            const int j = (t < nE - 1) ? col[e0 + t] : i;
+            if (t < nE - 1 && j == i) continue;                           // PyG removes existing self loops
+            s_j[n] = j; s_t[n] = t; ++n;
+        }
+        s_nv = n;
+        for (int s = 0; s < FS_STAGES; ++s) fs_mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int q = tid; q < H * stride; q += FS_NT) s_e[q] = -INFINITY;
+    __syncthreads();
+    const int nV = s_nv;
+    if (tid == 0) {
+        const int pre = nV < FS_STAGES ? nV : FS_STAGES;
+        for (int n = 0; n < pre; ++n) {
+            fs_mbar_expect_tx(&full[n], seg_bytes);
+            fs_bulk_load(ring + (size_t)n * seg_stride, xl + (int64_t)s_j[n] * ld + sg.off, seg_bytes, &full[n]);
+        }
+    }
+    // per-thread constants: x_r[i] and att of the owned vectors
+    float4 xr4[NV], at4[NV], acc[NV];
+    const __nv_bfloat16* xri = xr + (int64_t)i * ld + sg.off + h * sg.C;
+    const float* atth = att + sg.off + h * sg.C;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int u = lt + k * TPH;
+        acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (u < C4) {
+            xr4[k] = bf4_to_f4(__ldg(reinterpret_cast<const uint2*>(xri + 4 * u)));
+            at4[k] = __ldg(reinterpret_cast<const float4*>(atth + 4 * u));
+        } else {
+            xr4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            at4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    float m_run = -INFINITY, l_run = 0.f;
+    for (int it = 0; it < nV; ++it) {
+        const int s = it % FS_STAGES;
+        fs_mbar_wait(&full[s], (uint32_t)((it / FS_STAGES) & 1));
+        const uint8_t* row = ring + (size_t)s * seg_stride + (size_t)h * sg.C * 2;
+        float4 a[NV];
+        float p = 0.f;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int u = lt + k * TPH;
+            if (u < C4) {
+                a[k] = bf4_to_f4(*reinterpret_cast<const uint2*>(row + 8 * u));
+                p += at4[k].x * leaky_relu(a[k].x + xr4[k].x, slope) + at4[k].y * leaky_relu(a[k].y + xr4[k].y, slope) +
+                     at4[k].z * leaky_relu(a[k].z + xr4[k].z, slope) + at4[k].w * leaky_relu(a[k].w + xr4[k].w, slope);
+            } else {
+                a[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        p = warp_sum(p);
+        float* red = s_red + (it & 1) * (FS_NT / 32);
+        if (lane == 0) red[warp] = p;
+        __syncthreads();                       // scores visible; every thread has finished reading stage s
+        if (tid == 0 && it + FS_STAGES < nV) {
+            const int n = it + FS_STAGES;
+            fs_mbar_expect_tx(&full[s], seg_bytes);
+            fs_bulk_load(ring + (size_t)s * seg_stride, xl + (int64_t)s_j[n] * ld + sg.off, seg_bytes, &full[s]);
+        }
+        float e = 0.f;
+        for (int w = 0; w < WPH; ++w) e += red[h * WPH + w];
+        if (lt == 0) s_e[h * stride + s_t[it]] = e;
+        const float m_new = fmaxf(m_run, e);
+        const float corr = expf(m_run - m_new);          // 0 on the first neighbour (m_run = -inf)
+        const float wgt = expf(e - m_new);
+        l_run = l_run * corr + wgt;
+        m_run = m_new;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            acc[k].x = acc[k].x * corr + wgt * a[k].x;
+            acc[k].y = acc[k].y * corr + wgt * a[k].y;
+            acc[k].z = acc[k].z * corr + wgt * a[k].z;
+            acc[k].w = acc[k].w * corr + wgt * a[k].w;
+        }
+    }
+    __syncthreads();                           // s_e complete, ring free for the head-mean staging
+    const float inv_l = 1.0f / (l_run + 1e-16f);
+    // attention coefficients of every slot of this target (0 for the removed self entries)
+    for (int t = lt; t < nE; t += TPH)
+        alpha[(int64_t)(e0 + i + t) * NCH + c * H + h] = expf(s_e[h * stride + t] - m_run) * inv_l;
+    float* s_o = (float*)ring;                 // [H][C]
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int u = lt + k * TPH;
+        if (u < C4)
+            *reinterpret_cast<float4*>(s_o + h * sg.C + 4 * u) =
+                make_float4(acc[k].x * inv_l, acc[k].y * inv_l, acc[k].z * inv_l, acc[k].w * inv_l);
+    }
+    __syncthreads();
+    const float invH = 1.0f / (float)H;
+    for (int k = tid; k < sg.C; k += FS_NT) {
+        float v = 0.f;
+        for (int hh = 0; hh < H; ++hh) v += s_o[hh * sg.C + k];
+        out[(int64_t)i * ldo + sg.out_off + k] = v * invH + (bias ? __ldg(bias + sg.out_off + k) : 0.f);
+    }
+}
+
 // ------------------------------------------------------------------------- backward, per target
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(GT)
@@ -224,6 +393,179 @@ k_gatv2_bwd_dst(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, 
     }
 }
 
+// ------------------------------------------------------------------------- backward per target, streaming (bf16)
+// One CTA per (chunk of TCH consecutive targets, conv, head group of HG heads); 256 threads, two CTAs
+// per SM.  Every neighbour's segment of the head group is streamed ONCE through the shared-memory
+// ring; the softmax backward
+//   ds_t = alpha_t (dalpha_t - D),  D = sum_t alpha_t dalpha_t
+// is folded into running sums so no second pass over the rows is needed:
+//   d x_r = att * (A1 - D A2),  d att += B1 - D B2,
+//   A1 = sum_t alpha_t dalpha_t s'_t, A2 = sum_t alpha_t s'_t, B1/B2 the same with s'_t (x_l[t] + x_r),
+// s'_t = LeakyReLU'(x_l[t] + x_r).  d att is kept in registers over the chunk: one atomicAdd per
+// element and chunk.
+constexpr int BS_NT = 256;
+
+template <int NV>
+__global__ void __launch_bounds__(BS_NT, 2)
+k_gatv2_bwd_dst_stream(const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __restrict__ xr, int64_t ld,
+                       const float* __restrict__ att, const int32_t* __restrict__ rowptr,
+                       const int32_t* __restrict__ col, const int32_t* __restrict__ seg, int n_conv, int H, int HG,
+                       int TCH, int n_dst, int max_deg, int seg_stride, float slope,
+                       const float* __restrict__ dout, int64_t ldo, const float* __restrict__ alpha,
+                       float* __restrict__ ds, __nv_bfloat16* __restrict__ dxr, float* __restrict__ datt) {
+    extern __shared__ __align__(128) uint8_t fs_smem[];
+    const int stride = max_deg + 1;
+    uint8_t* ring = fs_smem;
+    float* s_al = (float*)(ring + (size_t)FS_STAGES * seg_stride);        // [HG][stride] alpha
+    float* s_da = s_al + HG * stride;                                     // [HG][stride] d alpha
+    int* s_j = (int*)(s_da + HG * stride);                                // compacted source ids
+    int* s_t = s_j + stride;                                              // their entry index
+    int* s_raw = s_t + stride;                                            // raw source ids of the row
+    float* s_red = (float*)(s_raw + stride);                              // [2][BS_NT/32]
+    uint64_t* full = (uint64_t*)(((uintptr_t)(s_red + 2 * (BS_NT / 32)) + 7) & ~(uintptr_t)7);
+    __shared__ int s_nv;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_hg = H / HG;
+    const int c = blockIdx.y / n_hg, hg = blockIdx.y - c * n_hg;
+    const Seg sg = load_seg(seg, c);
+    const int TPH = BS_NT / HG, hl = tid / TPH, lt = tid - hl * TPH;      // hl: head inside the group
+    const int h = hg * HG + hl;
+    const int WPH = TPH / 32;
+    const int NCH = n_conv * H;
+    const float invH = 1.0f / (float)H;
+    const int C4 = sg.C >> 2;
+    const uint32_t seg_bytes = (uint32_t)(HG * sg.C * 2);
+    const int64_t seg_off = (int64_t)sg.off + (int64_t)hg * HG * sg.C;    // first element of the group's segment
+    if (tid == 0) {
+        for (int s = 0; s < FS_STAGES; ++s) fs_mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    float4 at4[NV], dacc[NV];
+    const float* atth = att + sg.off + h * sg.C;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int u = lt + k * TPH;
+        at4[k] = (u < C4) ? __ldg(reinterpret_cast<const float4*>(atth + 4 * u)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        dacc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    uint32_t it_glob = 0;                      // ring position runs on across the targets of the chunk
+    const int i0 = blockIdx.x * TCH, i1 = min(n_dst, i0 + TCH);
+    for (int i = i0; i < i1; ++i) {
+        const int e0 = rowptr[i], e1 = rowptr[i + 1];
+        const int nE = e1 - e0 + 1;
+        __syncthreads();                       // previous target fully consumed; barrier init visible
+        for (int t = tid; t < nE; t += BS_NT) s_raw[t] = (t < nE - 1) ? col[e0 + t] : i;
+        for (int q = tid; q < nE * HG; q += BS_NT) {
+            const int t = q / HG, hh = q - t * HG;
+            s_al[hh * stride + t] = alpha[(int64_t)(e0 + i + t) * NCH + c * H + hg * HG + hh];
+            s_da[hh * stride + t] = 0.f;
+        }
+        float4 xr4[NV], g4[NV], A1[NV], A2[NV], B1[NV], B2[NV];
+        const __nv_bfloat16* xri = xr + (int64_t)i * ld + sg.off + h * sg.C;
+        const float* gi = dout + (int64_t)i * ldo + sg.out_off;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int u = lt + k * TPH;
+            A1[k] = A2[k] = B1[k] = B2[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (u < C4) {
+                xr4[k] = bf4_to_f4(__ldg(reinterpret_cast<const uint2*>(xri + 4 * u)));
+                g4[k] = __ldg(reinterpret_cast<const float4*>(gi + 4 * u));
+            } else {
+                xr4[k] = g4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int n = 0;
+            for (int t = 0; t < nE; ++t) {
+                const int j = s_raw[t];
+                if (t < nE - 1 && j == i) continue;          // PyG removes existing self loops
+                s_j[n] = j; s_t[n] = t; ++n;
+            }
+            s_nv = n;
+            const int pre = n < FS_STAGES ? n : FS_STAGES;
+            for (int q = 0; q < pre; ++q) {
+                const int s = (int)((it_glob + q) % FS_STAGES);
+                fs_mbar_expect_tx(&full[s], seg_bytes);
+                fs_bulk_load(ring + (size_t)s * seg_stride, xl + (int64_t)s_j[q] * ld + seg_off, seg_bytes, &full[s]);
+            }
+        }
+        __syncthreads();
+        const int nV = s_nv;
+        float D = 0.f;
+        for (int it = 0; it < nV; ++it, ++it_glob) {
+            const int s = (int)(it_glob % FS_STAGES);
+            fs_mbar_wait(&full[s], (it_glob / FS_STAGES) & 1);
+            const uint8_t* row = ring + (size_t)s * seg_stride + (size_t)hl * sg.C * 2;
+            float4 a[NV];
+            float p = 0.f;
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                const int u = lt + k * TPH;
+                if (u < C4) {
+                    a[k] = bf4_to_f4(*reinterpret_cast<const uint2*>(row + 8 * u));
+                    p += a[k].x * g4[k].x + a[k].y * g4[k].y + a[k].z * g4[k].z + a[k].w * g4[k].w;
+                } else {
+                    a[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            p = warp_sum(p);
+            float* red = s_red + (it_glob & 1) * (BS_NT / 32);
+            if (lane == 0) red[warp] = p;
+            __syncthreads();
+            if (tid == 0 && it + FS_STAGES < nV) {
+                const int n = it + FS_STAGES;
+                fs_mbar_expect_tx(&full[s], seg_bytes);
+                fs_bulk_load(ring + (size_t)s * seg_stride, xl + (int64_t)s_j[n] * ld + seg_off, seg_bytes, &full[s]);
+            }
+            float da = 0.f;
+            for (int w = 0; w < WPH; ++w) da += red[hl * WPH + w];
+            da *= invH;
+            const int t = s_t[it];
+            const float al = s_al[hl * stride + t];
+            if (lt == 0) s_da[hl * stride + t] = da;
+            const float w1a = al * da;
+            D += w1a;
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                float v, sp;
+                v = a[k].x + xr4[k].x; sp = v > 0.f ? 1.f : slope; A1[k].x += w1a * sp; A2[k].x += al * sp; B1[k].x += w1a * sp * v; B2[k].x += al * sp * v;
+                v = a[k].y + xr4[k].y; sp = v > 0.f ? 1.f : slope; A1[k].y += w1a * sp; A2[k].y += al * sp; B1[k].y += w1a * sp * v; B2[k].y += al * sp * v;
+                v = a[k].z + xr4[k].z; sp = v > 0.f ? 1.f : slope; A1[k].z += w1a * sp; A2[k].z += al * sp; B1[k].z += w1a * sp * v; B2[k].z += al * sp * v;
+                v = a[k].w + xr4[k].w; sp = v > 0.f ? 1.f : slope; A1[k].w += w1a * sp; A2[k].w += al * sp; B1[k].w += w1a * sp * v; B2[k].w += al * sp * v;
+            }
+        }
+        __nv_bfloat16* dxi = dxr + (int64_t)i * ld + sg.off + h * sg.C;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int u = lt + k * TPH;
+            if (u < C4) {
+                float4 r;
+                r.x = at4[k].x * (A1[k].x - D * A2[k].x); r.y = at4[k].y * (A1[k].y - D * A2[k].y);
+                r.z = at4[k].z * (A1[k].z - D * A2[k].z); r.w = at4[k].w * (A1[k].w - D * A2[k].w);
+                Elem<__nv_bfloat16>::st4(dxi + 4 * u, r);
+                dacc[k].x += B1[k].x - D * B2[k].x; dacc[k].y += B1[k].y - D * B2[k].y;
+                dacc[k].z += B1[k].z - D * B2[k].z; dacc[k].w += B1[k].w - D * B2[k].w;
+            }
+        }
+        __syncthreads();                       // s_da complete
+        for (int t = lt; t < nE; t += TPH) {
+            const float al = s_al[hl * stride + t];
+            ds[(int64_t)(e0 + i + t) * NCH + c * H + h] = al * (s_da[hl * stride + t] - D);
+        }
+    }
+    float* da = datt + sg.off + h * sg.C;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int u = lt + k * TPH;
+        if (u < C4) {
+            atomicAdd(da + 4 * u, dacc[k].x); atomicAdd(da + 4 * u + 1, dacc[k].y);
+            atomicAdd(da + 4 * u + 2, dacc[k].z); atomicAdd(da + 4 * u + 3, dacc[k].w);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------- backward, per source
 constexpr int SRC_STAGE = 64;
 template <typename T, bool VEC>
@@ -278,6 +620,15 @@ bool vec_ok(const void* a, const void* b, int64_t ld, const int32_t* seg_host, i
         if (seg_host[c * 4] % 4 != 0 || seg_host[c * 4 + 1] % 4 != 0) return false;
     return true;
 }
+// every conv's x_l segment can be fetched by cp.async.bulk: 16-byte aligned start, 16-byte multiple length,
+// and the head <-> thread mapping of the streaming kernels needs 32*H | 256
+bool stream_ok(const void* xl, int64_t ld, const int32_t* seg_host, int n_conv, int H) {
+    if ((uintptr_t)xl % 16 != 0 || ld % 8 != 0) return false;
+    if (!(H == 1 || H == 2 || H == 4 || H == 8)) return false;
+    for (int c = 0; c < n_conv; ++c)
+        if (seg_host[c * 4] % 8 != 0 || (H * seg_host[c * 4 + 1]) % 8 != 0) return false;
+    return true;
+}
 }  // namespace
 
 extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
@@ -293,6 +644,33 @@ extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t l
     cudaStream_t s = (cudaStream_t)stream;
     dim3 grid(n_dst, n_conv);
     const bool v = vec_ok(xl, xr, ld, seg_host, n_conv, dtype == NC_F32 ? 4 : 2) && ((uintptr_t)att % 16 == 0);
+    // streaming kernel: bf16 rows, every conv segment a legal bulk-copy source (16-byte aligned, 16-byte multiple)
+    if (dtype == NC_BF16 && v && stream_ok(xl, ld, seg_host, n_conv, H)) {
+        int maxC = 0;
+        for (int c = 0; c < n_conv; ++c) maxC = seg_host[c * 4 + 1] > maxC ? seg_host[c * 4 + 1] : maxC;
+        const int TPH = FS_NT / H;
+        const int nv = (maxC / 4 + TPH - 1) / TPH;
+        const int seg_stride = (H * maxC * 2 + 127) / 128 * 128;
+        const size_t sm = (size_t)FS_STAGES * seg_stride + ((size_t)H * (max_deg + 1) + 2 * (max_deg + 1) + 2 * (FS_NT / 32)) * 4 + 8 + FS_STAGES * 8;
+        if (nv <= 8 && sm <= 100 * 1024) {
+#define LS(NV)                                                                                                       \
+    do {                                                                                                             \
+        static bool attr_set = false;                                                                                \
+        if (!attr_set) {                                                                                             \
+            cudaFuncSetAttribute(k_gatv2_fwd_stream<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);   \
+            attr_set = true;                                                                                         \
+        }                                                                                                            \
+        k_gatv2_fwd_stream<NV><<<grid, FS_NT, sm, s>>>((const __nv_bfloat16*)xl, (const __nv_bfloat16*)xr, ld, att, \
+                                                       bias, rowptr, col, seg, n_conv, H, max_deg, seg_stride,       \
+                                                       neg_slope, out, ldo, alpha);                                  \
+    } while (0)
+            if (nv <= 2) LS(2); else if (nv <= 4) LS(4); else if (nv <= 6) LS(6); else LS(8);
+#undef LS
+            nc_count_launch(1);
+            NC_CHECK_LAUNCH("nc_gatv2_fwd");
+            return NC_OK;
+        }
+    }
 #define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, bias, rowptr, col, seg, n_conv, H, max_deg, neg_slope, out, ldo, alpha)
     if (dtype == NC_F32) { if (v) L(float, true); else L(float, false); }
     else { if (v) L(__nv_bfloat16, true); else L(__nv_bfloat16, false); }
@@ -318,6 +696,53 @@ extern "C" int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t l
     const bool v = vec_ok(xl, xr, ld, seg_host, n_conv, dtype == NC_F32 ? 4 : 2) && ((uintptr_t)att % 16 == 0) &&
                    ((uintptr_t)dxl % 16 == 0) && ((uintptr_t)dxr % 16 == 0);
     dim3 gd(n_dst, n_conv), gs(n_src, n_conv);
+    // streaming per-target kernel (bf16 rows, bulk-copyable segments); d bias = column sums of dout
+    const int HG = H >= 2 ? 2 : 1;
+    bool bs_ok = dtype == NC_BF16 && v && n_dst > 0 && stream_ok(xl, ld, seg_host, n_conv, H) && H % HG == 0 &&
+                 ldo % 4 == 0 && (uintptr_t)dout % 16 == 0;
+    for (int c = 0; c < n_conv && bs_ok; ++c)
+        bs_ok = (HG * seg_host[c * 4 + 1]) % 8 == 0 && seg_host[c * 4 + 2] % 4 == 0;
+    if (bs_ok) {
+        int maxC = 0;
+        for (int c = 0; c < n_conv; ++c) maxC = seg_host[c * 4 + 1] > maxC ? seg_host[c * 4 + 1] : maxC;
+        const int TPH = BS_NT / HG;
+        const int nv = (maxC / 4 + TPH - 1) / TPH;
+        const int seg_stride = (HG * maxC * 2 + 127) / 128 * 128;
+        const size_t sm = (size_t)FS_STAGES * seg_stride + ((size_t)2 * HG * (max_deg + 1) + 3 * (max_deg + 1) + 2 * (BS_NT / 32)) * 4 + 8 + FS_STAGES * 8;
+        if (nv <= 4 && sm <= 100 * 1024) {
+            const int TCH = n_dst >= 512 ? 4 : 1;
+            dim3 grid((unsigned)nc_cdiv(n_dst, TCH), (unsigned)(n_conv * (H / HG)));
+#define LBS(NV)                                                                                                      \
+    do {                                                                                                             \
+        static bool attr_set = false;                                                                                \
+        if (!attr_set) {                                                                                             \
+            cudaFuncSetAttribute(k_gatv2_bwd_dst_stream<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); \
+            attr_set = true;                                                                                         \
+        }                                                                                                            \
+        k_gatv2_bwd_dst_stream<NV><<<grid, BS_NT, sm, s>>>((const __nv_bfloat16*)xl, (const __nv_bfloat16*)xr, ld,  \
+            att, rowptr, col, seg, n_conv, H, HG, TCH, n_dst, max_deg, seg_stride, neg_slope, dout, ldo, alpha,      \
+            ds_ws, (__nv_bfloat16*)dxr, datt);                                                                       \
+    } while (0)
+            if (nv <= 1) LBS(1); else if (nv <= 2) LBS(2); else if (nv <= 3) LBS(3); else LBS(4);
+#undef LBS
+            nc_count_launch(1);
+            NC_CHECK_LAUNCH("nc_gatv2_bwd (dst)");
+            if (dbias) {
+                int ow = 0;
+                for (int c = 0; c < n_conv; ++c) {
+                    const int e = seg_host[c * 4 + 2] + seg_host[c * 4 + 1];
+                    ow = e > ow ? e : ow;
+                }
+                int rc = nc_col_sum(dout, NC_F32, ldo, n_dst, ow, dbias, stream);
+                if (rc) return rc;
+            }
+            k_gatv2_bwd_src<__nv_bfloat16, true><<<gs, GT, 0, s>>>((const __nv_bfloat16*)xl, (const __nv_bfloat16*)xr, ld,
+                att, rptr, rdst, rslot, seg, n_conv, H, neg_slope, dout, ldo, alpha, ds_ws, (__nv_bfloat16*)dxl);
+            nc_count_launch(1);
+            NC_CHECK_LAUNCH("nc_gatv2_bwd (src)");
+            return NC_OK;
+        }
+    }
 #define LD(T, V) if (n_dst > 0) k_gatv2_bwd_dst<T, V><<<gd, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, rowptr, col, seg, n_conv, H, max_deg, neg_slope, dout, ldo, alpha, ds_ws, (T*)dxr, datt, dbias)
 #define LS(T, V) k_gatv2_bwd_src<T, V><<<gs, GT, 0, s>>>((const T*)xl, (const T*)xr, ld, att, rptr, rdst, rslot, seg, n_conv, H, neg_slope, dout, ldo, alpha, ds_ws, (T*)dxl)
     if (dtype == NC_F32) { if (v) { LD(float, true); LS(float, true); } else { LD(float, false); LS(float, false); } }

@@ -481,43 +481,50 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
         nbl = node_model_output.get("_nb_loss")
         if nbl is None:
             raise RuntimeError("node_model_output was not produced by VGPGAE.forward(decoder='omics')")
-        L["gene_expr_recon_loss"] = lambda_gene_expr_recon * nbl["target_rna"]
-        L["gene_expr_recon_loss"] = L["gene_expr_recon_loss"] + lambda_gene_expr_recon * nbl["source_rna"]
+        L["gene_expr_recon_loss"] = lambda_gene_expr_recon * (nbl["target_rna"] + nbl["source_rna"])
         L["masked_gp_l1_reg_loss"] = lambda_l1_masked * compute_gp_l1_reg_loss(
             self, gp_type="prior", l1_targets_mask=l1_targets_mask, l1_sources_mask=l1_sources_mask) \
-            if lambda_l1_masked != 0 else torch.zeros((), device=self.device)
+            if lambda_l1_masked != 0 else self._zero_scalar()
         L["group_lasso_reg_loss"] = lambda_group_lasso * compute_gp_group_lasso_reg_loss(self) \
-            if lambda_group_lasso != 0 else torch.zeros((), device=self.device)
+            if lambda_group_lasso != 0 else self._zero_scalar()
         if self.n_addon_gp_ != 0:
             L["addon_gp_l1_reg_loss"] = lambda_l1_addon * compute_gp_l1_reg_loss(self, gp_type="addon") \
-                if lambda_l1_addon != 0 else torch.zeros((), device=self.device)
+                if lambda_l1_addon != 0 else self._zero_scalar()
         if "atac" in self.modalities_:
-            L["chrom_access_recon_loss"] = lambda_chrom_access_recon * nbl["target_atac"]
-            L["chrom_access_recon_loss"] = (L["chrom_access_recon_loss"]
-                                            + lambda_chrom_access_recon * nbl["source_atac"])
-        g = L["kl_reg_loss"]
-        o = L["kl_reg_loss"]
+            L["chrom_access_recon_loss"] = lambda_chrom_access_recon * (nbl["target_atac"] + nbl["source_atac"])
+        # global / optimisation loss: the reference's chain of additions (modules/vgpgae.py:1100-1143),
+        # evaluated as one stacked sum per loss (two small kernels instead of ~20)
+        g_terms, o_terms = [L["kl_reg_loss"]], [L["kl_reg_loss"]]
         if self.include_edge_recon_loss_:
-            g = g + L["edge_recon_loss"]
+            g_terms.append(L["edge_recon_loss"])
             if edge_recon_active:
-                o = o + L["edge_recon_loss"]
+                o_terms.append(L["edge_recon_loss"])
         if self.include_cat_covariates_contrastive_loss_ and "cat_covariates_contrastive_loss" in L:
-            g = g + L["cat_covariates_contrastive_loss"]
+            g_terms.append(L["cat_covariates_contrastive_loss"])
             if cat_covariates_contrastive_active:
-                o = o + L["cat_covariates_contrastive_loss"]
+                o_terms.append(L["cat_covariates_contrastive_loss"])
         if self.include_gene_expr_recon_loss_:
             for k in ("gene_expr_recon_loss", "group_lasso_reg_loss", "masked_gp_l1_reg_loss"):
-                g = g + L[k]
-                o = o + L[k]
+                g_terms.append(L[k])
+                o_terms.append(L[k])
             if self.n_addon_gp_ != 0:
-                g = g + L["addon_gp_l1_reg_loss"]
-                o = o + L["addon_gp_l1_reg_loss"]
+                g_terms.append(L["addon_gp_l1_reg_loss"])
+                o_terms.append(L["addon_gp_l1_reg_loss"])
         if ("atac" in self.modalities_) and self.include_chrom_access_recon_loss_:
-            g = g + L["chrom_access_recon_loss"]
-            o = o + L["chrom_access_recon_loss"]
+            g_terms.append(L["chrom_access_recon_loss"])
+            o_terms.append(L["chrom_access_recon_loss"])
+        o = torch.stack(o_terms).sum()
+        same = len(g_terms) == len(o_terms)
+        g = o if same else torch.stack(g_terms).sum()
         L["global_loss"] = g
         L["optim_loss"] = o
         return L
+
+    def _zero_scalar(self) -> torch.Tensor:
+        z = self._static_dev.get(("zero", self.device))
+        if z is None:
+            z = self._static_dev[("zero", self.device)] = torch.zeros((), device=self.device)
+        return z
 
     # ------------------------------------------------------------------ gp weights / active mask
     @torch.no_grad()
