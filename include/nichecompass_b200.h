@@ -118,6 +118,14 @@ int nc_gemm_bf16(const void* A, int64_t lda, int trans_a, const void* B, int64_t
                  int32_t K, const float* bias, int relu, const float* mask, int64_t ldmask,
                  int accumulate, void* stream);
 
+/* Weight gradient of a MaskedLinear whose mask is sparse (nn/layercomponents.py:77-80 backward):
+ * dW[f, p] += mval[e] * sum_b dlT[f, b] * zT[p, b] for every stored entry e = (f, p = mcol[e]) of
+ * the mask in CSR form by feature (mrowptr int32[F+1]); mval == NULL means 1.  dlT [F, nb] and
+ * zT [P, nb] are the transposed fp32 logit gradients / decoder inputs.  dW is ACCUMULATED.        */
+int nc_masked_sddmm(const float* dlT, int64_t lddl, const float* zT, int64_t ldz, int32_t nb,
+                    const int32_t* mrowptr, const int32_t* mcol, const float* mval, int32_t F,
+                    float* dW, int64_t lddw, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Fused GATv2 edge kernels (PyG GATv2Conv.forward message passing; nn/encoders.py:124-140,
  * 197-207): gather x_l[j] + x_r[i] -> LeakyReLU -> att dot -> segment

@@ -149,14 +149,16 @@ k_cosine_bwd(const float* __restrict__ z, int64_t ldz, int P, int n_pairs, const
     float* da = dz + (int64_t)warp * lddz;
     float* db = dz + (int64_t)(n_pairs + warp) * lddz;
     const float ra = norms[warp], rb = norms[n_pairs + warp];
-    const float na = fmaxf(ra, 1e-8f), nb = fmaxf(rb, 1e-8f);
+    const float ina = 1.0f / fmaxf(ra, 1e-8f), inb = 1.0f / fmaxf(rb, 1e-8f);
     const float g = dlogits[warp], cs = logits[warp];
     // a_hat = a / na.  If |a| > eps: d cos/da = (b_hat - cos * a_hat) / na, else b_hat / na.
-    const bool ca = ra > 1e-8f, cb = rb > 1e-8f;
+    const float ca = ra > 1e-8f ? cs : 0.f, cb = rb > 1e-8f ? cs : 0.f;
+    const float ga = g * ina, gb = g * inb;
+#pragma unroll 4
     for (int k = lane; k < P; k += 32) {
-        const float ah = a[k] / na, bh = b[k] / nb;
-        da[k] = g * (bh - (ca ? cs * ah : 0.f)) / na;
-        db[k] = g * (ah - (cb ? cs * bh : 0.f)) / nb;
+        const float ah = a[k] * ina, bh = b[k] * inb;
+        da[k] = ga * (bh - ca * ah);
+        db[k] = gb * (ah - cb * bh);
     }
 }
 

@@ -438,3 +438,54 @@ extern "C" int nc_dense_gather_rows(const float* x, int64_t ldx, int32_t n_cols,
     NC_CHECK_LAUNCH("nc_dense_gather_rows");
     return NC_OK;
 }
+
+// ------------------------------------------------------------------------- masked weight gradient (SDDMM)
+// dW[f, p] += mval * sum_b dlT[f, b] * zT[p, b] for the stored (f, p) of a sparse gene-program mask
+// (CSR by feature f).  Replaces the dense dlogits^T @ z followed by `* mask` of MaskedLinear's
+// backward (nn/layercomponents.py:77-80): gene-program masks connect 5..50 of several thousand genes
+// to a program, so only ~0.5 % of the [F, P] outer product is ever needed.  One warp per feature
+// row: its column of dlogits stays in registers, every non-zero costs one coalesced row of zT.
+namespace {
+constexpr int SD_MAXB = 8;      // 32 * SD_MAXB rows of the batch held in registers per pass
+__global__ void __launch_bounds__(128)
+k_masked_sddmm(const float* __restrict__ dlT, int64_t lddl, const float* __restrict__ zT, int64_t ldz, int nb,
+               const int32_t* __restrict__ mrowptr, const int32_t* __restrict__ mcol, const float* __restrict__ mval,
+               int F, float* __restrict__ dW, int64_t lddw) {
+    const int f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (f >= F) return;
+    const int p0 = mrowptr[f], p1 = mrowptr[f + 1];
+    if (p0 == p1) return;
+    const float* dr = dlT + (int64_t)f * lddl;
+    for (int b0 = 0; b0 < nb; b0 += 32 * SD_MAXB) {
+        float d[SD_MAXB];
+#pragma unroll
+        for (int q = 0; q < SD_MAXB; ++q) {
+            const int b = b0 + q * 32 + lane;
+            d[q] = b < nb ? __ldg(dr + b) : 0.f;
+        }
+        for (int e = p0; e < p1; ++e) {
+            const float* zr = zT + (int64_t)mcol[e] * ldz;
+            float acc = 0.f;
+#pragma unroll
+            for (int q = 0; q < SD_MAXB; ++q) {
+                const int b = b0 + q * 32 + lane;
+                if (b < nb) acc += d[q] * __ldg(zr + b);
+            }
+            acc = warp_sum(acc);
+            if (lane == 0) dW[(int64_t)f * lddw + mcol[e]] += (mval ? mval[e] : 1.f) * acc;
+        }
+    }
+}
+}  // namespace
+
+extern "C" int nc_masked_sddmm(const float* dlT, int64_t lddl, const float* zT, int64_t ldz, int32_t nb,
+                               const int32_t* mrowptr, const int32_t* mcol, const float* mval, int32_t F,
+                               float* dW, int64_t lddw, void* stream) {
+    NC_REQUIRE(nb >= 0 && F >= 0 && lddl >= nb && ldz >= nb, NC_ESHAPE, "nc_masked_sddmm: bad shape nb=%d F=%d", nb, F);
+    if (nb == 0 || F == 0) return NC_OK;
+    k_masked_sddmm<<<(unsigned)nc_cdiv(F, 4), 128, 0, (cudaStream_t)stream>>>(dlT, lddl, zT, ldz, nb, mrowptr, mcol, mval,
+                                                                            F, dW, lddw);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_masked_sddmm");
+    return NC_OK;
+}

@@ -471,6 +471,38 @@ def pack_decoder_weight(key, params, masks, dtype, offs, Kp) -> torch.Tensor:
     return buf
 
 
+_MASK_INFO = {}
+
+
+def mask_info(mask: Optional[torch.Tensor]):
+    """Structure of a MaskedLinear mask [F, P] (cached per tensor version; one host read-back when a
+    mask is first seen): ("none",) for an absent / all-ones mask, ("sparse", rowptr, col, val) with the
+    CSR-by-feature form when fewer than 10 % of the entries are set, else ("dense",)."""
+    if mask is None:
+        return ("none",)
+    key = (mask.data_ptr(), mask._version, tuple(mask.shape))
+    hit = _MASK_INFO.get(key)
+    if hit is not None:
+        return hit
+    if len(_MASK_INFO) > 64:
+        _MASK_INFO.clear()
+    with torch.no_grad():
+        nz = mask != 0
+        nnz = int(nz.sum())
+        if nnz == mask.numel() and bool((mask == 1).all()):
+            info = ("none",)
+        elif nnz < 0.1 * mask.numel():
+            idx = nz.nonzero()                                    # row-major: sorted by feature, then program
+            rowptr = torch.zeros(mask.size(0) + 1, dtype=torch.int32, device=mask.device)
+            rowptr[1:] = torch.cumsum(torch.bincount(idx[:, 0], minlength=mask.size(0)), 0)
+            info = ("sparse", rowptr, idx[:, 1].to(torch.int32).contiguous(),
+                    mask[idx[:, 0], idx[:, 1]].float().contiguous())
+        else:
+            info = ("dense",)
+    _MASK_INFO[key] = info
+    return info
+
+
 class MaskedDecoderFn(torch.autograd.Function):
     """logits = cat(z, embed) @ (W * mask)^T for the decoder weight blocks
     [F, P_prior | P_addon | n_embed] (nn/layers.py:83-142, nn/layercomponents.py:53-81) as ONE
@@ -519,15 +551,27 @@ class MaskedDecoderFn(torch.autograd.Function):
         dzp = ops.gemm(dl, Wp, trans_b=True, out_dtype=torch.float32, M=nb, N=Kp, K=F)
         dz = dzp[:, :widths[0]] if n == 1 else torch.cat([dzp[:, o:o + w] for w, o in zip(widths, offs)], dim=1)
         grads = []
+        dlT = None
         for i, (w, o) in enumerate(zip(widths, offs)):
             m = saved_masks.pop(0) if has_mask[i] else None
             if not ctx.needs_input_grad[4 + i]:
                 grads.append(None)
                 continue
-            ldm = m.stride(0) if m is not None else 0
+            info = mask_info(m)
+            if info[0] == "none":
+                m = None
             zb = za[:, o:o + pad8(w)]
             g = grad_view([ctx.params[i]], [True]) if w % 4 == 0 else None
-            if g is not None:
+            if info[0] == "sparse":
+                # gene-program masks are ~0.5 % dense: only the connected (feature, program) pairs
+                if dlT is None:
+                    dlT = dlogits.float().t().contiguous()                       # [F, nb]
+                zT = zb[:, :w].float().t().contiguous()                           # [w, nb]
+                dst = g.view(F, w) if g is not None else torch.zeros(F, w, dtype=torch.float32, device=za.device)
+                call("nc_masked_sddmm", dlT, dlT.stride(0), zT, zT.stride(0), nb, info[1], info[2], info[3], F,
+                     dst, dst.stride(0))
+                grads.append(None if g is not None else dst)
+            elif g is not None:
                 ops.gemm(dl, zb, trans_a=True, trans_b=True, out=g.view(F, w), mask=m, accumulate=True, M=F, N=w, K=nb)
                 grads.append(None)
             else:

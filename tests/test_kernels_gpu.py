@@ -4,6 +4,7 @@ import pytest
 import torch
 
 from nichecompass_b200 import ops
+from nichecompass_b200._lib import call
 from nichecompass_b200.data.store import CSRFeatureStore
 from oracle import pyg_semantics as S
 from oracle import sampler_ref as R
@@ -152,3 +153,24 @@ def test_gemm_bf16_large_persistent():
     out = ops.gemm(A, B, out_dtype=torch.float32)
     ref = A.float() @ B.float().t()          # torch fp32 reference of the same op
     assert H.rel_err(out, ref) < 1e-4
+
+
+@pytest.mark.parametrize("nb", [64, 300])
+def test_masked_sddmm_matches_dense(nb):
+    """Sparse-mask weight gradient == (dlogits^T @ z) * mask of MaskedLinear's backward."""
+    from nichecompass_b200.functional import mask_info
+    g = torch.Generator().manual_seed(4)
+    F, P = 500, 96
+    mask = (torch.rand(F, P, generator=g) < 0.03).float().to(DEV)
+    mask[7] = 0                                              # an empty feature row
+    dl = torch.randn(nb, F, generator=g).to(DEV)
+    z = torch.randn(nb, P, generator=g).to(DEV)
+    info = mask_info(mask)
+    assert info[0] == "sparse"
+    dW = torch.full((F, P), 0.5, device=DEV)                 # accumulates
+    dlT, zT = dl.t().contiguous(), z.t().contiguous()
+    call("nc_masked_sddmm", dlT, dlT.stride(0), zT, zT.stride(0), nb, info[1], info[2], info[3], F, dW, dW.stride(0))
+    ref = 0.5 + (dl.double().t() @ z.double()) * mask.double()
+    assert H.rel_err(dW, ref) < 1e-5
+    assert mask_info(torch.ones(4, 4, device=DEV))[0] == "none"
+    assert mask_info((torch.rand(50, 50, generator=g) < 0.5).float().to(DEV))[0] == "dense"
