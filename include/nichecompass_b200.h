@@ -163,8 +163,7 @@ int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t ld, const fl
  * modules/vgpgae.py:714-749 column selection + library size over selected columns,
  * modules/losses.py:169-212 NB log-likelihood, theta = exp(theta_param)).
  * logits [n_rows, ldl], x [n_rows, ldx] raw labels over all F features, sel[F] != 0 marks the
- * reconstructed columns.  loss_sum += sum_rows sum_sel -ll (fp64; the caller multiplies by
- * `scale` = lambda / n_rows); dlogits = scale * d(sum -ll)/dlogits; dtheta += scale * ...;
+ * reconstructed columns.  loss_sum += scale * sum_rows sum_sel -ll (fp64; `scale` = lambda / n_rows); dlogits = scale * d(sum -ll)/dlogits; dtheta += scale * ...;
  * means (nullable) receives exp(log_lib)*softmax over all F columns.                       */
 int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x, int64_t ldx,
                      const uint8_t* sel, const float* theta_param, int32_t n_rows, int32_t F,
@@ -215,10 +214,11 @@ int nc_abs_mean_ema(const float* mu, int64_t ldmu, int32_t R, int32_t P, float m
 int nc_weight_col_stats(const float* W, int64_t ld, int32_t F, int32_t P, const uint8_t* l1mask,
                         const float* mask, int64_t ldmask, float* abs_sum, float* sq_sum,
                         float* nnz, float* mask_cnt, void* stream);
-/* dW += l1_scale * sign(W) * l1mask + gl_coef[c] * W                                        */
+/* dW += gscale * (l1_scale * sign(W) * l1mask + gl_coef[c] * W); gscale: device scalar (the
+ * upstream gradient of the loss term), NULL means 1.                                          */
 int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t P, float l1_scale,
-                       const uint8_t* l1mask, const float* gl_coef, float* dW, int64_t lddw,
-                       void* stream);
+                       const uint8_t* l1mask, const float* gl_coef, const float* gscale, float* dW,
+                       int64_t lddw, void* stream);
 
 /* Fused Adam over a flat parameter segment with torch.optim.Adam semantics
  * (train/trainer.py:339-342,418-421): optional clip_grad_value_ (clip_value > 0), optional

@@ -94,7 +94,7 @@ k_nb_fused(const float* __restrict__ logits, int64_t ldl, const float* __restric
     }
     loss = block_sum_d(loss, redd);
     D = block_sum_d(D, redd);
-    if (tid == 0) { atomicAdd(loss_sum, loss); xd[0] = D; }
+    if (tid == 0) { atomicAdd(loss_sum, loss * (double)scale); xd[0] = D; }
     cluster.sync();
     D = 0.0;
 #pragma unroll

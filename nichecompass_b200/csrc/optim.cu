@@ -110,15 +110,16 @@ k_col_stats(const float* __restrict__ W, int64_t ld, int F, int P, const uint8_t
 // dW += l1_scale * sign(W) * l1mask + gl_coef[c] * W   (gl_coef[c] = lambda * sqrt(cnt_c) / ||W[:,c]||, 0 if norm 0)
 __global__ void k_reg_grad(const float* __restrict__ W, int64_t ld, int F, int P, float l1_scale,
                            const uint8_t* __restrict__ l1mask, const float* __restrict__ gl_coef,
-                           float* __restrict__ dW, int64_t lddw) {
+                           const float* __restrict__ gscale, float* __restrict__ dW, int64_t lddw) {
     const int64_t total = (int64_t)F * P;
+    const float gs = gscale ? __ldg(gscale) : 1.f;
     for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
         const int f = (int)(q / P), c = (int)(q % P);
         const float w = W[(int64_t)f * ld + c];
         float g = 0.f;
         if (l1_scale != 0.f && (!l1mask || l1mask[q])) g += l1_scale * (w > 0.f ? 1.f : (w < 0.f ? -1.f : 0.f));
         if (gl_coef) g += gl_coef[c] * w;
-        dW[(int64_t)f * lddw + c] += g;
+        dW[(int64_t)f * lddw + c] += gs * g;
     }
 }
 
@@ -184,6 +185,31 @@ __global__ void k_cast_bf16(const float* __restrict__ src, int64_t lds, const fl
             if (mask) v *= mask[(int64_t)r * ldm + c];
         }
         dst[(int64_t)r * ldd + c] = __float2bfloat16_rn(v);
+    }
+}
+// 4 columns per thread, grid.y tiles rows (all pitches multiples of 4, 16 / 8-byte aligned bases)
+__global__ void __launch_bounds__(256)
+k_cast_bf16_v4(const float* __restrict__ src, int64_t lds, const float* __restrict__ mask, int64_t ldm,
+               int R, int C, __nv_bfloat16* __restrict__ dst, int64_t ldd, int W) {
+    const int nv = W >> 2;
+    for (int r = blockIdx.y; r < R; r += gridDim.y) {
+        for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += gridDim.x * blockDim.x) {
+            const int c = v * 4;
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c + 3 < C) {
+                o = __ldg(reinterpret_cast<const float4*>(src + (int64_t)r * lds + c));
+                if (mask) {
+                    const float4 m = __ldg(reinterpret_cast<const float4*>(mask + (int64_t)r * ldm + c));
+                    o.x *= m.x; o.y *= m.y; o.z *= m.z; o.w *= m.w;
+                }
+            } else {
+                float t[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int k = 0; k < 4; ++k)
+                    if (c + k < C) t[k] = src[(int64_t)r * lds + c + k] * (mask ? mask[(int64_t)r * ldm + c + k] : 1.f);
+                o = make_float4(t[0], t[1], t[2], t[3]);
+            }
+            Elem<__nv_bfloat16>::st4(dst + (int64_t)r * ldd + c, o);
+        }
     }
 }
 }  // namespace
@@ -253,9 +279,10 @@ extern "C" int nc_weight_col_stats(const float* W, int64_t ld, int32_t F, int32_
 }
 
 extern "C" int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t P, float l1_scale,
-                                  const uint8_t* l1mask, const float* gl_coef, float* dW, int64_t lddw, void* stream) {
+                                  const uint8_t* l1mask, const float* gl_coef, const float* gscale, float* dW,
+                                  int64_t lddw, void* stream) {
     NC_REQUIRE(F > 0 && P > 0 && ld >= P && lddw >= P, NC_ESHAPE, "nc_weight_reg_grad: bad shape");
-    k_reg_grad<<<grid_for((int64_t)F * P), 256, 0, (cudaStream_t)stream>>>(W, ld, F, P, l1_scale, l1mask, gl_coef, dW, lddw);
+    k_reg_grad<<<grid_for((int64_t)F * P), 256, 0, (cudaStream_t)stream>>>(W, ld, F, P, l1_scale, l1mask, gl_coef, gscale, dW, lddw);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_weight_reg_grad");
     return NC_OK;
@@ -283,6 +310,16 @@ extern "C" int nc_cast_bf16(const float* src, int64_t lds, const float* mask, in
     if (fill_cols <= 0) fill_cols = (int32_t)ldd;
     NC_REQUIRE(R >= 0 && C > 0 && lds >= C && fill_cols >= C && ldd >= fill_cols, NC_ESHAPE, "nc_cast_bf16: bad shape");
     if (R == 0) return NC_OK;
+    if (R > 1 && lds % 4 == 0 && (!mask || (ldmask % 4 == 0 && (uintptr_t)mask % 16 == 0)) && ldd % 4 == 0 &&
+        fill_cols % 4 == 0 && (uintptr_t)src % 16 == 0 && (uintptr_t)dst % 8 == 0) {
+        dim3 grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(nc_cdiv(fill_cols / 4, 256), 8)),
+                  (unsigned)std::min<int64_t>(R, 2048));
+        k_cast_bf16_v4<<<grid, 256, 0, (cudaStream_t)stream>>>(src, lds, mask, ldmask, R, C, (__nv_bfloat16*)dst, ldd,
+                                                               fill_cols);
+        nc_count_launch(1);
+        NC_CHECK_LAUNCH("nc_cast_bf16");
+        return NC_OK;
+    }
     k_cast_bf16<<<grid_for((int64_t)R * fill_cols), 256, 0, (cudaStream_t)stream>>>(src, lds, mask, ldmask, R, C,
                                                                                    (__nv_bfloat16*)dst, ldd, fill_cols);
     nc_count_launch(1);
@@ -314,6 +351,35 @@ k_col_sum(const T* __restrict__ x, int64_t ld, int R, int C, float* __restrict__
     }
 }
 
+// 4 columns per thread (8 / 16-byte loads), 8 row groups per CTA, one atomicAdd per column and CTA
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_col_sum_v4(const T* __restrict__ x, int64_t ld, int R, int C, float* __restrict__ out) {
+    __shared__ float4 s[8][32];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c = (blockIdx.x * 32 + tx) * 4;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (c < C) {
+        const int rows_per = (R + gridDim.y - 1) / gridDim.y;
+        const int r0 = blockIdx.y * rows_per, r1 = min(R, r0 + rows_per);
+#pragma unroll 4
+        for (int r = r0 + ty; r < r1; r += 8) {
+            const float4 v = Elem<T>::ld4(x + (int64_t)r * ld + c);
+            a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+        }
+    }
+    s[ty][tx] = a;
+    __syncthreads();
+    if (ty == 0 && c < C) {
+        float4 t = s[0][tx];
+        for (int k = 1; k < 8; ++k) { t.x += s[k][tx].x; t.y += s[k][tx].y; t.z += s[k][tx].z; t.w += s[k][tx].w; }
+        atomicAdd(out + c, t.x);
+        if (c + 1 < C) atomicAdd(out + c + 1, t.y);
+        if (c + 2 < C) atomicAdd(out + c + 2, t.z);
+        if (c + 3 < C) atomicAdd(out + c + 3, t.w);
+    }
+}
+
 // out = dh * (h > 0), cast to T; pad columns [C, ldo) are zeroed
 template <typename T>
 __global__ void k_relu_bwd(const float* __restrict__ dh, int64_t lddh, const T* __restrict__ h, int64_t ldh, int R,
@@ -326,11 +392,51 @@ __global__ void k_relu_bwd(const float* __restrict__ dh, int64_t lddh, const T* 
         Elem<T>::st(out + q, v);
     }
 }
+
+// same, 4 columns per thread (all row pitches multiples of 4, 16-byte aligned bases, C % 4 == 0 or ld padding
+// readable): grid.y tiles rows
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_relu_bwd_v4(const float* __restrict__ dh, int64_t lddh, const T* __restrict__ h, int64_t ldh, int R, int C,
+              T* __restrict__ out, int64_t ldo) {
+    const int nv = (int)(ldo >> 2);
+    for (int r = blockIdx.y; r < R; r += gridDim.y) {
+        for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < nv; v += gridDim.x * blockDim.x) {
+            const int c = v * 4;
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c + 3 < C) {
+                const float4 hv = Elem<T>::ld4(h + (int64_t)r * ldh + c);
+                const float4 d = __ldg(reinterpret_cast<const float4*>(dh + (int64_t)r * lddh + c));
+                o.x = hv.x > 0.f ? d.x : 0.f; o.y = hv.y > 0.f ? d.y : 0.f;
+                o.z = hv.z > 0.f ? d.z : 0.f; o.w = hv.w > 0.f ? d.w : 0.f;
+            } else {
+                float t[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int k = 0; k < 4; ++k)
+                    if (c + k < C && Elem<T>::ld(h + (int64_t)r * ldh + c + k) > 0.f) t[k] = dh[(int64_t)r * lddh + c + k];
+                o = make_float4(t[0], t[1], t[2], t[3]);
+            }
+            Elem<T>::st4(out + (int64_t)r * ldo + c, o);
+        }
+    }
+}
 }  // namespace
 
 extern "C" int nc_col_sum(const void* x, int dtype, int64_t ld, int32_t R, int32_t C, float* out, void* stream) {
     NC_REQUIRE(R >= 0 && C > 0 && ld >= C, NC_ESHAPE, "nc_col_sum: bad shape");
     if (R == 0) return NC_OK;
+    NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_col_sum: bad dtype %d", dtype);
+    const size_t esz = dtype == NC_F32 ? 4 : 2;
+    if (ld % 4 == 0 && (uintptr_t)x % (4 * esz) == 0 && C >= 64) {
+        const unsigned gx = (unsigned)nc_cdiv(C, 128);
+        int64_t gy = nc_cdiv(4 * (int64_t)nc_num_sms(), gx);
+        gy = std::max<int64_t>(1, std::min<int64_t>(gy, nc_cdiv(R, 32)));
+        dim3 grid(gx, (unsigned)gy);
+        if (dtype == NC_F32) k_col_sum_v4<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, ld, R, C, out);
+        else k_col_sum_v4<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ld, R, C, out);
+        nc_count_launch(1);
+        NC_CHECK_LAUNCH("nc_col_sum");
+        return NC_OK;
+    }
     dim3 grid((unsigned)nc_cdiv(C, 32), (unsigned)std::min<int64_t>(nc_cdiv(R, 64), 128));
     if (dtype == NC_F32) k_col_sum<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, ld, R, C, out);
     else if (dtype == NC_BF16) k_col_sum<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ld, R, C, out);
@@ -344,6 +450,18 @@ extern "C" int nc_relu_bwd(const float* dh, int64_t lddh, const void* h, int dty
                            void* out, int64_t ldo, void* stream) {
     NC_REQUIRE(R >= 0 && C > 0 && lddh >= C && ldh >= C && ldo >= C, NC_ESHAPE, "nc_relu_bwd: bad shape");
     if (R == 0) return NC_OK;
+    NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_relu_bwd: bad dtype %d", dtype);
+    const size_t esz = dtype == NC_F32 ? 4 : 2;
+    if (lddh % 4 == 0 && ldh % 4 == 0 && ldo % 4 == 0 && (uintptr_t)dh % 16 == 0 && (uintptr_t)h % (4 * esz) == 0 &&
+        (uintptr_t)out % (4 * esz) == 0) {
+        dim3 grid((unsigned)std::max<int64_t>(1, std::min<int64_t>(nc_cdiv(ldo / 4, 256), 8)),
+                  (unsigned)std::min<int64_t>(R, 2048));
+        if (dtype == NC_F32) k_relu_bwd_v4<float><<<grid, 256, 0, (cudaStream_t)stream>>>(dh, lddh, (const float*)h, ldh, R, C, (float*)out, ldo);
+        else k_relu_bwd_v4<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(dh, lddh, (const __nv_bfloat16*)h, ldh, R, C, (__nv_bfloat16*)out, ldo);
+        nc_count_launch(1);
+        NC_CHECK_LAUNCH("nc_relu_bwd");
+        return NC_OK;
+    }
     const int g = grid_for((int64_t)R * ldo);
     if (dtype == NC_F32) k_relu_bwd<float><<<g, 256, 0, (cudaStream_t)stream>>>(dh, lddh, (const float*)h, ldh, R, C, (float*)out, ldo);
     else if (dtype == NC_BF16) k_relu_bwd<__nv_bfloat16><<<g, 256, 0, (cudaStream_t)stream>>>(dh, lddh, (const __nv_bfloat16*)h, ldh, R, C, (__nv_bfloat16*)out, ldo);

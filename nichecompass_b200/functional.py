@@ -351,6 +351,28 @@ class GatherRowsFn(torch.autograd.Function):
         return dsrc, None
 
 
+class SplitLatentFn(torch.autograd.Function):
+    """(mu | logstd) [R, 2P] -> mu, logstd views.  Autograd's own slicing would materialise two
+    zero-filled [R, 2P] gradients and add them; here the backward is one concatenation."""
+
+    @staticmethod
+    def forward(ctx, ml, P):
+        ctx.P, ctx.shape = P, tuple(ml.shape)
+        return ml[:, :P], ml[:, P:]
+
+    @staticmethod
+    def backward(ctx, dmu, dls):
+        R, W = ctx.shape
+        if dmu is None and dls is None:
+            return None, None
+        ref = dmu if dmu is not None else dls
+        if dmu is None:
+            dmu = ref.new_zeros(R, ctx.P)
+        if dls is None:
+            dls = ref.new_zeros(R, W - ctx.P)
+        return torch.cat((dmu, dls), dim=1), None
+
+
 class ReparamFn(torch.autograd.Function):
     """z = (mu + eps * exp(logstd)) with inactive gene programs zeroed
     (modules/vgaemodulemixin.py:34-41, modules/vgpgae.py:632-637)."""
@@ -412,7 +434,7 @@ class CosineFn(torch.autograd.Function):
     def backward(ctx, dlogits):
         z, logits, norms = ctx.saved_tensors
         n = z.size(0) // 2
-        dz = torch.zeros_like(z)
+        dz = torch.empty_like(z)
         call("nc_cosine_bwd", z, z.stride(0), z.size(1), n, logits, norms, dlogits.contiguous(), dz, dz.stride(0))
         return dz
 
@@ -472,6 +494,7 @@ def pack_decoder_weight(key, params, masks, dtype, offs, Kp) -> torch.Tensor:
 
 
 _MASK_INFO = {}
+_ZA_CACHE = {}
 
 
 def mask_info(mask: Optional[torch.Tensor]):
@@ -525,11 +548,17 @@ class MaskedDecoderFn(torch.autograd.Function):
         Wp = pack_decoder_weight(cache_key, params, eff_masks, act_dtype, offs, Kp)
         F = params[0].size(0)
         nb = zcat.size(0)
-        za = torch.zeros(nb, Kp, dtype=act_dtype, device=zcat.device)
-        zd, c = zcat.detach(), 0
-        for w, o in zip(widths, offs):
-            za[:, o:o + w] = zd[:, c:c + w]
-            c += w
+        # the target and the source decoder contract the same z: pack it once
+        zkey = (zcat.data_ptr(), zcat._version, act_dtype, tuple(widths), tuple(zcat.shape))
+        if _ZA_CACHE.get("key") == zkey:
+            za = _ZA_CACHE["za"]
+        else:
+            za = torch.zeros(nb, Kp, dtype=act_dtype, device=zcat.device)
+            zd, c = zcat.detach(), 0
+            for w, o in zip(widths, offs):
+                za[:, o:o + w] = zd[:, c:c + w]
+                c += w
+            _ZA_CACHE.update(key=zkey, za=za, src=zcat)           # `src` keeps the pointer from being recycled
         logits = ops.gemm(za, Wp, out_dtype=torch.float32, M=nb, N=F, K=Kp)
         ctx.save_for_backward(za, Wp, *[m for m in eff_masks if m is not None])
         ctx.meta = (F, widths, offs, Kp, [m is not None for m in eff_masks], act_dtype)
@@ -598,7 +627,7 @@ class NBLossFusedFn(torch.autograd.Function):
              nb, F, 1.0 / nb, means, F, acc, dlog, F, dth)
         ctx.save_for_backward(dlog, dth)
         ctx.mark_non_differentiable(means)
-        return (acc / nb).float().reshape(()), means
+        return acc.float().reshape(()), means
 
     @staticmethod
     def backward(ctx, g, _gm):
@@ -637,18 +666,24 @@ class WeightRegFn(torch.autograd.Function):
         ctx.l1_scale = l1_scale
         ctx.l1masks = l1masks
         ctx.coefs = coefs
+        ctx.params = weights
         ctx.save_for_backward(*weights)
         return total
 
     @staticmethod
     def backward(ctx, g):
         grads = []
-        for W, lm, coef in zip(ctx.saved_tensors, ctx.l1masks, ctx.coefs):
-            dW = torch.zeros_like(W, dtype=torch.float32)
+        gs = g.detach().float().contiguous()
+        for i, (W, lm, coef) in enumerate(zip(ctx.saved_tensors, ctx.l1masks, ctx.coefs)):
+            if not ctx.needs_input_grad[4 + i]:
+                grads.append(None)
+                continue
             Wd = W.detach()
-            call("nc_weight_reg_grad", Wd, Wd.stride(0), W.size(0), W.size(1), float(ctx.l1_scale), lm, coef,
+            gv = grad_view([ctx.params[i]], [True])
+            dW = gv.view_as(W) if gv is not None else torch.zeros_like(W, dtype=torch.float32)
+            call("nc_weight_reg_grad", Wd, Wd.stride(0), W.size(0), W.size(1), float(ctx.l1_scale), lm, coef, gs,
                  dW, dW.stride(0))
-            grads.append(dW * g)
+            grads.append(None if gv is not None else dW)
         return (None, None, None, None, *grads)
 
 

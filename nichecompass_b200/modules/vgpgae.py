@@ -20,7 +20,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
-from ..functional import GatherRowsFn, ReparamFn, SubgraphCSR
+from ..functional import GatherRowsFn, ReparamFn, SplitLatentFn, SubgraphCSR
 from .._lib import call
 from ..nn import (CosineSimGraphDecoder, Encoder, MaskedOmicsFeatureDecoder,
                   OneHopAttentionNodeLabelAggregator, OneHopGCNNormNodeLabelAggregator,
@@ -356,7 +356,7 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
             ml = GatherRowsFn.apply(ml_u, batch_rows)
         else:
             raise ValueError(f"unknown decoder {decoder}")
-        self.mu, self.logstd = ml[:, :P], ml[:, P:]
+        self.mu, self.logstd = SplitLatentFn.apply(ml, P) if ml.requires_grad else (ml[:, :P], ml[:, P:])
         output = {"mu": self.mu, "logstd": self.logstd}
         active = self.get_active_gp_mask() if use_only_active_gps else None
         active_u8 = active.to(torch.uint8) if active is not None else None
