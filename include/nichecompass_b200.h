@@ -55,8 +55,9 @@ int nc_gcn_norm_weights(const int32_t* rowptr, const int32_t* col, int32_t n_nod
                         int32_t n_rows, int use_out_degree, int32_t* deg_ws, float* w,
                         float* wself, void* stream);
 
-/* Reverse (by-source) view of the first n_rows rows of a dst-CSR, self entries dropped and
- * one self edge i->i appended for every i < n_rows when add_self != 0.
+/* Reverse (by-source) view of the first n_rows rows of a dst-CSR.  add_self == 1: self entries
+ * dropped and one self edge i->i appended for every i < n_rows (GATv2Conv); 0: self entries
+ * dropped; 2: every entry kept as given, nothing appended (attention aggregator).
  * rptr[n_nodes+1], rdst[*], rslot[*]: target row and "slot" of each out-edge, where the slot
  * of entry e of row i is e + i and the slot of the appended self edge is rowptr[i+1] + i
  * (the indexing used by nc_gatv2_*).  Entries of one source are sorted by slot.
@@ -158,17 +159,41 @@ int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t ld, const fl
                  float* dbias, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Attention node-label aggregator (nn/aggregators.py:113-156).
+ * gl [n_src, ld] = linear_l_l(x), gr [n_dst, ld] = linear_r_l(x) (head h in columns [h*F, (h+1)*F)),
+ * attn [H*F].  Edges exactly as sampled (no self-loop re-normalisation).  The messages are the raw
+ * rows x[j], identical for every head, so out[i] = sum_j w_ij x[j] with w = mean_h alpha:
+ * nc_attn_agg_fwd writes alpha [(rowptr[n_dst] + n_dst) * H] (slot of entry e of row i = e + i)
+ * and the per-entry SpMM weights w [rowptr[n_dst]]; the aggregation itself is nc_spmm_csr.
+ * seg: device int32[4] = {0, F, 0, 0}.
+ * nc_attn_agg_bwd: dout [n_dst, ldo] (gradient of out), x [n_src, ldx] fp32 raw rows;
+ * rptr/rdst/rslot = nc_reverse_csr(..., add_self = 2); dalpha_ws / ds_ws: fp32 workspaces of the
+ * size of alpha; dgl [n_src, ld] / dgr [n_dst, ld] overwritten, dattn ACCUMULATED.               */
+int nc_attn_agg_fwd(const void* gl, const void* gr, int dtype, int64_t ld, const float* attn,
+                    const int32_t* rowptr, const int32_t* col, int32_t n_dst, const int32_t* seg,
+                    int32_t H, int32_t F, int32_t max_deg, float neg_slope, float* alpha, float* w,
+                    void* stream);
+int nc_attn_agg_bwd(const void* gl, const void* gr, int dtype, int64_t ld, const float* attn,
+                    const int32_t* rowptr, const int32_t* col, int32_t n_dst, int32_t n_src,
+                    const int32_t* rptr, const int32_t* rdst, const int32_t* rslot, const int32_t* seg,
+                    int32_t H, int32_t F, int32_t max_deg, float neg_slope, const float* dout,
+                    int64_t ldo, const float* x, int64_t ldx, const float* alpha, float* dalpha_ws,
+                    float* ds_ws, void* dgl, void* dgr, float* dattn, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Decoder epilogue + negative-binomial loss, forward value and gradients in one pass
  * (nn/layers.py:143 softmax over ALL features, nn/decoders.py:168 exp(log_lib)*softmax,
  * modules/vgpgae.py:714-749 column selection + library size over selected columns,
  * modules/losses.py:169-212 NB log-likelihood, theta = exp(theta_param)).
  * logits [n_rows, ldl], x [n_rows, ldx] raw labels over all F features, sel[F] != 0 marks the
  * reconstructed columns.  loss_sum += scale * sum_rows sum_sel -ll (fp64; `scale` = lambda / n_rows); dlogits = scale * d(sum -ll)/dlogits; dtheta += scale * ...;
- * means (nullable) receives exp(log_lib)*softmax over all F columns.                       */
+ * means (nullable) receives exp(log_lib)*softmax over all F columns; dx (nullable) the gradient
+ * w.r.t. the labels x (direct term + library size; labels produced by the attention aggregator
+ * are differentiable, modules/vgpgae.py:704-726).                       */
 int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x, int64_t ldx,
                      const uint8_t* sel, const float* theta_param, int32_t n_rows, int32_t F,
                      float scale, float* means, int64_t ldm, double* loss_sum, float* dlogits,
-                     int64_t lddl, float* dtheta, void* stream);
+                     int64_t lddl, float* dtheta, float* dx, int64_t lddx, void* stream);
 
 /* Cosine-similarity graph decoder (nn/decoders.py:56-62, nn/utils.py:8-36): rows [0,n_pairs)
  * of z against rows [n_pairs, 2*n_pairs).  norms: fp32[2*n_pairs] saved for the backward.   */

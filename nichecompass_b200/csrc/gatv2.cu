@@ -59,7 +59,9 @@ __global__ void __launch_bounds__(GT)
 k_gatv2_fwd(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, const float* __restrict__ att,
             const float* __restrict__ bias, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
             const int32_t* __restrict__ seg, int n_conv, int H, int max_deg, float slope,
-            float* __restrict__ out, int64_t ldo, float* __restrict__ alpha) {
+            float* __restrict__ out, int64_t ldo, float* __restrict__ alpha, int self_mode) {
+    // self_mode 1: PyG GATv2Conv (existing self entries dropped, one self edge appended per target);
+    // self_mode 0: edges exactly as given (attention node-label aggregator); out == NULL: alpha only
     extern __shared__ float s_mem[];
     const int stride = max_deg + 1;
     float* s_sc = s_mem;                               // [H][stride]
@@ -68,15 +70,16 @@ k_gatv2_fwd(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, cons
     const Seg sg = load_seg(seg, c);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int e0 = rowptr[i], e1 = rowptr[i + 1];
-    const int nE = e1 - e0 + 1;
+    const int nE = e1 - e0 + self_mode;
     const int NCH = n_conv * H;
-    for (int t = tid; t < nE; t += GT) s_j[t] = (t < nE - 1) ? col[e0 + t] : i;
+    for (int t = tid; t < nE; t += GT) s_j[t] = (t < e1 - e0) ? col[e0 + t] : i;
+    if (!self_mode && tid < H) alpha[(int64_t)(e1 + i) * NCH + c * H + tid] = 0.f;   // unused self slot
     __syncthreads();
     const T* xri = xr + (int64_t)i * ld + sg.off;
     // pass 1: raw attention scores, one warp per incoming edge
     for (int t = warp; t < nE; t += GT / 32) {
         const int j = s_j[t];
-        const bool skip = (t < nE - 1) && (j == i);
+        const bool skip = self_mode && (t < e1 - e0) && (j == i);
         const T* xlj = xl + (int64_t)j * ld + sg.off;
         for (int h = 0; h < H; ++h) {
             float p = 0.f;
@@ -110,6 +113,7 @@ k_gatv2_fwd(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, cons
         }
     }
     __syncthreads();
+    if (out == nullptr) return;
     // pass 2: weighted sum of x_l rows, mean over heads, + bias
     const float invH = 1.0f / (float)H;
     for (int k = tid * 4; k < sg.C; k += GT * 4) {
@@ -307,7 +311,9 @@ k_gatv2_bwd_dst(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, 
                 const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
                 const int32_t* __restrict__ seg, int n_conv, int H, int max_deg, float slope,
                 const float* __restrict__ dout, int64_t ldo, const float* __restrict__ alpha,
-                float* __restrict__ ds, T* __restrict__ dxr, float* __restrict__ datt, float* __restrict__ dbias) {
+                float* __restrict__ ds, T* __restrict__ dxr, float* __restrict__ datt, float* __restrict__ dbias,
+                int self_mode, const float* __restrict__ dalpha_ext) {
+    // dalpha_ext != NULL: d alpha is supplied per slot (attention aggregator: the messages are not x_l)
     extern __shared__ float s_mem[];
     const int stride = max_deg + 1;
     float* s_al = s_mem;                               // [H][stride] alpha
@@ -317,18 +323,20 @@ k_gatv2_bwd_dst(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, 
     const Seg sg = load_seg(seg, c);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int e0 = rowptr[i], e1 = rowptr[i + 1];
-    const int nE = e1 - e0 + 1;
+    const int nE = e1 - e0 + self_mode;
     const int NCH = n_conv * H;
     const float invH = 1.0f / (float)H;
-    for (int t = tid; t < nE; t += GT) s_j[t] = (t < nE - 1) ? col[e0 + t] : i;
+    for (int t = tid; t < nE; t += GT) s_j[t] = (t < e1 - e0) ? col[e0 + t] : i;
     for (int q = tid; q < nE * H; q += GT) {
         const int t = q / H, h = q % H;
         s_al[h * stride + t] = alpha[(int64_t)(e0 + i + t) * NCH + c * H + h];
+        if (dalpha_ext) s_ds[h * stride + t] = dalpha_ext[(int64_t)(e0 + i + t) * NCH + c * H + h];
     }
+    if (!self_mode && tid < H) ds[(int64_t)(e1 + i) * NCH + c * H + tid] = 0.f;       // unused self slot
     __syncthreads();
-    const float* g = dout + (int64_t)i * ldo + sg.out_off;
+    const float* g = dout ? dout + (int64_t)i * ldo + sg.out_off : nullptr;
     // d alpha[t,h] = (1/H) <g, x_l[j_t, h, :]>
-    for (int t = warp; t < nE; t += GT / 32) {
+    for (int t = warp; t < nE && !dalpha_ext; t += GT / 32) {
         const T* xlj = xl + (int64_t)s_j[t] * ld + sg.off;
         for (int h = 0; h < H; ++h) {
             float p = 0.f;
@@ -382,7 +390,7 @@ k_gatv2_bwd_dst(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, 
             if (k + 2 < sg.C) atomicAdd(da + k + 2, aa.z);
             if (k + 3 < sg.C) atomicAdd(da + k + 3, aa.w);
         }
-        if (dbias) {
+        if (dbias && g) {
             float4 gg = ldf<false>(g, k, sg.C);
             float* db = dbias + sg.out_off;
             if (k < sg.C) atomicAdd(db + k, gg.x);
@@ -601,7 +609,8 @@ k_gatv2_bwd_src(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, 
                 const int slot = staged ? s_slot[p - p0] : rslot[p];
                 const float al = __ldg(alpha + (int64_t)slot * NCH + c * H + h) * invH;
                 const float d = __ldg(ds + (int64_t)slot * NCH + c * H + h);
-                const float4 gg = ldf<false>(dout + (int64_t)i * ldo + sg.out_off, k, sg.C);
+                const float4 gg = dout ? ldf<false>(dout + (int64_t)i * ldo + sg.out_off, k, sg.C)
+                                       : make_float4(0.f, 0.f, 0.f, 0.f);
                 const float4 b = ldv<T, VEC>(xr + (int64_t)i * ld + sg.off + base, k, sg.C);
                 acc.x += al * gg.x + d * w.x * ((a.x + b.x) > 0.f ? 1.f : slope);
                 acc.y += al * gg.y + d * w.y * ((a.y + b.y) > 0.f ? 1.f : slope);
@@ -671,7 +680,7 @@ extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t l
             return NC_OK;
         }
     }
-#define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, bias, rowptr, col, seg, n_conv, H, max_deg, neg_slope, out, ldo, alpha)
+#define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, bias, rowptr, col, seg, n_conv, H, max_deg, neg_slope, out, ldo, alpha, 1)
     if (dtype == NC_F32) { if (v) L(float, true); else L(float, false); }
     else { if (v) L(__nv_bfloat16, true); else L(__nv_bfloat16, false); }
 #undef L
@@ -743,7 +752,7 @@ extern "C" int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t l
             return NC_OK;
         }
     }
-#define LD(T, V) if (n_dst > 0) k_gatv2_bwd_dst<T, V><<<gd, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, rowptr, col, seg, n_conv, H, max_deg, neg_slope, dout, ldo, alpha, ds_ws, (T*)dxr, datt, dbias)
+#define LD(T, V) if (n_dst > 0) k_gatv2_bwd_dst<T, V><<<gd, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, rowptr, col, seg, n_conv, H, max_deg, neg_slope, dout, ldo, alpha, ds_ws, (T*)dxr, datt, dbias, 1, nullptr)
 #define LS(T, V) k_gatv2_bwd_src<T, V><<<gs, GT, 0, s>>>((const T*)xl, (const T*)xr, ld, att, rptr, rdst, rslot, seg, n_conv, H, neg_slope, dout, ldo, alpha, ds_ws, (T*)dxl)
     if (dtype == NC_F32) { if (v) { LD(float, true); LS(float, true); } else { LD(float, false); LS(float, false); } }
     else { if (v) { LD(__nv_bfloat16, true); LS(__nv_bfloat16, true); } else { LD(__nv_bfloat16, false); LS(__nv_bfloat16, false); } }
@@ -751,5 +760,93 @@ extern "C" int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t l
 #undef LS
     nc_count_launch(2);
     NC_CHECK_LAUNCH("nc_gatv2_bwd");
+    return NC_OK;
+}
+
+// ============================================================================ attention node-label aggregator
+// nn/aggregators.py:113-156: scores from g_l = linear_l_l(x), g_r = linear_r_l(x),
+// messages are the RAW feature rows, identical for every head, so
+//   out[i] = mean_h sum_j alpha_ijh x[j] = sum_j abar_ij x[j],  abar = mean_h alpha
+// is the CSR SpMM of spmm.cu with abar as edge weights; the score / softmax machinery is the GATv2 one
+// with the edges exactly as sampled (no self-loop re-normalisation).
+namespace {
+// w[e] = mean_h alpha[slot(e), h] for the CSR entries of the first n_dst rows (slot = e + row)
+__global__ void k_agg_mean_alpha(const float* __restrict__ alpha, const int32_t* __restrict__ rowptr, int n_dst, int H,
+                                 float* __restrict__ w) {
+    const int i = blockIdx.x;
+    const float invH = 1.0f / (float)H;
+    for (int e = rowptr[i] + threadIdx.x; e < rowptr[i + 1]; e += blockDim.x) {
+        float a = 0.f;
+        for (int h = 0; h < H; ++h) a += alpha[(int64_t)(e + i) * H + h];
+        w[e] = a * invH;
+    }
+}
+// d alpha[slot(e), h] = (1/H) <dout[i], x[col[e]]>, one warp per entry
+__global__ void __launch_bounds__(128)
+k_agg_dalpha(const float* __restrict__ dout, int64_t ldo, const float* __restrict__ x, int64_t ldx, int F,
+             const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, int n_dst, int H,
+             float* __restrict__ dalpha) {
+    const int i = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float* g = dout + (int64_t)i * ldo;
+    const float invH = 1.0f / (float)H;
+    for (int e = rowptr[i] + warp; e < rowptr[i + 1]; e += 4) {
+        const float* xr = x + (int64_t)col[e] * ldx;
+        float p = 0.f;
+        for (int k = lane; k < F; k += 32) p += __ldg(g + k) * __ldg(xr + k);
+        p = warp_sum(p) * invH;
+        if (lane < H) dalpha[(int64_t)(e + i) * H + lane] = p;
+    }
+    if (threadIdx.x < H) dalpha[(int64_t)(rowptr[i + 1] + i) * H + threadIdx.x] = 0.f;   // unused self slot
+}
+}  // namespace
+
+extern "C" int nc_attn_agg_fwd(const void* gl, const void* gr, int dtype, int64_t ld, const float* attn,
+                               const int32_t* rowptr, const int32_t* col, int32_t n_dst, const int32_t* seg,
+                               int32_t H, int32_t F, int32_t max_deg, float neg_slope, float* alpha, float* w,
+                               void* stream) {
+    NC_REQUIRE(n_dst >= 0 && H > 0 && H <= 32 && F > 0 && max_deg >= 0, NC_ESHAPE, "nc_attn_agg_fwd: bad sizes");
+    NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_attn_agg_fwd: bad dtype %d", dtype);
+    if (n_dst == 0) return NC_OK;
+    const size_t smem = ((size_t)H * (max_deg + 1) + (max_deg + 1)) * 4;
+    NC_REQUIRE(smem <= 48 * 1024, NC_EUNSUPPORTED, "nc_attn_agg_fwd: max_deg=%d too large", max_deg);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int32_t seg_host[4] = {0, F, 0, 0};
+    dim3 grid(n_dst, 1);
+    const bool v = vec_ok(gl, gr, ld, seg_host, 1, dtype == NC_F32 ? 4 : 2) && ((uintptr_t)attn % 16 == 0);
+#define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)gl, (const T*)gr, ld, attn, nullptr, rowptr, col, seg, 1, H, max_deg, neg_slope, nullptr, 0, alpha, 0)
+    if (dtype == NC_F32) { if (v) L(float, true); else L(float, false); }
+    else { if (v) L(__nv_bfloat16, true); else L(__nv_bfloat16, false); }
+#undef L
+    k_agg_mean_alpha<<<n_dst, 32, 0, s>>>(alpha, rowptr, n_dst, H, w);
+    nc_count_launch(2);
+    NC_CHECK_LAUNCH("nc_attn_agg_fwd");
+    return NC_OK;
+}
+
+extern "C" int nc_attn_agg_bwd(const void* gl, const void* gr, int dtype, int64_t ld, const float* attn,
+                               const int32_t* rowptr, const int32_t* col, int32_t n_dst, int32_t n_src,
+                               const int32_t* rptr, const int32_t* rdst, const int32_t* rslot, const int32_t* seg,
+                               int32_t H, int32_t F, int32_t max_deg, float neg_slope, const float* dout,
+                               int64_t ldo, const float* x, int64_t ldx, const float* alpha, float* dalpha_ws,
+                               float* ds_ws, void* dgl, void* dgr, float* dattn, void* stream) {
+    NC_REQUIRE(n_dst >= 0 && n_src >= n_dst && H > 0 && H <= 32 && F > 0, NC_ESHAPE, "nc_attn_agg_bwd: bad sizes");
+    NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_attn_agg_bwd: bad dtype %d", dtype);
+    if (n_src == 0) return NC_OK;
+    const size_t smem = ((size_t)2 * H * (max_deg + 1) + (max_deg + 1)) * 4;
+    NC_REQUIRE(smem <= 48 * 1024, NC_EUNSUPPORTED, "nc_attn_agg_bwd: max_deg=%d too large", max_deg);
+    cudaStream_t s = (cudaStream_t)stream;
+    const int32_t seg_host[4] = {0, F, 0, 0};
+    const bool v = vec_ok(gl, gr, ld, seg_host, 1, dtype == NC_F32 ? 4 : 2) && ((uintptr_t)attn % 16 == 0) &&
+                   ((uintptr_t)dgl % 16 == 0) && ((uintptr_t)dgr % 16 == 0);
+    dim3 gd(n_dst, 1), gs(n_src, 1);
+    if (n_dst > 0) k_agg_dalpha<<<n_dst, 128, 0, s>>>(dout, ldo, x, ldx, F, rowptr, col, n_dst, H, dalpha_ws);
+#define LD(T, V) if (n_dst > 0) k_gatv2_bwd_dst<T, V><<<gd, GT, smem, s>>>((const T*)gl, (const T*)gr, ld, attn, rowptr, col, seg, 1, H, max_deg, neg_slope, nullptr, 0, alpha, ds_ws, (T*)dgr, dattn, nullptr, 0, dalpha_ws)
+#define LS(T, V) k_gatv2_bwd_src<T, V><<<gs, GT, 0, s>>>((const T*)gl, (const T*)gr, ld, attn, rptr, rdst, rslot, seg, 1, H, neg_slope, nullptr, 0, alpha, ds_ws, (T*)dgl)
+    if (dtype == NC_F32) { if (v) { LD(float, true); LS(float, true); } else { LD(float, false); LS(float, false); } }
+    else { if (v) { LD(__nv_bfloat16, true); LS(__nv_bfloat16, true); } else { LD(__nv_bfloat16, false); LS(__nv_bfloat16, false); } }
+#undef LD
+#undef LS
+    nc_count_launch(3);
+    NC_CHECK_LAUNCH("nc_attn_agg_bwd");
     return NC_OK;
 }

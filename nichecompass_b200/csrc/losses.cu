@@ -30,7 +30,8 @@ __global__ void __launch_bounds__(NB_T)
 k_nb_fused(const float* __restrict__ logits, int64_t ldl, const float* __restrict__ x, int64_t ldx,
            const uint8_t* __restrict__ sel, const float* __restrict__ theta_param, int F, float scale,
            float* __restrict__ means, int64_t ldm, double* __restrict__ loss_sum,
-           float* __restrict__ dlogits, int64_t lddl, float* __restrict__ dtheta) {
+           float* __restrict__ dlogits, int64_t lddl, float* __restrict__ dtheta, float* __restrict__ dx,
+           int64_t lddx) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
     __shared__ float red[32];
@@ -112,6 +113,23 @@ k_nb_fused(const float* __restrict__ logits, int64_t ldl, const float* __restric
                 dmu = -(xv / (mu + eps) - (xv + th) / (th + mu + eps));
             }
             dr[c] = (float)((double)scale * (mu * dmu - p * D));
+        }
+    }
+    // gradient w.r.t. the labels (only the attention node-label aggregator produces labels that carry one):
+    // d(-ll_k)/dx_k directly, plus D / L through the library size L = sum_sel x that scales every mean
+    if (dx) {
+        float* dxr = dx + (int64_t)r * lddx;
+        const double DL = D / L;
+        for (int c = c0 + tid; c < c1; c += NB_T) {
+            double gx = 0.0;
+            if (sel[c]) {
+                const double p = (double)expf(lr[c] - m) * inv_se;
+                const double mu = L * p;
+                const double xv = (double)xr[c];
+                const double th = exp((double)theta_param[c]);
+                gx = -(log(mu + eps) - log(th + mu + eps) + digamma_d(xv + th) - digamma_d(xv + 1.0)) + DL;
+            }
+            dxr[c] = (float)((double)scale * gx);
         }
     }
 }
@@ -228,7 +246,7 @@ k_kl(const float* __restrict__ mu, int64_t ldmu, const float* __restrict__ ls, i
 extern "C" int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x, int64_t ldx, const uint8_t* sel,
                                 const float* theta_param, int32_t n_rows, int32_t F, float scale, float* means,
                                 int64_t ldm, double* loss_sum, float* dlogits, int64_t lddl, float* dtheta,
-                                void* stream) {
+                                float* dx, int64_t lddx, void* stream) {
     NC_REQUIRE(n_rows >= 0 && F > 0 && ldl >= F && ldx >= F, NC_ESHAPE, "nc_nb_loss_fused: bad shape rows=%d F=%d", n_rows, F);
     if (n_rows == 0) return NC_OK;
     cudaLaunchConfig_t cfg = {};
@@ -244,7 +262,7 @@ extern "C" int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     cudaError_t le = cudaLaunchKernelEx(&cfg, k_nb_fused, logits, ldl, x, ldx, sel, theta_param, (int)F, scale, means,
-                                        ldm, loss_sum, dlogits, lddl, dtheta);
+                                        ldm, loss_sum, dlogits, lddl, dtheta, dx, lddx);
     if (le != cudaSuccess) { nc_set_error("nc_nb_loss_fused: launch failed: %s", cudaGetErrorString(le)); return NC_ECUDA; }
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_nb_loss_fused");

@@ -61,9 +61,9 @@ __global__ void k_rev_count(const int32_t* __restrict__ rowptr, const int32_t* _
     if (i >= n_rows) return;
     for (int e = rowptr[i]; e < rowptr[i + 1]; ++e) {
         int j = col[e];
-        if (j != i) atomicAdd(&cnt[j], 1);
+        if (j != i || add_self == 2) atomicAdd(&cnt[j], 1);
     }
-    if (add_self) atomicAdd(&cnt[i], 1);
+    if (add_self == 1) atomicAdd(&cnt[i], 1);
 }
 
 // single-CTA exclusive scan: out[0..n] (n+1 entries), in[0..n)
@@ -112,12 +112,12 @@ __global__ void k_rev_fill(const int32_t* __restrict__ rowptr, const int32_t* __
     if (i >= n_rows) return;
     for (int e = rowptr[i]; e < rowptr[i + 1]; ++e) {
         int j = col[e];
-        if (j == i) continue;
+        if (j == i && add_self != 2) continue;
         int pos = rptr[j] + atomicAdd(&cursor[j], 1);
         rdst[pos] = i;
         rslot[pos] = e + i;
     }
-    if (add_self) {
+    if (add_self == 1) {
         int pos = rptr[i] + atomicAdd(&cursor[i], 1);
         rdst[pos] = i;
         rslot[pos] = rowptr[i + 1] + i;

@@ -622,17 +622,23 @@ class NBLossFusedFn(torch.autograd.Function):
         dlog = torch.empty(nb, F, dtype=torch.float32, device=dev)
         dth = torch.zeros(F, dtype=torch.float32, device=dev)
         means = torch.empty(nb, F, dtype=torch.float32, device=dev)
+        dx = torch.empty(nb, F, dtype=torch.float32, device=dev) if ctx.needs_input_grad[2] else None
         logits = logits.contiguous()
-        call("nc_nb_loss_fused", logits, logits.stride(0), x_full, x_full.stride(0), sel, theta_param.detach(),
-             nb, F, 1.0 / nb, means, F, acc, dlog, F, dth)
-        ctx.save_for_backward(dlog, dth)
+        xd = x_full.detach()
+        call("nc_nb_loss_fused", logits, logits.stride(0), xd, xd.stride(0), sel, theta_param.detach(),
+             nb, F, 1.0 / nb, means, F, acc, dlog, F, dth, dx, F if dx is not None else 0)
+        if dx is not None:
+            ctx.save_for_backward(dlog, dth, dx)
+        else:
+            ctx.save_for_backward(dlog, dth)
         ctx.mark_non_differentiable(means)
         return acc.float().reshape(()), means
 
     @staticmethod
     def backward(ctx, g, _gm):
-        dlog, dth = ctx.saved_tensors
-        return dlog * g, dth * g, None, None
+        dlog, dth = ctx.saved_tensors[:2]
+        dx = ctx.saved_tensors[2] * g if len(ctx.saved_tensors) > 2 else None
+        return dlog * g, dth * g, dx, None
 
 
 # --------------------------------------------------------------------------- weight regularisers
@@ -688,14 +694,105 @@ class WeightRegFn(torch.autograd.Function):
 
 
 # --------------------------------------------------------------------------- attention aggregator
+_SEG_CACHE = {}
+
+
+def _agg_seg(F: int, device) -> torch.Tensor:
+    key = (F, str(device))
+    if key not in _SEG_CACHE:
+        _SEG_CACHE[key] = torch.tensor([0, F, 0, 0], dtype=torch.int32, device=device)
+    return _SEG_CACHE[key]
+
+
 class AttentionAggregatorFn(torch.autograd.Function):
-    """nn/aggregators.py:113-156.  Not covered by the round-1 kernels:
-    fails loudly instead of falling back to a framework implementation."""
+    """nn/aggregators.py:113-156: g_l = linear_l_l(x), g_r = linear_r_l(x) (tcgen05 /
+    SIMT GEMMs), alpha = segment softmax of attn . leaky_relu(g_r[i] + g_l[j]) over the incoming edges
+    exactly as sampled (GATv2 score kernels without self-loop re-normalisation), out[i] = mean_h sum_j
+    alpha_ijh x[j] = CSR SpMM of the raw rows with the head-averaged coefficients.  Returns
+    (out [n_dst, F] fp32, alpha [E_dst, H] in CSR entry order)."""
 
     @staticmethod
-    def forward(ctx, x, graph, heads, slope, act_dtype, cache_key, w_l, w_r, attn):
-        raise NotImplementedError("node_label_method='one-hop-attention' has no CUDA kernel yet "
-                                  "(DESIGN.md 'not yet covered'); use 'one-hop-norm' or 'one-hop-sum'")
+    def forward(ctx, x, graph: SubgraphCSR, heads, slope, act_dtype, cache_key, want_agg, w_l, w_r, attn):
+        dev = x.device
+        n_sub, n_dst = graph.n_nodes, graph.n_dst
+        F = x.size(1)
+        assert w_l.shape == (heads * F, F) and x.size(0) == n_sub
+        x = x.contiguous().float()
+        ldx = pad8(F)
+        xa = torch.zeros(n_sub, ldx, dtype=act_dtype, device=dev)
+        xa[:, :F] = x
+        Wl = pack_rows((cache_key, "Wl"), [w_l], act_dtype, F)
+        Wr = pack_rows((cache_key, "Wr"), [w_r], act_dtype, F)
+        NL = heads * F
+        ldg = pad8(NL)
+        Gl = torch.empty(n_sub, ldg, dtype=act_dtype, device=dev)
+        Gr = torch.empty(max(n_dst, 1), ldg, dtype=act_dtype, device=dev)
+        ops.gemm(xa, Wl, out=Gl[:, :NL], M=n_sub, N=NL, K=F)
+        ops.gemm(xa, Wr, out=Gr[:, :NL], M=n_dst, N=NL, K=F)
+        att = attn.detach().reshape(-1).float().contiguous()
+        n_slots = graph.n_slots
+        alpha = torch.empty(max(n_slots, 1) * heads, dtype=torch.float32, device=dev)
+        w = torch.empty(max(graph.col.numel(), 1), dtype=torch.float32, device=dev)
+        seg = _agg_seg(F, dev)
+        call("nc_attn_agg_fwd", Gl, Gr, dtype_code(act_dtype), ldg, att, graph.rowptr, graph.col, n_dst, seg, heads, F,
+             graph.max_deg, float(slope), alpha, w)
+        out = ops.spmm_csr(x, graph.rowptr, graph.col, w, None, False, n_dst)
+        ctx.save_for_backward(x, xa, Gl, Gr, alpha, att, Wl, Wr)
+        ctx.meta = (graph, heads, float(slope), F, NL, ldg, act_dtype)
+        ctx.params = (w_l, w_r, attn)
+        # per-entry, per-head coefficients in CSR entry order (slot of entry e of row i is e + i)
+        E = graph.col.numel() if want_agg else 0
+        if E > 0:
+            rows = torch.searchsorted(graph.rowptr[1:n_dst + 1].contiguous(),
+                                      torch.arange(E, device=dev, dtype=torch.int32), right=True)
+            slots = torch.arange(E, device=dev) + rows
+            agg = alpha.view(-1, heads)[slots.clamp_(max=max(n_slots - 1, 0))]
+        else:
+            agg = alpha.new_zeros(0, heads)
+        ctx.mark_non_differentiable(agg)
+        return out, agg
+
+    @staticmethod
+    def backward(ctx, dout, _dagg):
+        x, xa, Gl, Gr, alpha, att, Wl, Wr = ctx.saved_tensors
+        graph, heads, slope, F, NL, ldg, act = ctx.meta
+        w_l, w_r, attn = ctx.params
+        dev = x.device
+        n_sub, n_dst = graph.n_nodes, graph.n_dst
+        dout = dout.contiguous().float()
+        rev = ops.reverse_csr(graph.rowptr, graph.col, n_sub, n_dst, 2, graph.n_slots)
+        dGl = torch.empty(n_sub, ldg, dtype=act, device=dev)
+        dGr = torch.empty(max(n_dst, 1), ldg, dtype=act, device=dev)
+        if ldg != NL:
+            dGl[:, NL:].zero_()
+            dGr[:, NL:].zero_()
+        need = ctx.needs_input_grad
+        g_att = grad_view([attn], [need[9]])
+        datt = g_att if g_att is not None else torch.zeros(NL, dtype=torch.float32, device=dev)
+        dal = torch.empty_like(alpha)
+        ds = torch.empty_like(alpha)
+        seg = _agg_seg(F, dev)
+        call("nc_attn_agg_bwd", Gl, Gr, dtype_code(act), ldg, att, graph.rowptr, graph.col, n_dst, n_sub,
+             rev[0], rev[1], rev[2], seg, heads, F, graph.max_deg, slope, dout, dout.stride(0), x, x.stride(0),
+             alpha, dal, ds, dGl, dGr, datt)
+        g_wl = grad_view([w_l], [need[7]]) if F % 4 == 0 else None
+        g_wr = grad_view([w_r], [need[8]]) if F % 4 == 0 else None
+        if g_wl is not None:
+            ops.gemm(dGl, xa, trans_a=True, trans_b=True, out=g_wl.view(NL, F), accumulate=True, M=NL, N=F, K=n_sub)
+            dWl = None
+        else:
+            dWl = ops.gemm(dGl, xa, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=F, K=n_sub)
+        if g_wr is not None:
+            if n_dst > 0:
+                ops.gemm(dGr, xa, trans_a=True, trans_b=True, out=g_wr.view(NL, F), accumulate=True, M=NL, N=F, K=n_dst)
+            dWr = None
+        else:
+            dWr = ops.gemm(dGr, xa, trans_a=True, trans_b=True, out_dtype=torch.float32, M=NL, N=F, K=n_dst) \
+                if n_dst > 0 else torch.zeros(NL, F, device=dev)
+        d_attn = None if g_att is not None else datt.reshape(attn.shape)
+        return (None, None, None, None, None, None, None,
+                dWl.contiguous() if dWl is not None and dWl.stride(0) != F else dWl,
+                dWr.contiguous() if dWr is not None and dWr.stride(0) != F else dWr, d_attn)
 
 
 # --------------------------------------------------------------------------- GCN encoder

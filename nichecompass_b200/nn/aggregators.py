@@ -11,7 +11,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
-from ..functional import AttentionAggregatorFn, SubgraphCSR
+from ..functional import AttentionAggregatorFn, SubgraphCSR, new_cache_key
 from .conv import _Lin, glorot_
 
 
@@ -80,6 +80,7 @@ class OneHopAttentionNodeLabelAggregator(nn.Module):
         self.linear_r_l = _Lin(n_input, n_input * n_heads, bias=False)
         self.attn = nn.Parameter(glorot_(torch.empty(1, n_heads, n_input)))
         self.compute_dtype = torch.float32
+        self._key = new_cache_key()
         print(f"ONE HOP ATTENTION {modality.upper()} NODE LABEL AGGREGATOR -> "
               f"n_input: {n_input}, n_heads: {n_heads}")
 
@@ -88,6 +89,12 @@ class OneHopAttentionNodeLabelAggregator(nn.Module):
         if n_rows is not None and n_rows != graph.n_dst:
             graph = SubgraphCSR(graph.rowptr, graph.col, graph.n_nodes, n_rows, graph.max_deg)
         out, alpha = AttentionAggregatorFn.apply(x.detach(), graph, self.n_heads, self.leaky_relu_negative_slope,
-                                                 self.compute_dtype, id(self), self.linear_l_l.weight,
-                                                 self.linear_r_l.weight, self.attn)
+                                                 self.compute_dtype, self._key, bool(return_agg_weights),
+                                                 self.linear_l_l.weight, self.linear_r_l.weight, self.attn)
         return out, (alpha if return_agg_weights else None)
+
+    def forward_store(self, store, n_id, graph: SubgraphCSR, n_rows: int) -> torch.Tensor:
+        """Count rows of all sampled cells gathered densely from the store (the attention scores need
+        linear maps of every neighbour's full row), then the same kernels as ``forward``."""
+        x = ops.csr_gather_rows(store, n_id, graph.n_nodes, False, torch.float32)
+        return self.forward(x[:, :self.n_input], graph, n_rows=n_rows)[0]

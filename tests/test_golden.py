@@ -93,7 +93,7 @@ def test_oracle_reproduces_reference_golden(name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", [c for c in CASES if "attention" not in c])
+@pytest.mark.parametrize("name", CASES)
 def test_cuda_reproduces_reference_golden(name):
     from tests.test_vgpgae_gpu import build_module
     z, cfg, state, node_b, edge_b, only_active = load_case(name)

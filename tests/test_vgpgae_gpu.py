@@ -92,6 +92,8 @@ def run_pair(conv_layer, node_label_method, n_addon, dtype, n_genes=40, use_only
     ("gatv2conv", "one-hop-sum", 0, 43),
     ("gcnconv", "one-hop-norm", 4, 40),
     ("gatv2conv", "one-hop-norm", 3, 41),     # C % 4 != 0 -> scalar kernel paths
+    ("gatv2conv", "one-hop-attention", 0, 40),
+    ("gcnconv", "one-hop-attention", 2, 43),  # F % 4 != 0 -> scalar attention-aggregator paths
 ])
 def test_fp32_forward_loss_grads(conv_layer, node_label_method, n_addon, n_genes):
     orc, mod, (on, oe, ol), (cn, ce, cl), p64 = run_pair(conv_layer, node_label_method, n_addon,
