@@ -202,10 +202,11 @@ int nc_cosine_fwd(const float* z, int64_t ldz, int32_t P, int32_t n_pairs, float
 int nc_cosine_bwd(const float* z, int64_t ldz, int32_t P, int32_t n_pairs, const float* logits,
                   const float* norms, const float* dlogits, float* dz, int64_t lddz,
                   void* stream);
-/* Weighted BCE-with-logits, pos_weight = #neg/#pos over the included edges
- * (modules/losses.py:123-166); loss_out = mean loss, dlogits = scale * dloss/dlogits.      */
+/* BCE-with-logits over the included edges (incl NULL = all): use_pos_weight != 0 weighs the positives
+ * by #neg/#pos (modules/losses.py:123-166), 0 is the plain mean BCE of the covariate contrastive loss
+ * (modules/losses.py:103-118); loss_out = mean loss, dlogits = scale * dloss/dlogits.       */
 int nc_bce_fwd_bwd(const float* logits, const float* labels, const uint8_t* incl, int32_t n,
-                   float scale, float* loss_out, float* dlogits, void* stream);
+                   float scale, float* loss_out, float* dlogits, int use_pos_weight, void* stream);
 /* KL regulariser (modules/losses.py:255-284): sum_out += kl (fp64); dmu/dlogstd (nullable)
  * = scale * dkl/d.                                                                          */
 int nc_kl_fwd_bwd(const float* mu, int64_t ldmu, const float* logstd, int64_t ldls, int32_t R,

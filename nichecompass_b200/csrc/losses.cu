@@ -187,7 +187,7 @@ __device__ __forceinline__ float softplusf(float v) { return fmaxf(v, 0.f) + log
 
 __global__ void __launch_bounds__(1024)
 k_bce(const float* __restrict__ logits, const float* __restrict__ labels, const uint8_t* __restrict__ incl,
-      int n, float scale, float* __restrict__ loss_out, float* __restrict__ dlogits) {
+      int n, float scale, float* __restrict__ loss_out, float* __restrict__ dlogits, int use_pos_weight) {
     __shared__ float red[32];
     const int tid = threadIdx.x;
     float np = 0.f, nn = 0.f;
@@ -201,7 +201,7 @@ k_bce(const float* __restrict__ logits, const float* __restrict__ labels, const 
     float cnt = 0.f;
     for (int e = tid; e < n; e += 1024) cnt += (incl && !incl[e]) ? 0.f : 1.f;
     cnt = block_sum(cnt, red);
-    const float pw = nn / np;
+    const float pw = use_pos_weight ? nn / np : 1.f;
     float acc = 0.f;
     for (int e = tid; e < n; e += 1024) {
         const bool in = !(incl && !incl[e]);
@@ -291,9 +291,9 @@ extern "C" int nc_cosine_bwd(const float* z, int64_t ldz, int32_t P, int32_t n_p
 }
 
 extern "C" int nc_bce_fwd_bwd(const float* logits, const float* labels, const uint8_t* incl, int32_t n, float scale,
-                              float* loss_out, float* dlogits, void* stream) {
+                              float* loss_out, float* dlogits, int use_pos_weight, void* stream) {
     NC_REQUIRE(n > 0, NC_ESHAPE, "nc_bce_fwd_bwd: empty input");
-    k_bce<<<1, 1024, 0, (cudaStream_t)stream>>>(logits, labels, incl, n, scale, loss_out, dlogits);
+    k_bce<<<1, 1024, 0, (cudaStream_t)stream>>>(logits, labels, incl, n, scale, loss_out, dlogits, use_pos_weight);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_bce_fwd_bwd");
     return NC_OK;

@@ -443,18 +443,19 @@ class BCEFn(torch.autograd.Function):
     """modules/losses.py:123-166 (pos_weight = #neg / #pos over the included edges)."""
 
     @staticmethod
-    def forward(ctx, logits, labels, incl):
+    def forward(ctx, logits, labels, incl, use_pos_weight=True):
         n = logits.numel()
         loss = torch.empty(1, dtype=torch.float32, device=logits.device)
         dlog = torch.empty(n, dtype=torch.float32, device=logits.device)
-        call("nc_bce_fwd_bwd", logits.contiguous(), labels.contiguous().float(), incl, n, 1.0, loss, dlog)
+        call("nc_bce_fwd_bwd", logits.contiguous(), labels.contiguous().float(), incl, n, 1.0, loss, dlog,
+             int(bool(use_pos_weight)))
         ctx.save_for_backward(dlog)
         return loss.reshape(())
 
     @staticmethod
     def backward(ctx, g):
         (dlog,) = ctx.saved_tensors
-        return dlog * g, None, None
+        return dlog * g, None, None, None
 
 
 # --------------------------------------------------------------------------- masked decoder

@@ -86,10 +86,28 @@ def compute_cat_covariates_contrastive_loss(edge_recon_logits: torch.Tensor,
                                             contrastive_logits_pos_ratio: float = 0.,
                                             contrastive_logits_neg_ratio: float = 0.) -> torch.Tensor:
     """modules/losses.py:15-120.  Returns 0 exactly like the reference when no covariates are
-    given or both ratios are 0 (the default of ``NicheCompass.train``); the top-k thresholded
-    variant has no CUDA kernel yet and fails loudly."""
+    given or both ratios are 0 (the default of ``NicheCompass.train``).  Selection of the
+    top / bottom logits among the cross-category pairs is index plumbing (``torch.topk``); the loss
+    and its gradient are the BCE kernel without the positive weight."""
     if edge_same_cat_covariates_cat is None or (contrastive_logits_pos_ratio == 0 and
                                                 contrastive_logits_neg_ratio == 0):
         return torch.tensor(0., device=edge_recon_logits.device)
-    raise NotImplementedError("cat-covariates contrastive loss with non-zero ratios is not implemented "
-                              "in the CUDA path yet (SURVEY.md 8a row a17, lowest priority)")
+    import math
+    total = torch.zeros((), dtype=torch.float32, device=edge_recon_logits.device)
+    logits = edge_recon_logits
+    for same in edge_same_cat_covariates_cat:
+        diff = ~same
+        diff_logits = logits.detach()[diff]
+        n_diff = int(diff_logits.numel())                    # host read-back (the reference's len())
+        n_pos = math.ceil(contrastive_logits_pos_ratio * n_diff)
+        n_neg = math.ceil(contrastive_logits_neg_ratio * n_diff)
+        pos_thresh = torch.topk(diff_logits, n_pos).values[-1] if n_pos > 0 else float("inf")
+        neg_thresh = torch.topk(diff_logits, n_neg, largest=False).values[-1] if n_neg > 0 else float("-inf")
+        pos_ex = diff & (logits.detach() >= pos_thresh)
+        neg_ex = diff & (logits.detach() <= neg_thresh)
+        # the reference relabels IN PLACE (modules/losses.py:96-101): later covariates see the new labels
+        edge_recon_labels[pos_ex] = 1
+        edge_recon_labels[neg_ex] = 0
+        sel = (pos_ex | neg_ex).to(torch.uint8).contiguous()
+        total = total + BCEFn.apply(logits, edge_recon_labels.clone(), sel, False)
+    return total

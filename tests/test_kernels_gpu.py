@@ -174,3 +174,23 @@ def test_masked_sddmm_matches_dense(nb):
     assert H.rel_err(dW, ref) < 1e-5
     assert mask_info(torch.ones(4, 4, device=DEV))[0] == "none"
     assert mask_info((torch.rand(50, 50, generator=g) < 0.5).float().to(DEV))[0] == "dense"
+
+
+def test_cat_covariates_contrastive_loss_matches_oracle():
+    """modules/losses.py:15-120: value and logit gradient, two covariates (labels relabelled in place)."""
+    from nichecompass_b200.modules.losses import compute_cat_covariates_contrastive_loss
+    from oracle.vgpgae_ref import contrastive_loss
+    g = torch.Generator().manual_seed(9)
+    n = 200
+    logits = (torch.rand(n, generator=g) * 2 - 1)
+    labels = torch.cat((torch.ones(n // 2), torch.zeros(n // 2)))
+    same = [torch.rand(n, generator=g) < 0.6, torch.rand(n, generator=g) < 0.4]
+    lo = logits.double().clone().requires_grad_(True)
+    ref = contrastive_loss(lo, labels.double().clone(), [s.clone() for s in same], 0.125, 0.25)
+    ref.backward()
+    lc = logits.to(DEV).requires_grad_(True)
+    lab = labels.to(DEV).clone()
+    out = compute_cat_covariates_contrastive_loss(lc, lab, [s.to(DEV) for s in same], 0.125, 0.25)
+    out.backward()
+    assert H.rel_err(out, ref) < 1e-5
+    assert H.rel_err(lc.grad, lo.grad) < 1e-5
