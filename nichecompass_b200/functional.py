@@ -500,14 +500,15 @@ _ZA_CACHE = {}
 
 def mask_info(mask: Optional[torch.Tensor]):
     """Structure of a MaskedLinear mask [F, P] (cached per tensor version; one host read-back when a
-    mask is first seen): ("none",) for an absent / all-ones mask, ("sparse", rowptr, col, val) with the
+    mask is first seen; the entry pins the tensor so that a freed mask's address cannot alias a new
+    one): ("none",) for an absent / all-ones mask, ("sparse", rowptr, col, val) with the
     CSR-by-feature form when fewer than 10 % of the entries are set, else ("dense",)."""
     if mask is None:
         return ("none",)
     key = (mask.data_ptr(), mask._version, tuple(mask.shape))
     hit = _MASK_INFO.get(key)
     if hit is not None:
-        return hit
+        return hit[0]
     if len(_MASK_INFO) > 64:
         _MASK_INFO.clear()
     with torch.no_grad():
@@ -523,7 +524,7 @@ def mask_info(mask: Optional[torch.Tensor]):
                     mask[idx[:, 0], idx[:, 1]].float().contiguous())
         else:
             info = ("dense",)
-    _MASK_INFO[key] = info
+    _MASK_INFO[key] = (info, mask)            # holding the tensor keeps its pointer from being recycled
     return info
 
 
