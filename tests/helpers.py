@@ -68,3 +68,52 @@ def batch_to(batch, dtype=None, device=None):
 def rel_err(a, b):
     a, b = a.detach().double().cpu(), b.detach().double().cpu()
     return float((a - b).abs().max() / (b.abs().max() + 1e-30))
+
+
+def multimodal_covariate_problem(n_cells=140, n_genes=36, n_peaks=52, n_prior_gp=10, n_addon_gp=3, seed=0,
+                                 conv_layer="gatv2conv", node_label_method="one-hop-norm",
+                                 injection=("encoder", "gene_expr_decoder", "chrom_access_decoder"),
+                                 with_atac=True, with_covariates=True):
+    """Tiny C3/C4-shaped problem: two samples (covariate 0, no cross-category edges) + a random
+    'condition' covariate (covariate 1), RNA + ATAC counts, gene-peak mapping, peak masks derived
+    from the gene masks as in models/nichecompass.py:404-447.  Returns (adata, cfg, x [N, F+Fp]
+    fp64, cats long [N, 2] or None)."""
+    rng = np.random.default_rng(seed + 100)
+    adata = tiny_problem(n_cells=n_cells, n_genes=n_genes, n_prior_gp=n_prior_gp, seed=seed, n_samples=2)
+    extra = {}
+    x = dense_x(adata, torch.float64)
+    if with_atac:
+        gp = (rng.random((n_genes, n_peaks)) < 0.08)
+        gp[rng.integers(0, n_genes, n_peaks), np.arange(n_peaks)] = True       # every peak maps to a gene
+        gpm = torch.tensor(gp)
+        tm = torch.tensor(adata.varm["nichecompass_gp_targets"].T, dtype=torch.int64)
+        sm = torch.tensor(adata.varm["nichecompass_gp_sources"].T, dtype=torch.int64)
+        tam = (tm @ gpm.to(torch.int64)) > 0                                    # [Pp, Fp]
+        sam = (sm @ gpm.to(torch.int64)) > 0
+        xa = torch.tensor(rng.poisson(0.6, size=(n_cells, n_peaks)), dtype=torch.float64)
+        xa[:, 0] += 1.                                                          # no empty rows
+        x = torch.cat((x, xa), dim=1)
+        extra.update(n_input=n_genes + n_peaks, n_output_peaks=n_peaks, gene_peaks_mask=gpm,
+                     target_atac_mask=tam, source_atac_mask=sam)
+    cats = None
+    if with_covariates:
+        sample = torch.tensor([int(s[-1]) for s in adata.obs["batch"]], dtype=torch.long)
+        cond = torch.tensor(rng.integers(0, 3, n_cells), dtype=torch.long)
+        cats = torch.stack((sample, cond), dim=1)
+        extra.update(cat_covariates_embeds_nums=[3, 2], cat_covariates_num_cats=[2, 3],
+                     cat_covariates_no_edges=[True, False],
+                     cat_covariates_embeds_injection=list(injection),
+                     include_cat_covariates_contrastive_loss=True)
+    cfg = oracle_cfg_from_adata(adata, n_addon_gp=n_addon_gp, conv_layer=conv_layer,
+                                node_label_method=node_label_method,
+                                n_hidden=min(n_genes, n_prior_gp + n_addon_gp), **extra)
+    if with_atac:
+        fd = cfg["features_idx_dict"]
+        for ent, m in (("target", tam), ("source", sam)):
+            masked = torch.nonzero(m.sum(0) > 0).flatten().tolist()
+            ms = set(masked)
+            fd[f"{ent}_masked_atac_idx"] = masked
+            fd[f"{ent}_unmasked_atac_idx"] = [i for i in range(n_peaks) if i not in ms]
+        both = sorted(set(fd["target_masked_atac_idx"]) | {i + n_peaks for i in fd["source_masked_atac_idx"]})
+        fd["masked_atac_idx"] = both
+    return adata, cfg, x, cats

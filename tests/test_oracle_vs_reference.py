@@ -159,3 +159,123 @@ def test_only_active_gps_path_matches_reference():
     for k in ("target_rna_nb_means", "source_rna_nb_means"):
         assert H.rel_err(on[k], rn[k]) < 1e-10, k
     assert H.rel_err(orc.running_mean_abs_mu, m.running_mean_abs_mu) < 1e-12
+
+
+# ----------------------------------------------------------------------------- C3 / C4 shapes
+def build_reference_module_mm(ref, cfg, with_atac, with_cov):
+    feat = copy.deepcopy(cfg["features_idx_dict"])
+    kw = {}
+    if with_atac:
+        kw.update(n_output_peaks=cfg["n_output_peaks"], target_atac_decoder_mask=cfg["target_atac_mask"],
+                  source_atac_decoder_mask=cfg["source_atac_mask"], gene_peaks_mask=cfg["gene_peaks_mask"])
+    if with_cov:
+        kw.update(cat_covariates_cats=[["sample0", "sample1"], ["a", "b", "c"]],
+                  cat_covariates_no_edges=cfg["cat_covariates_no_edges"],
+                  cat_covariates_embeds_injection=cfg["cat_covariates_embeds_injection"])
+    with quiet():
+        m = ref.modules.VGPGAE(
+            n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+            n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"], n_addon_gp=cfg["n_addon_gp"],
+            cat_covariates_embeds_nums=cfg["cat_covariates_embeds_nums"],
+            n_output_genes=cfg["n_output_genes"],
+            target_rna_decoder_mask=cfg["target_rna_mask"], source_rna_decoder_mask=cfg["source_rna_mask"],
+            features_idx_dict=feat,
+            features_scale_factors=torch.ones(2 * cfg["n_output_genes"]),
+            conv_layer_encoder=cfg["conv_layer"], encoder_n_attention_heads=cfg["heads"],
+            node_label_method=cfg["node_label_method"], active_gp_thresh_ratio=0.01,
+            include_cat_covariates_contrastive_loss=with_cov, **kw)
+    return m.double()
+
+
+def make_batches_mm(adata, x, cats, edge_bs=16, node_bs=8):
+    torch.manual_seed(0)
+    n = adata.n_obs
+    ei = R.adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
+    splits = R.edge_level_split(ei, n, 0.1)
+    train_mask, _ = R.node_level_split_mask(n, 0.1)
+    nl = R.NodeLoaderRef(x, ei, n, train_mask, node_bs, cat_covariates_cats=cats)
+    ll = R.LinkLoaderRef(x, splits["train"].edge_index, n, splits["train"].edge_label_index, edge_bs,
+                         cat_covariates_cats=cats)
+    return next(iter(nl)), next(iter(ll))
+
+
+LAM_MM = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lambda_l1_addon=30.,
+              lambda_group_lasso=2., lambda_gene_expr_recon=300., lambda_chrom_access_recon=100.,
+              lambda_edge_recon=500000., lambda_cat_covariates_contrastive=1000.,
+              contrastive_logits_pos_ratio=0.25, contrastive_logits_neg_ratio=0.25)
+
+
+@pytest.mark.parametrize("with_atac,with_cov,conv_layer,injection", [
+    (False, True, "gatv2conv", ("encoder", "gene_expr_decoder")),          # C3: multi-sample atlas
+    (True, False, "gatv2conv", ()),                                        # C4: RNA + ATAC
+    (True, True, "gcnconv", ("gene_expr_decoder", "chrom_access_decoder")),
+])
+def test_covariates_and_atac_match_reference(with_atac, with_cov, conv_layer, injection):
+    ref = load_reference()
+    adata, cfg, x, cats = H.multimodal_covariate_problem(conv_layer=conv_layer, injection=injection,
+                                                         with_atac=with_atac, with_covariates=with_cov)
+    torch.manual_seed(4)
+    m = build_reference_module_mm(ref, cfg, with_atac, with_cov)
+    m.train()
+    with torch.no_grad():
+        for k, p in m.named_parameters():
+            if k.endswith("bias"):
+                p.uniform_(-0.1, 0.1)
+    params = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point and
+                                                   not k.endswith(("mask", "running_mean_abs_mu")))
+              for k, v in m.state_dict().items()}
+    orc = VGPGAERef(cfg, params)
+    node_b, edge_b = make_batches_mm(adata, x, cats)
+    edge_b.edge_label = edge_b.edge_label.double()      # keep the reference's contrastive BCE in fp64 too
+    P = cfg["n_prior_gp"] + cfg["n_addon_gp"]
+    g = torch.Generator().manual_seed(5)
+    eps_n = torch.randn(node_b.batch_size, P, generator=g, dtype=torch.float64)
+    eps_e = torch.randn(2 * edge_b.edge_label_index.size(1), P, generator=g, dtype=torch.float64)
+    draws = [eps_n, eps_e]
+    real_randn_like = torch.randn_like
+    torch.randn_like = lambda t, *a, **k: draws.pop(0)
+    try:
+        rn = m(data_batch=node_b, decoder="omics")
+        re_ = m(data_batch=copy.deepcopy(edge_b), decoder="graph")
+    finally:
+        torch.randn_like = real_randn_like
+    lam = dict(LAM_MM)
+    if not with_cov:
+        lam["lambda_cat_covariates_contrastive"] = 0.
+    rl = m.loss(edge_model_output=re_, node_model_output=rn, **lam)
+    rl["optim_loss"].backward()
+    on = orc.forward(node_b, "omics", eps=eps_n)
+    oe = orc.forward(copy.deepcopy(edge_b), "graph", eps=eps_e)
+    ol = orc.loss(oe, on, **lam)
+    ol["optim_loss"].backward()
+
+    mods = ["rna"] + (["atac"] if with_atac else [])
+    for mod in mods:
+        for ent in ("target", "source"):
+            assert H.rel_err(on[f"{ent}_{mod}_nb_means"], rn[f"{ent}_{mod}_nb_means"]) < 1e-10, (ent, mod)
+            assert H.rel_err(on["node_labels"][f"{ent}_{mod}"], rn["node_labels"][f"{ent}_{mod}"]) < 1e-12
+    assert H.rel_err(oe["edge_recon_logits"], re_["edge_recon_logits"]) < 1e-10
+    if with_cov:
+        assert torch.equal(oe["edge_incl"], re_["edge_incl"])
+        assert "cat_covariates_contrastive_loss" in rl
+    if with_atac:
+        assert "chrom_access_recon_loss" in rl
+    assert set(ol.keys()) == set(rl.keys())
+    # modules/losses.py:80-81,118: the reference accumulates the contrastive loss into a float32
+    # ``torch.tensor(0.)`` in place, so its value (and the sums containing it) is rounded to fp32
+    fp32_keys = ("cat_covariates_contrastive_loss", "global_loss", "optim_loss") if with_cov else ()
+    for k, v in rl.items():
+        assert H.rel_err(torch.as_tensor(ol[k]), torch.as_tensor(v)) < (2e-7 if k in fp32_keys else 1e-10), k
+    n_checked = 0
+    for k, p in m.named_parameters():
+        if p.grad is None:
+            continue
+        assert params[k].grad is not None, k
+        assert H.rel_err(params[k].grad, p.grad) < 1e-9, k
+        n_checked += 1
+    assert n_checked >= 10
+    m.eval()
+    orc.training = False
+    mu_r = m.get_latent_representation(node_b, only_active_gps=False)
+    mu_o = orc.get_latent_representation(node_b, only_active_gps=False)
+    assert H.rel_err(mu_o, mu_r) < 1e-10

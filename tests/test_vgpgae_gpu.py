@@ -156,3 +156,114 @@ def test_latent_representation_eval():
         mu_c, std_c = mod.get_latent_representation(H.batch_to(node_b, torch.float32, DEV),
                                                     only_active_gps=True, return_mu_std=True)
     assert H.rel_err(mu_c, mu_o) < 1e-5 and H.rel_err(std_c, std_o) < 1e-5
+
+
+# ----------------------------------------------------------------------------- C3 / C4 shapes
+LAM_MM = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lambda_l1_addon=30.,
+              lambda_group_lasso=2., lambda_gene_expr_recon=300., lambda_chrom_access_recon=100.,
+              lambda_edge_recon=500000., lambda_cat_covariates_contrastive=1000.,
+              contrastive_logits_pos_ratio=0.25, contrastive_logits_neg_ratio=0.25)
+
+
+def build_module_mm(cfg, params, with_atac, with_cov):
+    from nichecompass_b200.modules import VGPGAE
+    kw = {}
+    if with_atac:
+        kw.update(n_output_peaks=cfg["n_output_peaks"], target_atac_decoder_mask=cfg["target_atac_mask"],
+                  source_atac_decoder_mask=cfg["source_atac_mask"], gene_peaks_mask=cfg["gene_peaks_mask"])
+    if with_cov:
+        kw.update(cat_covariates_cats=[["sample0", "sample1"], ["a", "b", "c"]],
+                  cat_covariates_no_edges=cfg["cat_covariates_no_edges"],
+                  cat_covariates_embeds_injection=cfg["cat_covariates_embeds_injection"])
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+                   n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"], n_addon_gp=cfg["n_addon_gp"],
+                   cat_covariates_embeds_nums=cfg["cat_covariates_embeds_nums"],
+                   n_output_genes=cfg["n_output_genes"],
+                   target_rna_decoder_mask=cfg["target_rna_mask"], source_rna_decoder_mask=cfg["source_rna_mask"],
+                   features_idx_dict=copy.deepcopy(cfg["features_idx_dict"]),
+                   features_scale_factors=torch.ones(2 * cfg["n_output_genes"]),
+                   conv_layer_encoder=cfg["conv_layer"], encoder_n_attention_heads=cfg["heads"],
+                   node_label_method=cfg["node_label_method"], active_gp_thresh_ratio=0.01,
+                   include_cat_covariates_contrastive_loss=with_cov, **kw)
+    m.load_state_dict({k: v.float() for k, v in params.items()}, strict=True)
+    return m.to(DEV)
+
+
+def run_pair_mm(with_atac, with_cov, conv_layer, injection, dtype):
+    adata, cfg, x, cats = H.multimodal_covariate_problem(conv_layer=conv_layer, injection=injection,
+                                                         with_atac=with_atac, with_covariates=with_cov)
+    p32 = init_params(cfg, seed=7)
+    p64 = {k: v.double().clone().requires_grad_(v.is_floating_point() and not k.endswith(("mask", "abs_mu")))
+           for k, v in p32.items()}
+    orc = VGPGAERef(cfg, p64)
+    mod = build_module_mm(cfg, p32, with_atac, with_cov).set_compute_dtype(dtype)
+    mod.train()
+    torch.manual_seed(0)
+    n = adata.n_obs
+    ei = R.adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
+    splits = R.edge_level_split(ei, n, 0.1)
+    train_mask, _ = R.node_level_split_mask(n, 0.1)
+    node_b = next(iter(R.NodeLoaderRef(x, ei, n, train_mask, 8, cat_covariates_cats=cats)))
+    edge_b = next(iter(R.LinkLoaderRef(x, splits["train"].edge_index, n, splits["train"].edge_label_index, 16,
+                                       cat_covariates_cats=cats)))
+    P = cfg["n_prior_gp"] + cfg["n_addon_gp"]
+    g = torch.Generator().manual_seed(5)
+    eps_n = torch.randn(node_b.batch_size, P, generator=g, dtype=torch.float64)
+    eps_e = torch.randn(2 * edge_b.edge_label_index.size(1), P, generator=g, dtype=torch.float64)
+    lam = dict(LAM_MM)
+    if not with_cov:
+        lam["lambda_cat_covariates_contrastive"] = 0.
+    on = orc.forward(node_b, "omics", eps=eps_n)
+    oe = orc.forward(copy.deepcopy(edge_b), "graph", eps=eps_e)
+    ol = orc.loss(oe, on, **lam)
+    ol["optim_loss"].backward()
+    mod._eps_queue = [eps_n, eps_e]
+    cn = mod(H.batch_to(node_b, torch.float32, DEV), "omics")
+    ce = mod(H.batch_to(copy.deepcopy(edge_b), torch.float32, DEV), "graph")
+    cl = mod.loss(ce, cn, **lam)
+    cl["optim_loss"].backward()
+    return orc, mod, (on, oe, ol), (cn, ce, cl), p64
+
+
+@pytest.mark.parametrize("with_atac,with_cov,conv_layer,injection", [
+    (False, True, "gatv2conv", ("encoder", "gene_expr_decoder")),          # C3: multi-sample atlas
+    (True, False, "gatv2conv", ()),                                        # C4: RNA + ATAC
+    (True, True, "gcnconv", ("gene_expr_decoder", "chrom_access_decoder")),
+])
+def test_fp32_covariates_and_atac(with_atac, with_cov, conv_layer, injection):
+    orc, mod, (on, oe, ol), (cn, ce, cl), p64 = run_pair_mm(with_atac, with_cov, conv_layer, injection,
+                                                            torch.float32)
+    tol = 1e-5
+    mods = ["rna"] + (["atac"] if with_atac else [])
+    for k in ("mu", "logstd"):
+        assert H.rel_err(cn[k], on[k]) < tol and H.rel_err(ce[k], oe[k]) < tol, k
+    for m_ in mods:
+        for ent in ("target", "source"):
+            assert H.rel_err(cn[f"{ent}_{m_}_nb_means"], on[f"{ent}_{m_}_nb_means"]) < tol, (ent, m_)
+            assert H.rel_err(cn["node_labels"][f"{ent}_{m_}"], on["node_labels"][f"{ent}_{m_}"]) < 1e-6
+    assert H.rel_err(ce["edge_recon_logits"], oe["edge_recon_logits"]) < tol
+    if with_cov:
+        assert torch.equal(ce["edge_incl"].cpu(), oe["edge_incl"])
+    assert set(cl.keys()) == set(ol.keys())
+    for k, v in ol.items():
+        assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(v)) < tol, k
+    checked = 0
+    for k, p in mod.named_parameters():
+        ref = p64[k].grad
+        if ref is None:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+            continue
+        assert p.grad is not None, k
+        assert H.rel_err(p.grad, ref) < 2e-5, k
+        checked += 1
+    assert checked >= 10
+
+
+def test_bf16_covariates_and_atac_losses():
+    orc, mod, (on, oe, ol), (cn, ce, cl), _ = run_pair_mm(True, True, "gatv2conv",
+                                                         ("encoder", "gene_expr_decoder", "chrom_access_decoder"),
+                                                         torch.bfloat16)
+    for k in ("global_loss", "optim_loss", "edge_recon_loss", "gene_expr_recon_loss", "chrom_access_recon_loss",
+              "kl_reg_loss"):
+        assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(ol[k])) < 2e-3, k
