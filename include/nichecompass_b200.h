@@ -146,7 +146,17 @@ int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t ld, const fl
                  const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
                  int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
                  void* stream);
-/* Backward of the above.  rptr/rdst/rslot: nc_reverse_csr(..., add_self=1) of the same graph.
+/* Forward only, over a TILE of targets of a large resident graph (full-graph latent inference,
+ * models/nichecompass.py:1264-1381 / modules/vgpgae.py:1368-1437 without the loader's per-batch
+ * recomputation): targets are rows [dst_off, dst_off + n_dst) of rowptr and -- for the self edge --
+ * of xl; xr [n_dst, ld] and out [n_dst, ldo] hold the tile only.  col indexes xl rows.  No
+ * attention coefficients are stored.                                                          */
+int nc_gatv2_fwd_tile(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
+                      const float* bias, const int32_t* rowptr, const int32_t* col, int32_t dst_off,
+                      int32_t n_dst, const int32_t* seg, const int32_t* seg_host, int32_t n_conv,
+                      int32_t H, int32_t max_deg, float neg_slope, float* out, int64_t ldo,
+                      void* stream);
+/* Backward of nc_gatv2_fwd.  rptr/rdst/rslot: nc_reverse_csr(..., add_self=1) of the same graph.
  * dxl [n_src, ld] and dxr [n_dst, ld] (same dtype as xl) are fully overwritten; datt (indexed
  * like att) and dbias (indexed like out columns, may be NULL) are ACCUMULATED with atomics.
  * ds_ws: fp32 workspace of the size of alpha.                                               */

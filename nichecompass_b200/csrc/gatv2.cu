@@ -59,23 +59,25 @@ __global__ void __launch_bounds__(GT)
 k_gatv2_fwd(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, const float* __restrict__ att,
             const float* __restrict__ bias, const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
             const int32_t* __restrict__ seg, int n_conv, int H, int max_deg, float slope,
-            float* __restrict__ out, int64_t ldo, float* __restrict__ alpha, int self_mode) {
+            float* __restrict__ out, int64_t ldo, float* __restrict__ alpha, int self_mode, int dst_off) {
     // self_mode 1: PyG GATv2Conv (existing self entries dropped, one self edge appended per target);
-    // self_mode 0: edges exactly as given (attention node-label aggregator); out == NULL: alpha only
+    // self_mode 0: edges exactly as given (attention node-label aggregator); out == NULL: alpha only.
+    // dst_off: targets are rows [dst_off, dst_off + gridDim.x) of rowptr / xl; xr and out hold the tile
+    // only (row blockIdx.x).  alpha == NULL (inference tiles): coefficients are not stored.
     extern __shared__ float s_mem[];
     const int stride = max_deg + 1;
     float* s_sc = s_mem;                               // [H][stride]
     int* s_j = (int*)(s_mem + H * stride);             // [stride]
-    const int i = blockIdx.x, c = blockIdx.y;
+    const int ir = blockIdx.x, i = ir + dst_off, c = blockIdx.y;
     const Seg sg = load_seg(seg, c);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int e0 = rowptr[i], e1 = rowptr[i + 1];
     const int nE = e1 - e0 + self_mode;
     const int NCH = n_conv * H;
     for (int t = tid; t < nE; t += GT) s_j[t] = (t < e1 - e0) ? col[e0 + t] : i;
-    if (!self_mode && tid < H) alpha[(int64_t)(e1 + i) * NCH + c * H + tid] = 0.f;   // unused self slot
+    if (!self_mode && alpha && tid < H) alpha[(int64_t)(e1 + i) * NCH + c * H + tid] = 0.f;   // unused self slot
     __syncthreads();
-    const T* xri = xr + (int64_t)i * ld + sg.off;
+    const T* xri = xr + (int64_t)ir * ld + sg.off;
     // pass 1: raw attention scores, one warp per incoming edge
     for (int t = warp; t < nE; t += GT / 32) {
         const int j = s_j[t];
@@ -109,7 +111,7 @@ k_gatv2_fwd(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, cons
         for (int t = lane; t < nE; t += 32) {
             const float a = expf(s_sc[h * stride + t] - m) / s;
             s_sc[h * stride + t] = a;
-            alpha[(int64_t)(e0 + i + t) * NCH + c * H + h] = a;
+            if (alpha) alpha[(int64_t)(e0 + i + t) * NCH + c * H + h] = a;
         }
     }
     __syncthreads();
@@ -131,7 +133,7 @@ k_gatv2_fwd(const T* __restrict__ xl, const T* __restrict__ xr, int64_t ld, cons
         if (bias) b = ldf<false>(bias + sg.out_off, k, sg.C);
         acc.x = acc.x * invH + b.x; acc.y = acc.y * invH + b.y;
         acc.z = acc.z * invH + b.z; acc.w = acc.w * invH + b.w;
-        stv<float, false>(out + (int64_t)i * ldo + sg.out_off, k, sg.C, acc);
+        stv<float, false>(out + (int64_t)ir * ldo + sg.out_off, k, sg.C, acc);
     }
 }
 
@@ -180,7 +182,8 @@ __global__ void __launch_bounds__(FS_NT, 2)
 k_gatv2_fwd_stream(const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __restrict__ xr, int64_t ld,
                    const float* __restrict__ att, const float* __restrict__ bias, const int32_t* __restrict__ rowptr,
                    const int32_t* __restrict__ col, const int32_t* __restrict__ seg, int n_conv, int H, int max_deg,
-                   int seg_stride, float slope, float* __restrict__ out, int64_t ldo, float* __restrict__ alpha) {
+                   int seg_stride, float slope, float* __restrict__ out, int64_t ldo, float* __restrict__ alpha,
+                   int dst_off) {
     extern __shared__ __align__(128) uint8_t fs_smem[];
     const int stride = max_deg + 1;
     uint8_t* ring = fs_smem;                                              // FS_STAGES * seg_stride bytes
@@ -191,7 +194,7 @@ k_gatv2_fwd_stream(const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __
     uint64_t* full = (uint64_t*)(((uintptr_t)(s_red + 2 * (FS_NT / 32)) + 7) & ~(uintptr_t)7);
     __shared__ int s_nv;
 
-    const int i = blockIdx.x, c = blockIdx.y;
+    const int ir = blockIdx.x, i = ir + dst_off, c = blockIdx.y;   // see k_gatv2_fwd for dst_off / NULL alpha
     const Seg sg = load_seg(seg, c);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int TPH = FS_NT / H, h = tid / TPH, lt = tid - h * TPH;         // TPH is a multiple of 32
@@ -225,7 +228,7 @@ k_gatv2_fwd_stream(const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __
     }
     // per-thread constants: x_r[i] and att of the owned vectors
     float4 xr4[NV], at4[NV], acc[NV];
-    const __nv_bfloat16* xri = xr + (int64_t)i * ld + sg.off + h * sg.C;
+    const __nv_bfloat16* xri = xr + (int64_t)ir * ld + sg.off + h * sg.C;
     const float* atth = att + sg.off + h * sg.C;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
@@ -285,8 +288,9 @@ k_gatv2_fwd_stream(const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __
     __syncthreads();                           // s_e complete, ring free for the head-mean staging
     const float inv_l = 1.0f / (l_run + 1e-16f);
     // attention coefficients of every slot of this target (0 for the removed self entries)
-    for (int t = lt; t < nE; t += TPH)
-        alpha[(int64_t)(e0 + i + t) * NCH + c * H + h] = expf(s_e[h * stride + t] - m_run) * inv_l;
+    if (alpha)
+        for (int t = lt; t < nE; t += TPH)
+            alpha[(int64_t)(e0 + i + t) * NCH + c * H + h] = expf(s_e[h * stride + t] - m_run) * inv_l;
     float* s_o = (float*)ring;                 // [H][C]
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
@@ -300,7 +304,7 @@ k_gatv2_fwd_stream(const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __
     for (int k = tid; k < sg.C; k += FS_NT) {
         float v = 0.f;
         for (int hh = 0; hh < H; ++hh) v += s_o[hh * sg.C + k];
-        out[(int64_t)i * ldo + sg.out_off + k] = v * invH + (bias ? __ldg(bias + sg.out_off + k) : 0.f);
+        out[(int64_t)ir * ldo + sg.out_off + k] = v * invH + (bias ? __ldg(bias + sg.out_off + k) : 0.f);
     }
 }
 
@@ -640,11 +644,11 @@ bool stream_ok(const void* xl, int64_t ld, const int32_t* seg_host, int n_conv, 
 }
 }  // namespace
 
-extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
-                            const float* bias, const int32_t* rowptr, const int32_t* col, int32_t n_dst,
-                            const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
-                            int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
-                            void* stream) {
+static int gatv2_fwd_impl(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
+                          const float* bias, const int32_t* rowptr, const int32_t* col, int32_t dst_off, int32_t n_dst,
+                          const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
+                          int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
+                          void* stream) {
     NC_REQUIRE(n_dst >= 0 && n_conv > 0 && H > 0 && max_deg >= 0, NC_ESHAPE, "nc_gatv2_fwd: bad sizes");
     NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_gatv2_fwd: bad dtype %d", dtype);
     if (n_dst == 0) return NC_OK;
@@ -671,7 +675,7 @@ extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t l
         }                                                                                                            \
         k_gatv2_fwd_stream<NV><<<grid, FS_NT, sm, s>>>((const __nv_bfloat16*)xl, (const __nv_bfloat16*)xr, ld, att, \
                                                        bias, rowptr, col, seg, n_conv, H, max_deg, seg_stride,       \
-                                                       neg_slope, out, ldo, alpha);                                  \
+                                                       neg_slope, out, ldo, alpha, dst_off);                         \
     } while (0)
             if (nv <= 2) LS(2); else if (nv <= 4) LS(4); else if (nv <= 6) LS(6); else LS(8);
 #undef LS
@@ -680,13 +684,36 @@ extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t l
             return NC_OK;
         }
     }
-#define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, bias, rowptr, col, seg, n_conv, H, max_deg, neg_slope, out, ldo, alpha, 1)
+#define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)xl, (const T*)xr, ld, att, bias, rowptr, col, seg, n_conv, H, max_deg, neg_slope, out, ldo, alpha, 1, dst_off)
     if (dtype == NC_F32) { if (v) L(float, true); else L(float, false); }
     else { if (v) L(__nv_bfloat16, true); else L(__nv_bfloat16, false); }
 #undef L
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_gatv2_fwd");
     return NC_OK;
+}
+
+extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
+                            const float* bias, const int32_t* rowptr, const int32_t* col, int32_t n_dst,
+                            const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
+                            int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
+                            void* stream) {
+    NC_REQUIRE(alpha != nullptr, NC_EINVAL, "nc_gatv2_fwd: alpha must be given (the backward consumes it)");
+    return gatv2_fwd_impl(xl, xr, dtype, ld, att, bias, rowptr, col, 0, n_dst, seg, seg_host, n_conv, H, max_deg,
+                          neg_slope, out, ldo, alpha, stream);
+}
+
+// Inference over a tile of targets of a large resident graph: targets are rows
+// [dst_off, dst_off + n_dst) of rowptr (and of xl, for the self edge); xr and out hold the tile only.
+// No attention coefficients are stored.
+extern "C" int nc_gatv2_fwd_tile(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
+                                 const float* bias, const int32_t* rowptr, const int32_t* col, int32_t dst_off,
+                                 int32_t n_dst, const int32_t* seg, const int32_t* seg_host, int32_t n_conv,
+                                 int32_t H, int32_t max_deg, float neg_slope, float* out, int64_t ldo,
+                                 void* stream) {
+    NC_REQUIRE(dst_off >= 0 && out != nullptr, NC_EINVAL, "nc_gatv2_fwd_tile: bad dst_off / out");
+    return gatv2_fwd_impl(xl, xr, dtype, ld, att, bias, rowptr, col, dst_off, n_dst, seg, seg_host, n_conv, H,
+                          max_deg, neg_slope, out, ldo, nullptr, stream);
 }
 
 extern "C" int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
@@ -813,7 +840,7 @@ extern "C" int nc_attn_agg_fwd(const void* gl, const void* gr, int dtype, int64_
     const int32_t seg_host[4] = {0, F, 0, 0};
     dim3 grid(n_dst, 1);
     const bool v = vec_ok(gl, gr, ld, seg_host, 1, dtype == NC_F32 ? 4 : 2) && ((uintptr_t)attn % 16 == 0);
-#define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)gl, (const T*)gr, ld, attn, nullptr, rowptr, col, seg, 1, H, max_deg, neg_slope, nullptr, 0, alpha, 0)
+#define L(T, V) k_gatv2_fwd<T, V><<<grid, GT, smem, s>>>((const T*)gl, (const T*)gr, ld, attn, nullptr, rowptr, col, seg, 1, H, max_deg, neg_slope, nullptr, 0, alpha, 0, 0)
     if (dtype == NC_F32) { if (v) L(float, true); else L(float, false); }
     else { if (v) L(__nv_bfloat16, true); else L(__nv_bfloat16, false); }
 #undef L

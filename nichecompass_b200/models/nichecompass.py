@@ -445,9 +445,17 @@ class NicheCompass(BaseModelMixin):
                                   return_mu_std: bool = False,
                                   node_batch_size: int = 64,
                                   dtype: type = np.float64,
+                                  layerwise: Optional[bool] = None,
+                                  partition: str = "auto",
                                   ) -> Union[np.ndarray, Tuple[np.ndarray, np.ndarray]]:
         """Latent representation (gene-program scores) of every observation
         (models/nichecompass.py:1264-1381).
+
+        ``layerwise`` / ``partition`` are extensions of this build: with the 1-layer GATv2 encoder the
+        default is the layer-wise full-graph path of ``models/tiled_inference.py`` (every node's
+        ``fc_l1`` / ``lin_l`` rows computed once; with ``torch.distributed`` initialised the nodes are
+        split into spatial tiles, one per rank, and boundary ``hidden`` rows are exchanged over NCCL;
+        every rank returns the full array).  ``layerwise=False`` forces the loader walk below.
 
         The reference walks a ``NeighborLoader`` over consecutive blocks of ``node_batch_size``
         nodes.  With the GATv2 encoder and all neighbours sampled, a node's output does not depend
@@ -473,6 +481,15 @@ class NicheCompass(BaseModelMixin):
             node_val_ratio=0.,
             node_test_ratio=0.,
             device=device)
+        from . import tiled_inference as TI
+        if layerwise is None:
+            layerwise = TI.supports(self.model)
+        elif layerwise and not TI.supports(self.model):
+            raise ValueError("layerwise inference needs the 1-layer GATv2 encoder (outputs of the GCN encoder "
+                             "depend on the sampled batch: SURVEY.md App. B-6)")
+        if layerwise:
+            return self._latent_layerwise(adata, data_dict["node_masked_data"], only_active_gps, return_mu_std,
+                                          dtype, partition, adj_key)
         tile = node_batch_size
         if self.model.conv_layer_encoder_ == "gatv2conv" and self.model.n_layers_encoder_ == 1:
             tile = max(node_batch_size, 8192)
@@ -501,6 +518,57 @@ class NicheCompass(BaseModelMixin):
             lo = hi
         self.model.train(was_training)
         host = [o.cpu().numpy() for o in outs]
+        return (host[0], host[1]) if return_mu_std else host[0]
+
+    def _latent_layerwise(self, adata, data, only_active_gps, return_mu_std, dtype, partition, adj_key):
+        """Layer-wise full-graph inference over spatial tiles (models/tiled_inference.py)."""
+        import torch.distributed as dist
+        from . import tiled_inference as TI
+        device = next(self.model.parameters()).device
+        dist_on = dist.is_available() and dist.is_initialized()
+        rank, world = (dist.get_rank(), dist.get_world_size()) if dist_on else (0, 1)
+        n_obs = adata.shape[0]
+        if partition == "auto" and world == 1:
+            partition = "none"
+        obsm = getattr(adata, "obsm", None)
+        coords = obsm["spatial"] if (obsm is not None and "spatial" in obsm) else None
+        perm_np = TI.partition_order(n_obs, coords, adata.obsp[adj_key], partition)
+        bounds = TI.tile_bounds(n_obs, world)
+        perm = torch.from_numpy(perm_np).to(device)
+        inv = torch.empty_like(perm)
+        inv[perm] = torch.arange(n_obs, device=device)
+        g = data.device_graph()
+        lo, hi = bounds[rank], bounds[rank + 1]
+        lg = TI.build_local_graph(g.rowptr, g.col, perm, inv, lo, hi)
+        was_training = self.model.training
+        self.model.eval()
+        ml = TI.encode_partition(self.model, data.store, lg, perm[lo:hi], bounds, data.cats_device(),
+                                 want_logstd=return_mu_std)
+        P = self.n_prior_gp_ + self.n_addon_gp_
+        parts = [ml[:, :P]] + ([torch.exp(ml[:, P:])] if return_mu_std else [])
+        if only_active_gps:
+            a = self.model.get_active_gp_mask()
+            parts = [p_[:, a] for p_ in parts]
+        self.model.train(was_training)
+        tdt = {np.float16: torch.float16, np.float32: torch.float32, np.float64: torch.float64}.get(dtype)
+        if tdt is None:
+            tdt = torch.from_numpy(np.empty(0, dtype=dtype)).dtype
+        self.last_inference_stats_ = {"n_own": lg.n_own, "n_halo": lg.n_halo, "rank": rank, "world": world}
+        host = []
+        for part in parts:
+            part = part.to(tdt).contiguous()
+            full = torch.empty(n_obs, part.size(1), dtype=tdt, device=device)
+            if world == 1:
+                full[perm] = part
+            else:
+                n_max = max(bounds[r + 1] - bounds[r] for r in range(world))
+                mine = torch.zeros(n_max, part.size(1), dtype=tdt, device=device)
+                mine[:part.size(0)] = part
+                everyone = torch.empty(world * n_max, part.size(1), dtype=tdt, device=device)
+                dist.all_gather_into_tensor(everyone, mine)
+                for r in range(world):
+                    full[perm[bounds[r]:bounds[r + 1]]] = everyone[r * n_max:r * n_max + bounds[r + 1] - bounds[r]]
+            host.append(full.cpu().numpy())
         return (host[0], host[1]) if return_mu_std else host[0]
 
     # ------------------------------------------------------------------ out of scope

@@ -140,3 +140,32 @@ def test_nichecompass_train_latent_save_load(tmp_path):
     assert all(v == ("addon" in n or "theta" in n or "aggregator" in n) for n, v in flags.items())
     lat2 = loaded.get_latent_representation(adata, only_active_gps=True, node_batch_size=64)
     assert np.allclose(lat2, lat, rtol=1e-6, atol=1e-7)
+
+
+def test_layerwise_inference_equals_loader_walk():
+    """models/tiled_inference.py (every node's hidden / x_l rows computed once, spatially ordered
+    tiles) against the reference-shaped loader walk, and against the CPU oracle."""
+    from nichecompass_b200.models import NicheCompass
+    adata = H.tiny_problem(n_cells=500, n_genes=48, n_prior_gp=12, lib_mean=80., n_samples=2)
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = NicheCompass(adata, n_addon_gp=4, active_gp_thresh_ratio=0.01, cat_covariates_keys=["batch"],
+                             cat_covariates_embeds_injection=["encoder", "gene_expr_decoder"],
+                             cat_covariates_embeds_nums=[3], cat_covariates_no_edges=[True])
+        model.train(n_epochs=2, n_epochs_all_gps=1, edge_batch_size=64, verbose=False)
+    kw = dict(adata=adata, cat_covariates_keys=["batch"], only_active_gps=False, dtype=np.float32)
+    walk_mu, walk_std = model.get_latent_representation(layerwise=False, return_mu_std=True, **kw)
+    for part in ("none", "spatial", "rcm"):
+        mu, std = model.get_latent_representation(layerwise=True, partition=part, return_mu_std=True, **kw)
+        assert mu.shape == walk_mu.shape == (500, 16)
+        assert np.allclose(mu, walk_mu, rtol=1e-5, atol=1e-6), part
+        assert np.allclose(std, walk_std, rtol=1e-5, atol=1e-6), part
+    only_mu = model.get_latent_representation(layerwise=True, partition="spatial", **kw)
+    assert np.allclose(only_mu, walk_mu, rtol=1e-5, atol=1e-6)
+    act = model.get_latent_representation(adata=adata, cat_covariates_keys=["batch"], only_active_gps=True,
+                                          dtype=np.float16)
+    assert act.dtype == np.float16 and act.shape[1] == len(model.get_active_gps())
+    assert model.last_inference_stats_["n_halo"] == 0 and model.last_inference_stats_["n_own"] == 500
+    # bf16 compute mode: same path, bf16 rounding of the activations
+    model.model.set_compute_dtype(torch.bfloat16)
+    mu_bf = model.get_latent_representation(layerwise=True, partition="spatial", **kw)
+    assert np.abs(mu_bf - walk_mu).max() < 3e-2 * np.abs(walk_mu).max()
