@@ -13,6 +13,7 @@
 // Replaces the cuBLAS call sites nn/encoders.py:179 (fc_l1), PyG GATv2Conv lin_l/lin_r,
 // GCNConv lin, nn/layercomponents.py:77-80 (MaskedLinear) and all their backward GEMMs.
 #include <cuda.h>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -26,10 +27,15 @@ constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 192;
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 
-template <int BN> struct Cfg {
-    static constexpr int B_STAGE_BYTES = BN * BK * 2;
+// NCTA = 2: one 256 x BN output tile per CTA PAIR (thread-block cluster of two SMs of a TPC), computed by
+// tcgen05.mma.cta_group::2 issued by the leader CTA: each CTA stages its own 128 rows of A and HALF of the
+// B tile (BN/2 rows), so a k-block costs 32 KB of L2->smem traffic per SM instead of 48 KB and the ring is
+// six stages deep; each CTA's TMEM receives its 128 accumulator rows and runs its own epilogue.
+template <int BN, int NCTA = 1> struct Cfg {
+    static constexpr int B_ROWS = BN / NCTA;       // rows of the B tile this CTA stages
+    static constexpr int B_STAGE_BYTES = B_ROWS * BK * 2;
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-    static constexpr int STAGES = (BN == 256) ? 4 : 6;
+    static constexpr int STAGES = (B_ROWS == 256) ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN;       // two accumulator stages (power of two)
     static constexpr int STAGING_BYTES = 4 /*warps*/ * 2 /*buffers*/ * 4096;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 /*align*/ + 256 /*barriers*/;
@@ -45,6 +51,7 @@ struct Epilogue {
     int bias_vec;      // bias is 16-byte aligned
     int mask_vec;      // mask rows are 16-byte aligned
     int splits;        // K splits per output tile
+    int band;          // tile rows per raster band (see item_to_tile)
 };
 
 // ------------------------------------------------------------------------- PTX wrappers
@@ -79,6 +86,57 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* tm, ui
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
         ::"r"(smem_u32(dst)), "l"((uint64_t)tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
+}
+// CTA-pair variants: the load lands in this CTA's smem, its bytes are counted on the LEADER's barrier
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* tm, uint32_t leader_bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"((uint64_t)tm), "r"(leader_bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {      // shared::cta -> shared::cluster
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {      // arrives on the same barrier of both CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
+// Raster order of the persistent schedule.  Concurrent work items (consecutive item ids) cover a BAND of
+// `band` tile rows x all tile columns, so one wave touches band/num_m of A and all of B: an operand larger
+// than L2 is streamed from HBM once instead of once per tile column.
+__device__ __forceinline__ void item_to_tile(int item, int splits, int num_m, int num_n, int band, int& tm, int& tn,
+                                             int& split) {
+    const int tile = item / splits;
+    split = item - tile * splits;
+    const int per_band = band * num_n;
+    const int b = tile / per_band, r = tile - b * per_band;
+    const int rows = min(band, num_m - b * band);
+    tn = r / rows;
+    tm = b * band + (r - tn * rows);
 }
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* src, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
@@ -194,11 +252,12 @@ __device__ __forceinline__ void epi_flush(const Epilogue& e, const CUtensorMap* 
 }
 
 // ------------------------------------------------------------------------- the kernel
-template <int BN, bool TA, bool TB>
+template <int BN, bool TA, bool TB, int NCTA>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmC, const Epilogue epi, int M, int N, int K) {
-    using C = Cfg<BN>;
+    using C = Cfg<BN, NCTA>;
+    constexpr int TILE_M = BM * NCTA;                     // output rows per work item (CTA or CTA pair)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* smem_a = smem;
@@ -212,10 +271,13 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     uint32_t* tmem_base_slot = (uint32_t*)(tmem_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_m = (M + BM - 1) / BM, num_n = (N + BN - 1) / BN;
+    const uint32_t cta_rank = (NCTA == 2) ? cluster_ctarank() : 0u;
+    const bool leader = cta_rank == 0;
+    const int unit = blockIdx.x / NCTA, n_units = gridDim.x / NCTA;       // work is dealt to CTAs / CTA pairs
+    const int num_m = (M + TILE_M - 1) / TILE_M, num_n = (N + BN - 1) / BN;
     const int num_kb = (K + BK - 1) / BK;
     const int splits = epi.splits;
-    const int num_items = num_m * num_n * splits;       // item = tile * splits + split
+    const int num_items = num_m * num_n * splits;
     const int kb_per = (num_kb + splits - 1) / splits;
 
     if (warp == 0 && lane == 0) {
@@ -228,63 +290,90 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], 128);
+            mbar_init(&tmem_empty[s], 128 * NCTA);        // the epilogue threads of every CTA of the pair
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_slot)),
-                     "r"((uint32_t)C::TMEM_COLS)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (NCTA == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_slot)),
+                         "r"((uint32_t)C::TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_base_slot)),
+                         "r"((uint32_t)C::TMEM_COLS) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     tcgen05_fence_before();
-    __syncthreads();
+    if (NCTA == 2) cluster_sync_all(); else __syncthreads();
     tcgen05_fence_after();
     const uint32_t tmem_base = *tmem_base_slot;
 
     if (warp == 0) {
-        // ===================================================== TMA producer
+        // ===================================================== TMA producer (every CTA stages its own operands)
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-                const int tile = item / splits, split = item - tile * splits;
-                const int m0 = (tile % num_m) * BM, n0 = (tile / num_m) * BN;
+            for (int item = unit; item < num_items; item += n_units) {
+                int tm, tn, split;
+                item_to_tile(item, splits, num_m, num_n, epi.band, tm, tn, split);
+                const int m0 = tm * TILE_M + (int)cta_rank * BM;
+                const int n0 = tn * BN + (int)cta_rank * C::B_ROWS;
                 const int kb0 = split * kb_per, kb1 = min(num_kb, kb0 + kb_per);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
                     uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
                     uint8_t* sb = smem_b + stage * C::B_STAGE_BYTES;
                     const int k0 = kb * BK;
-                    if (TA) {
+                    if (NCTA == 2) {
+                        // the leader's barrier counts the bytes of both CTAs
+                        if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::STAGE_BYTES);
+                        const uint32_t lbar = map_to_cta(smem_u32(&full_bar[stage]), 0);
+                        if (TA) {
 #pragma unroll
-                        for (int s = 0; s < BM / 64; ++s)
-                            tma_load_2d(sa + s * (BK * 128), &tmA, &full_bar[stage], m0 + s * 64, k0);
-                    } else {
-                        tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
-                    }
-                    if (TB) {
+                            for (int s = 0; s < BM / 64; ++s)
+                                tma_load_2d_pair(sa + s * (BK * 128), &tmA, lbar, m0 + s * 64, k0);
+                        } else {
+                            tma_load_2d_pair(sa, &tmA, lbar, k0, m0);
+                        }
+                        if (TB) {
 #pragma unroll
-                        for (int s = 0; s < BN / 64; ++s)
-                            tma_load_2d(sb + s * (BK * 128), &tmB, &full_bar[stage], n0 + s * 64, k0);
+                            for (int s = 0; s < C::B_ROWS / 64; ++s)
+                                tma_load_2d_pair(sb + s * (BK * 128), &tmB, lbar, n0 + s * 64, k0);
+                        } else {
+                            tma_load_2d_pair(sb, &tmB, lbar, k0, n0);
+                        }
                     } else {
-                        tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+                        mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                        if (TA) {
+#pragma unroll
+                            for (int s = 0; s < BM / 64; ++s)
+                                tma_load_2d(sa + s * (BK * 128), &tmA, &full_bar[stage], m0 + s * 64, k0);
+                        } else {
+                            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+                        }
+                        if (TB) {
+#pragma unroll
+                            for (int s = 0; s < BN / 64; ++s)
+                                tma_load_2d(sb + s * (BK * 128), &tmB, &full_bar[stage], n0 + s * 64, k0);
+                        } else {
+                            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+                        }
                     }
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc(BM, BN, TA, TB);
+        // ===================================================== MMA issuer (one lane; the leader CTA of a pair)
+        if (lane == 0 && leader) {
+            constexpr uint32_t idesc = make_idesc(TILE_M, BN, TA, TB);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+            for (int item = unit; item < num_items; item += n_units) {
                 const int split = item % splits;
                 const int kb0 = split * kb_per, kb1 = min(num_kb, kb0 + kb_per);
                 mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
@@ -304,25 +393,28 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                                   : make_desc(sa + k * 32, 16, 1024);
                         const uint64_t bdesc = TB ? make_desc(sb + k * 2048, BK * 128, 1024)
                                                   : make_desc(sb + k * 32, 16, 1024);
-                        umma_bf16(d_tmem, adesc, bdesc, idesc, ((kb - kb0) | k) != 0);
+                        if (NCTA == 2) umma_bf16_pair(d_tmem, adesc, bdesc, idesc, ((kb - kb0) | k) != 0);
+                        else umma_bf16(d_tmem, adesc, bdesc, idesc, ((kb - kb0) | k) != 0);
                     }
-                    umma_commit(&empty_bar[stage]);          // frees the smem slot when the MMAs retire
+                    // frees the smem slot (of both CTAs) when the MMAs retire
+                    if (NCTA == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&tmem_full[acc]);                // accumulator complete
+                if (NCTA == 2) umma_commit_pair(&tmem_full[acc]); else umma_commit(&tmem_full[acc]);   // accumulator complete
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
     } else {
-        // ===================================================== epilogue (warps 2..5)
+        // ===================================================== epilogue (warps 2..5), own 128 rows of the tile
         const int q = warp & 3;                              // TMEM lane quarter of this warp
         uint8_t* my_stage = smem_stage + q * 8192;
         int buf = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-            const int tile = item / splits, split = item - tile * splits;
-            const int m0 = (tile % num_m) * BM, n0 = (tile / num_m) * BN;
+        for (int item = unit; item < num_items; item += n_units) {
+            int tm, tn, split;
+            item_to_tile(item, splits, num_m, num_n, epi.band, tm, tn, split);
+            const int m0 = tm * TILE_M + (int)cta_rank * BM, n0 = tn * BN;
             const bool has_k = split * kb_per < num_kb;      // trailing splits can be empty
             mbar_wait(&tmem_full[acc], acc_phase);
             tcgen05_fence_after();
@@ -373,17 +465,24 @@ k_gemm_bf16(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 }
             }
             tcgen05_fence_before();
-            mbar_arrive(&tmem_empty[acc]);
+            // the MMA issuer (leader CTA) may overwrite this accumulator stage once both CTAs have drained it
+            if (NCTA == 2) mbar_arrive_cluster(map_to_cta(smem_u32(&tmem_empty[acc]), 0));
+            else mbar_arrive(&tmem_empty[acc]);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (lane == 0) bulk_wait_all();                      // staging buffers must outlive the bulk reads
     }
     tcgen05_fence_before();
-    __syncthreads();
+    // pair: neither CTA may exit (or free TMEM) while the other can still signal its barriers / read its smem
+    if (NCTA == 2) cluster_sync_all(); else __syncthreads();
     if (warp == 1) {
         tcgen05_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
-                     : "memory");
+        if (NCTA == 2)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
+                         : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)C::TMEM_COLS)
+                         : "memory");
     }
 }
 
@@ -424,21 +523,49 @@ int make_tmap(CUtensorMap* tm, const void* ptr, int64_t inner, int64_t outer, in
     return NC_OK;
 }
 
-template <int BN, bool TA, bool TB>
-int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Epilogue& epi, int M, int N,
+template <int BN, bool TA, bool TB, int NCTA>
+int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, Epilogue epi, int M, int N,
            int K, cudaStream_t s) {
+    using C = Cfg<BN, NCTA>;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_gemm_bf16<BN, TA, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             Cfg<BN>::SMEM_BYTES);
-        if (e != cudaSuccess) { nc_set_error("nc_gemm_bf16: cannot opt in to %d B smem: %s", Cfg<BN>::SMEM_BYTES, cudaGetErrorString(e)); return NC_ECUDA; }
+        cudaError_t e = cudaFuncSetAttribute(k_gemm_bf16<BN, TA, TB, NCTA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             C::SMEM_BYTES);
+        if (e != cudaSuccess) { nc_set_error("nc_gemm_bf16: cannot opt in to %d B smem: %s", C::SMEM_BYTES, cudaGetErrorString(e)); return NC_ECUDA; }
         attr_set = true;
     }
-    const int items = (int)(nc_cdiv(M, BM) * nc_cdiv(N, BN)) * epi.splits;
-    const int grid = items < nc_num_sms() ? items : nc_num_sms();
-    k_gemm_bf16<BN, TA, TB><<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, s>>>(tmA, tmB, tmC, epi, M, N, K);
+    const int num_m = (int)nc_cdiv(M, BM * NCTA), num_n = (int)nc_cdiv(N, BN);
+    const int items = num_m * num_n * epi.splits;
+    const int max_units = nc_num_sms() / NCTA;
+    const int units = items < max_units ? items : max_units;
+    int band = (int)nc_cdiv(units, num_n);                   // one wave ~ band tile rows x all tile columns
+    epi.band = band < 1 ? 1 : (band > num_m ? num_m : band);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(units * NCTA));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = NCTA;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = NCTA > 1 ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, k_gemm_bf16<BN, TA, TB, NCTA>, tmA, tmB, tmC, epi, M, N, K);
+    if (e != cudaSuccess) { nc_set_error("nc_gemm_bf16: launch failed: %s", cudaGetErrorString(e)); return NC_ECUDA; }
     nc_count_launch(1);
     return NC_OK;
+}
+
+// NC_GEMM_PAIR=0 disables the CTA-pair (cta_group::2) configuration (A/B measurements)
+bool pair_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("NC_GEMM_PAIR");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
 }
 
 }  // namespace
@@ -461,13 +588,16 @@ extern "C" int nc_gemm_bf16(const void* A, int64_t lda, int trans_a, const void*
     const int64_t tiles256 = nc_cdiv(M, BM) * nc_cdiv(N, 256);
     const bool wide = tiles256 >= 2 * (int64_t)nc_num_sms() || (N % 256 == 0 && tiles256 >= nc_num_sms());
     const int BNsel = wide ? 256 : 128;
+    // CTA pairs (256 x 256 tiles, cta_group::2) as soon as they give every pair of SMs a tile
+    const int64_t pair_tiles = nc_cdiv(M, 2 * BM) * nc_cdiv(N, 256);
+    const bool pair = pair_enabled() && (wide || pair_tiles >= nc_num_sms() / 2);
     CUtensorMap tmA, tmB;
     int rc;
     if (trans_a) rc = make_tmap(&tmA, A, M, K, lda, 64, BK);
     else         rc = make_tmap(&tmA, A, K, M, lda, BK, BM);
     if (rc) return rc;
     if (trans_b) rc = make_tmap(&tmB, B, N, K, ldb, 64, BK);
-    else         rc = make_tmap(&tmB, B, K, N, ldb, BK, BNsel);
+    else         rc = make_tmap(&tmB, B, K, N, ldb, BK, pair ? 128 : BNsel);
     if (rc) return rc;
     // split K when the tiles alone cannot fill the machine and the reduction is deep (fp32 C, no ReLU):
     // the partial tiles are summed in L2 by the TMA reduce-add.
@@ -493,15 +623,15 @@ extern "C" int nc_gemm_bf16(const void* A, int64_t lda, int trans_a, const void*
     if (rc) return rc;
     Epilogue epi{bias, mask, ldmask, c_dtype == NC_BF16, relu, (accumulate || splits > 1) ? 1 : 0,
                  ((uintptr_t)bias % 16 == 0) ? 1 : 0, (mask && (uintptr_t)mask % 16 == 0 && ldmask % 4 == 0) ? 1 : 0,
-                 splits};
-#define DISPATCH(BN)                                                                            \
-    do {                                                                                        \
-        if (trans_a && trans_b) rc = launch<BN, true, true>(tmA, tmB, tmC, epi, M, N, K, s);    \
-        else if (trans_a) rc = launch<BN, true, false>(tmA, tmB, tmC, epi, M, N, K, s);         \
-        else if (trans_b) rc = launch<BN, false, true>(tmA, tmB, tmC, epi, M, N, K, s);         \
-        else rc = launch<BN, false, false>(tmA, tmB, tmC, epi, M, N, K, s);                     \
+                 splits, 1};
+#define DISPATCH(BN, NCTA)                                                                              \
+    do {                                                                                                \
+        if (trans_a && trans_b) rc = launch<BN, true, true, NCTA>(tmA, tmB, tmC, epi, M, N, K, s);      \
+        else if (trans_a) rc = launch<BN, true, false, NCTA>(tmA, tmB, tmC, epi, M, N, K, s);           \
+        else if (trans_b) rc = launch<BN, false, true, NCTA>(tmA, tmB, tmC, epi, M, N, K, s);           \
+        else rc = launch<BN, false, false, NCTA>(tmA, tmB, tmC, epi, M, N, K, s);                       \
     } while (0)
-    if (BNsel == 256) DISPATCH(256); else DISPATCH(128);
+    if (pair) DISPATCH(256, 2); else if (BNsel == 256) DISPATCH(256, 1); else DISPATCH(128, 1);
 #undef DISPATCH
     if (rc) return rc;
     NC_CHECK_LAUNCH("nc_gemm_bf16");

@@ -145,6 +145,30 @@ def test_gemm_bf16_tcgen05(ta, tb, shape):
     assert H.rel_err(acc, ref + ref * mask.double().cpu()) < 1e-5, "mask+accumulate"
 
 
+@pytest.mark.parametrize("ta,tb", [(False, False), (True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("shape", [(3900, 2500, 520), (8704, 1600, 1000)])
+def test_gemm_bf16_cta_pair_tiles(ta, tb, shape):
+    """Shapes large enough for the CTA-pair configuration (256 x 256 tiles, tcgen05.mma.cta_group::2): odd
+    number of 128-row tiles (the pair's second CTA is entirely out of bounds), ragged N / K, every epilogue."""
+    g = torch.Generator().manual_seed(3)
+    M, N, K = shape
+    def mk(r, c):
+        return torch.randn(r, ops.pad8(c), generator=g).to(torch.bfloat16).to(DEV)[:, :c]
+    A = mk(K, M) if ta else mk(M, K)
+    B = mk(K, N) if tb else mk(N, K)
+    bias = torch.randn(N, generator=g).to(DEV)
+    ref = (A.t() if ta else A).float() @ (B if tb else B.t()).float()      # torch fp32 reference of the same op
+    out = ops.gemm(A, B, ta, tb, out_dtype=torch.float32)
+    assert H.rel_err(out, ref) < 1e-4, "plain"
+    out_b = ops.gemm(A, B, ta, tb, bias=bias, relu=True)
+    assert out_b.dtype == torch.bfloat16
+    assert H.rel_err(out_b.float(), torch.relu(ref + bias)) < 6e-3, "bias+relu bf16"
+    mask = (torch.rand(M, N, generator=g) > 0.5).float().to(DEV)
+    acc = out.clone()
+    ops.gemm(A, B, ta, tb, mask=mask, out=acc, accumulate=True)
+    assert H.rel_err(acc, ref + ref * mask) < 1e-4, "mask+accumulate"
+
+
 def test_gemm_bf16_large_persistent():
     g = torch.Generator().manual_seed(2)
     M, N, K = 4100, 3080, 1600
