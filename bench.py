@@ -286,6 +286,17 @@ def make_trainer(adata, wl, args, store_location="device"):
     return model, tr
 
 
+def ncu_traffic():
+    """DRAM bytes per GEMM launch (read + write) from the committed ncu capture of one C2-shaped step
+    (profiles/r1f_gemm_traffic.json, written from the launch list of tools/gpu_call5.sh); None if absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1f_gemm_traffic.json")
+    try:
+        with open(path) as fh:
+            return float(json.load(fh)["dram_bytes_per_launch"])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def run_steps(tr, it, n, read_loss=False):
     """n training iterations; returns the last loss dict (and host losses when read_loss)."""
     out = []
@@ -411,7 +422,7 @@ def run_ours(args):
         peak_tf = peaks["bf16_sustained"]
         roofline = {"kernel": "gemm_bf16_tcgen05 (nc_gemm_bf16)" if "nc_gemm_bf16" in kern else "gemm_f32_simt",
                     "bound": "tensor", "achieved": g["rate"], "peak": peak_tf, "unit": "TFLOP/s",
-                    "frac": g["rate"] / peak_tf if peak_tf else None, "traffic": None,
+                    "frac": g["rate"] / peak_tf if peak_tf else None, "traffic": ncu_traffic(),
                     "peak_source": f"{peaks['source']} bf16_tflops_sustained (kernel timed inside a long step)",
                     "launches_per_step": g["launches"] / args.steps, "share_of_step_kernel_time": g["share"],
                     "avg_launch_ms": g["ms"] / max(g["launches"], 1),

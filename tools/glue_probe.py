@@ -24,13 +24,20 @@ STEPS = 4
 with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True) as prof:
     bench.run_steps(tr, it, STEPS)
     torch.cuda.synchronize()
-rows = []
-for e in prof.key_averages(group_by_stack_n=4):
+rows = {}
+for e in prof.key_averages(group_by_stack_n=16):
     dt = getattr(e, "self_device_time_total", 0) or getattr(e, "self_cuda_time_total", 0)
-    if e.key.startswith("aten::") and dt > 0:
-        rows.append((dt / STEPS, e.count / STEPS, e.key, [s for s in e.stack if "nichecompass_b200" in s or "bench.py" in s][:2]))
-rows.sort(reverse=True)
-tot = sum(r[0] for r in rows)
-print(f"aten ops with device time: {tot:.1f} us / step")
-for dt, n, k, st in rows[:45]:
-    print(f"{dt:8.1f} us  x{n:5.1f}  {k:28s} {' | '.join(s.split('/')[-1] for s in st)}")
+    if not e.key.startswith("aten::"):
+        continue
+    site = next((f for f in e.stack if "nichecompass_b200/" in f or "bench.py" in f), "?")
+    site = site.split("nichecompass_b200/")[-1]
+    k = (e.key, site)
+    r = rows.setdefault(k, [0.0, 0.0, 0])
+    r[0] += dt / STEPS
+    r[1] += e.self_cpu_time_total / STEPS
+    r[2] += e.count / STEPS
+tot_d = sum(r[0] for r in rows.values())
+tot_c = sum(r[1] for r in rows.values())
+print(f"aten ops: device {tot_d:.1f} us / step, host (self cpu) {tot_c:.1f} us / step")
+for (k, site), (d, c, n) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:70]:
+    print(f"dev {d:7.1f} us  cpu {c:7.1f} us  x{n:5.1f}  {k:26s} {site}")
