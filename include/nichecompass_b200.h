@@ -285,6 +285,16 @@ int nc_sample_subgraph(const int32_t* g_rowptr, const int32_t* g_col, const int3
                        int64_t batch_id, int32_t* slot_ws, int32_t* n_id, int32_t cap_nodes,
                        int32_t* rowptr, int32_t* col, int32_t cap_edges, int32_t* cand_ws,
                        int32_t cap_cand, int32_t* counts, void* stream);
+
+/* Two sampled sub-graphs (a: the node batch, b: the edge batch of one training iteration,
+ * train/trainer.py:368-389 runs the encoder on each) merged into ONE block-diagonal encoder problem:
+ * merged node order = [a seeds | b seeds | a others | b others]; m_nid[a_sub + b_sub] the global ids in
+ * that order, m_rowptr[a_seed + b_seed + 1] / m_col the incoming-neighbour rows of the merged targets
+ * (a's entries first; m_col needs room for a_rowptr[a_seed] + b_rowptr[b_seed] entries).           */
+int nc_merge_subgraphs(const int32_t* a_rowptr, const int32_t* a_col, const int32_t* a_nid,
+                       int32_t a_seed, int32_t a_sub, const int32_t* b_rowptr, const int32_t* b_col,
+                       const int32_t* b_nid, int32_t b_seed, int32_t b_sub, int32_t* m_rowptr,
+                       int32_t* m_col, int32_t* m_nid, void* stream);
 /* torch.unique(ids, return_inverse=True) for the link-batch seeds (sorted ascending), n <= 16384. */
 int nc_unique_sorted_i32(const int32_t* ids, int32_t n, int32_t* uniq, int32_t* inverse,
                          int32_t* n_unique, void* stream);

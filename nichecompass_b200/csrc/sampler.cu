@@ -351,3 +351,61 @@ extern "C" int nc_sample_subgraph(const int32_t* g_rowptr, const int32_t* g_col,
     NC_CHECK_LAUNCH("nc_sample_subgraph");
     return NC_OK;
 }
+
+// ------------------------------------------------------------------------- merged sub-graphs
+// Two sampled sub-graphs (a: node batch, b: edge batch) as ONE block-diagonal problem for the encoder:
+// merged node order = [a seeds | b seeds | a others | b others], so the targets are again the leading rows.
+namespace {
+__device__ __forceinline__ int merge_map(int j, int n_seed_self, int add_seed, int add_other) {
+    return j < n_seed_self ? j + add_seed : j + add_other;
+}
+__global__ void k_merge_subgraphs(const int32_t* __restrict__ a_rowptr, const int32_t* __restrict__ a_col,
+                                  const int32_t* __restrict__ a_nid, int a_seed, int a_sub,
+                                  const int32_t* __restrict__ b_rowptr, const int32_t* __restrict__ b_col,
+                                  const int32_t* __restrict__ b_nid, int b_seed, int b_sub,
+                                  int32_t* __restrict__ m_rowptr, int32_t* __restrict__ m_col,
+                                  int32_t* __restrict__ m_nid) {
+    const int n_dst = a_seed + b_seed, n_sub = a_sub + b_sub;
+    const int Ea = a_rowptr[a_seed];
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    // node ids in merged order
+    for (int i = gtid; i < n_sub; i += gsz) {
+        int v;
+        if (i < a_seed) v = a_nid[i];
+        else if (i < n_dst) v = b_nid[i - a_seed];
+        else if (i < n_dst + (a_sub - a_seed)) v = a_nid[i - b_seed];
+        else v = b_nid[i - a_sub];
+        m_nid[i] = v;
+    }
+    // rows of the targets, column ids remapped: a: seeds stay, others + b_seed; b: seeds + a_seed, others + a_sub
+    for (int r = gtid; r <= n_dst; r += gsz)
+        m_rowptr[r] = r <= a_seed ? a_rowptr[r] : Ea + b_rowptr[r - a_seed];
+    const int warp = gtid >> 5, lane = gtid & 31, nwarp = gsz >> 5;
+    for (int r = warp; r < n_dst; r += nwarp) {
+        if (r < a_seed) {
+            const int e0 = a_rowptr[r], e1 = a_rowptr[r + 1];
+            for (int e = e0 + lane; e < e1; e += 32) m_col[e] = merge_map(a_col[e], a_seed, 0, b_seed);
+        } else {
+            const int q = r - a_seed;
+            const int e0 = b_rowptr[q], e1 = b_rowptr[q + 1];
+            for (int e = e0 + lane; e < e1; e += 32) m_col[Ea + e] = merge_map(b_col[e], b_seed, a_seed, a_sub);
+        }
+    }
+}
+}  // namespace
+
+extern "C" int nc_merge_subgraphs(const int32_t* a_rowptr, const int32_t* a_col, const int32_t* a_nid,
+                                  int32_t a_seed, int32_t a_sub, const int32_t* b_rowptr, const int32_t* b_col,
+                                  const int32_t* b_nid, int32_t b_seed, int32_t b_sub, int32_t* m_rowptr,
+                                  int32_t* m_col, int32_t* m_nid, void* stream) {
+    NC_REQUIRE(a_seed >= 0 && b_seed >= 0 && a_sub >= a_seed && b_sub >= b_seed, NC_ESHAPE,
+               "nc_merge_subgraphs: bad sizes");
+    if (a_sub + b_sub == 0) return NC_OK;
+    const int n = a_sub + b_sub;
+    const int grid = (int)std::min<int64_t>(nc_cdiv(n, 256), 2 * nc_num_sms());
+    k_merge_subgraphs<<<grid, 256, 0, (cudaStream_t)stream>>>(a_rowptr, a_col, a_nid, a_seed, a_sub, b_rowptr, b_col,
+                                                             b_nid, b_seed, b_sub, m_rowptr, m_col, m_nid);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_merge_subgraphs");
+    return NC_OK;
+}

@@ -278,8 +278,9 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
             return None
         return torch.cat([emb(cats[:, i]) for i, emb in enumerate(self.cat_covariates_embedders)], dim=1)
 
-    def _prepare(self, batch, decoder: str):
-        """-> (graph, x_enc tile, labels(n) accessor, aggregated-neighbour accessor, embed, batch rows)."""
+    def _prepare(self, batch, decoder: str, need_x_enc: bool = True):
+        """-> (graph, x_enc tile, labels(n) accessor, aggregated-neighbour accessor, embed, batch rows).
+        ``need_x_enc=False`` (the encoder ran on a merged batch, ``forward_joint``): no encoder tile."""
         dev = self.device
         store = getattr(batch, "store", None)
         embed = self._embed(getattr(batch, "cat_covariates_cats", None))
@@ -288,7 +289,9 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
         if store is not None:
             graph = batch.graph
             n_sub = graph.n_nodes
-            if enc_embed is None:
+            if not need_x_enc:
+                x_enc = None
+            elif enc_embed is None:
                 x_enc = ops.csr_gather_rows(store, batch.n_id, n_sub, self.log_variational_, self.compute_dtype, ld)
             else:
                 xd = ops.csr_gather_rows(store, batch.n_id, n_sub, self.log_variational_, torch.float32)
@@ -342,17 +345,26 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
                 decoder: Literal["graph", "omics"],
                 use_only_active_gps: bool = False,
                 return_agg_weights: bool = False,
-                update_atac_dynamic_decoder_mask: bool = False) -> dict:
-        graph, x_enc, target_rows, neighbor_rows, embed = self._prepare(data_batch, decoder)
+                update_atac_dynamic_decoder_mask: bool = False,
+                _latent=None) -> dict:
+        """``_latent`` (internal, ``forward_joint``): (encoder output of a merged batch, first row of this
+        batch's seeds in it) -- the encoder is then not run here."""
+        graph, x_enc, target_rows, neighbor_rows, embed = self._prepare(data_batch, decoder, _latent is None)
         P = self.n_prior_gp_ + self.n_addon_gp_
-        ml_u = self.encoder.encode(x_enc, graph)                      # [n_dst, 2P]
+        if _latent is None:
+            ml_u, row_off = self.encoder.encode(x_enc, graph), 0      # [n_dst, 2P]
+        else:
+            ml_u, row_off = _latent
         if decoder == "omics":
             nb = int(data_batch.batch_size)
-            ml = ml_u[:nb]
+            ml = ml_u[row_off:row_off + nb]
             batch_rows = None
         elif decoder == "graph":
             eli = data_batch.edge_label_index
-            batch_rows = torch.cat((eli[0], eli[1]), 0).to(torch.int32).contiguous()
+            batch_rows = torch.cat((eli[0], eli[1]), 0).to(torch.int32)
+            if row_off:
+                batch_rows = batch_rows + row_off
+            batch_rows = batch_rows.contiguous()
             ml = GatherRowsFn.apply(ml_u, batch_rows)
         else:
             raise ValueError(f"unknown decoder {decoder}")
@@ -427,6 +439,38 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
                     output["node_labels"][key] = labels_full.index_select(1, ridx)
                     output[f"{key}_nb_means"] = means.index_select(1, ridx)
         return output
+
+    # ------------------------------------------------------------------ one encoder pass per iteration
+    def joint_supported(self, node_batch, edge_batch) -> bool:
+        """The node batch and the edge batch of one training iteration (train/trainer.py:368-389) can share
+        ONE encoder pass when both are index batches over the same count store, the encoder is GATv2 (a
+        target's output depends on its own neighbourhood only, so a block-diagonal union of the two
+        sub-graphs gives the same rows) and no covariate embedding is injected into the encoder input."""
+        store = getattr(node_batch, "store", None)
+        return (store is not None and getattr(edge_batch, "store", None) is store
+                and self.encoder.conv_layer == "gatv2conv"
+                and not (self.n_cat_covariates_ > 0 and "encoder" in self.cat_covariates_embeds_injection_))
+
+    def forward_joint(self, node_batch, edge_batch, use_only_active_gps: bool = False):
+        """``(forward(node_batch, "omics"), forward(edge_batch, "graph"))`` with the two encoder passes merged:
+        ``nc_merge_subgraphs`` builds the block-diagonal problem [node seeds | edge seeds | others], the count
+        rows are gathered once, every encoder GEMM / attention kernel (forward and backward) runs once on
+        the union instead of once per batch."""
+        gn, ge = node_batch.graph, edge_batch.graph
+        a_seed, a_sub, b_seed, b_sub = gn.n_dst, gn.n_nodes, ge.n_dst, ge.n_nodes
+        dev = gn.rowptr.device
+        m_rowptr = torch.empty(a_seed + b_seed + 1, dtype=torch.int32, device=dev)
+        m_col = torch.empty(max(gn.col.numel() + ge.col.numel(), 1), dtype=torch.int32, device=dev)
+        m_nid = torch.empty(a_sub + b_sub, dtype=torch.int32, device=dev)
+        call("nc_merge_subgraphs", gn.rowptr, gn.col, node_batch.n_id, a_seed, a_sub, ge.rowptr, ge.col,
+             edge_batch.n_id, b_seed, b_sub, m_rowptr, m_col, m_nid)
+        gm = SubgraphCSR(m_rowptr, m_col, a_sub + b_sub, a_seed + b_seed, max(gn.max_deg, ge.max_deg))
+        x_enc = ops.csr_gather_rows(node_batch.store, m_nid, a_sub + b_sub, self.log_variational_,
+                                    self.compute_dtype, pad8(self.encoder.n_input))
+        ml_u = self.encoder.encode(x_enc, gm)
+        node_out = self.forward(node_batch, "omics", use_only_active_gps, _latent=(ml_u, 0))
+        edge_out = self.forward(edge_batch, "graph", use_only_active_gps, _latent=(ml_u, a_seed))
+        return node_out, edge_out
 
     def _update_atac_dynamic_masks(self):
         """Turn off peaks whose mapped genes were all regularised away (modules/vgpgae.py:813-857)."""

@@ -130,6 +130,7 @@ class Trainer(BaseTrainerMixin):
         self.compute_dtype_ = kwargs.pop("compute_dtype", None)
         self.store_location_ = kwargs.pop("store_location", "device")
         self.prefetch_ = kwargs.pop("prefetch", True)
+        self.joint_encoder_ = kwargs.pop("joint_encoder", True)
         kwargs.pop("latent_dtype", None)          # forwarded by NicheCompass.train, unused here (as in the reference)
         self.epoch = -1
         self.training_time = 0
@@ -216,10 +217,15 @@ class Trainer(BaseTrainerMixin):
     def train_iteration(self, edge_batch, node_batch) -> dict:
         """train/trainer.py:368-421: two forwards, loss, zero_grad, backward, clip, Adam step.
         Returns the loss dictionary (device scalars; nothing is read back here)."""
-        node_out = self.model(data_batch=node_batch.to(self.device), decoder="omics",
-                              use_only_active_gps=self.use_only_active_gps)
-        edge_out = self.model(data_batch=edge_batch.to(self.device), decoder="graph",
-                              use_only_active_gps=self.use_only_active_gps)
+        joint = getattr(self.model, "joint_supported", None)
+        if self.joint_encoder_ and joint is not None and joint(node_batch, edge_batch):
+            # one encoder pass over the block-diagonal union of the two sampled sub-graphs
+            node_out, edge_out = self.model.forward_joint(node_batch, edge_batch, self.use_only_active_gps)
+        else:
+            node_out = self.model(data_batch=node_batch.to(self.device), decoder="omics",
+                                  use_only_active_gps=self.use_only_active_gps)
+            edge_out = self.model(data_batch=edge_batch.to(self.device), decoder="graph",
+                                  use_only_active_gps=self.use_only_active_gps)
         loss_dict = self.model.loss(
             edge_model_output=edge_out, node_model_output=node_out, **self._loss_kwargs(),
             edge_recon_active=self.edge_recon_active,

@@ -169,3 +169,24 @@ def test_layerwise_inference_equals_loader_walk():
     model.model.set_compute_dtype(torch.bfloat16)
     mu_bf = model.get_latent_representation(layerwise=True, partition="spatial", **kw)
     assert np.abs(mu_bf - walk_mu).max() < 3e-2 * np.abs(walk_mu).max()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_joint_encoder_pass_equals_separate_passes(dtype):
+    """Trainer.train_iteration with the node + edge sub-graphs merged into one block-diagonal encoder
+    pass (VGPGAE.forward_joint, nc_merge_subgraphs) against the reference's two forwards."""
+    adata = H.tiny_problem(n_cells=220, n_genes=44, n_prior_gp=12)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=4)
+    p32 = init_params(cfg, seed=3)
+    ref, _, _ = _cpu_run(adata, cfg, p32, 3, 24)
+    tr_j, joint = _gpu_run(adata, cfg, p32, ref.noise_log, 3, 24, dtype=dtype, joint_encoder=True)
+    tr_s, sep = _gpu_run(adata, cfg, p32, ref.noise_log, 3, 24, dtype=dtype, joint_encoder=False)
+    tol = 2e-6 if dtype == torch.float32 else 2e-3
+    for it, (a, b) in enumerate(zip(joint, sep)):
+        for k in b:
+            assert abs(a[k] - b[k]) <= tol * abs(b[k]) * (1 + it) + 1e-12, (it, k, a[k], b[k])
+    if dtype == torch.float32:
+        sj, ss = tr_j.model.state_dict(), tr_s.model.state_dict()
+        for k in ss:
+            if ss[k].is_floating_point():
+                assert float((sj[k] - ss[k]).abs().max()) <= 2 * 1e-3 * 3 + 1e-9, k
