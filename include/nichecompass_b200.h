@@ -306,6 +306,10 @@ int nc_col_sum(const void* x, int dtype, int64_t ld, int32_t R, int32_t C, float
                void* stream);
 int nc_relu_bwd(const float* dh, int64_t lddh, const void* h, int dtype, int64_t ldh, int32_t R,
                 int32_t C, void* out, int64_t ldo, void* stream);
+/* out [R, ldo] (dtype) = relu(x [R, ldx] fp32), pad columns zeroed: the activation between the two conv
+ * layers of the 2-layer encoder (nn/encoders.py:191-194, ``hidden = activation(conv_l1(hidden))``).   */
+int nc_relu_cast(const float* x, int64_t ldx, int32_t R, int32_t C, void* out, int dtype, int64_t ldo,
+                 void* stream);
 
 #ifdef __cplusplus
 }

@@ -419,7 +419,29 @@ k_relu_bwd_v4(const float* __restrict__ dh, int64_t lddh, const T* __restrict__ 
         }
     }
 }
+// out = relu(x) cast to T; pad columns [C, ldo) are zeroed
+template <typename T>
+__global__ void k_relu_cast(const float* __restrict__ x, int64_t ldx, int R, int C, T* __restrict__ out, int64_t ldo) {
+    const int64_t total = (int64_t)R * ldo;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / ldo), c = (int)(q % ldo);
+        Elem<T>::st(out + q, c < C ? fmaxf(x[(int64_t)r * ldx + c], 0.f) : 0.f);
+    }
+}
 }  // namespace
+
+extern "C" int nc_relu_cast(const float* x, int64_t ldx, int32_t R, int32_t C, void* out, int dtype, int64_t ldo,
+                            void* stream) {
+    NC_REQUIRE(R >= 0 && C > 0 && ldx >= C && ldo >= C, NC_ESHAPE, "nc_relu_cast: bad shape");
+    NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_relu_cast: bad dtype %d", dtype);
+    if (R == 0) return NC_OK;
+    const int g = grid_for((int64_t)R * ldo);
+    if (dtype == NC_F32) k_relu_cast<float><<<g, 256, 0, (cudaStream_t)stream>>>(x, ldx, R, C, (float*)out, ldo);
+    else k_relu_cast<__nv_bfloat16><<<g, 256, 0, (cudaStream_t)stream>>>(x, ldx, R, C, (__nv_bfloat16*)out, ldo);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_relu_cast");
+    return NC_OK;
+}
 
 extern "C" int nc_col_sum(const void* x, int dtype, int64_t ld, int32_t R, int32_t C, float* out, void* stream) {
     NC_REQUIRE(R >= 0 && C > 0 && ld >= C, NC_ESHAPE, "nc_col_sum: bad shape");

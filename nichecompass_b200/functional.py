@@ -204,14 +204,16 @@ class EncoderGATv2Fn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x_enc, graph: SubgraphCSR, n_feat: int, heads: int, out_offsets, out_width: int,
-                cache_key, W1, b1, *tensors):
+                cache_key, act, W1, b1, *tensors):
+        """``W1 is None``: second conv layer of the 2-layer encoder -- ``x_enc`` is the fp32 output of
+        ``conv_l1`` [n_sub, Hd] and hidden = relu(x_enc) (nn/encoders.py:191-194)."""
         NC = len(tensors) // 6
         conv = [tensors[6 * c:6 * c + 6] for c in range(NC)]
-        act = x_enc.dtype
+        pre = W1 is None
         dev = x_enc.device
         n_sub, n_dst = graph.n_nodes, graph.n_dst
-        assert x_enc.size(0) == n_sub
-        Hd = W1.size(0)
+        assert x_enc.size(0) == n_sub and (pre or x_enc.dtype == act)
+        Hd = x_enc.size(1) if pre else W1.size(0)
         Cs = [cv[5].numel() for cv in conv]
         widths = [heads * C for C in Cs]
         offs = [sum(widths[:c]) for c in range(NC)]
@@ -219,7 +221,7 @@ class EncoderGATv2Fn(torch.autograd.Function):
         ldl = pad8(NL)
         seg_host = torch.tensor([[offs[c], Cs[c], out_offsets[c], 0] for c in range(NC)], dtype=torch.int32)
         seg = seg_host.to(dev, non_blocking=True)
-        W1p = pack_rows((cache_key, "W1"), [W1], act, W1.size(1))
+        W1p = None if pre else pack_rows((cache_key, "W1"), [W1], act, W1.size(1))
         Wl = pack_rows((cache_key, "Wl"), [cv[0] for cv in conv], act, Hd)
         Wr = pack_rows((cache_key, "Wr"), [cv[2] for cv in conv], act, Hd)
         bl, br = _cat_f32([cv[1] for cv in conv]), _cat_f32([cv[3] for cv in conv])
@@ -232,7 +234,11 @@ class EncoderGATv2Fn(torch.autograd.Function):
                 bias_out[out_offsets[c]:out_offsets[c] + Cs[c]] = conv[c][5].detach()
         ldh = pad8(Hd)
         Hbuf = torch.zeros(n_sub, ldh, dtype=act, device=dev) if ldh != Hd else torch.empty(n_sub, ldh, dtype=act, device=dev)
-        ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
+        if pre:
+            xin = x_enc.detach().float().contiguous()
+            call("nc_relu_cast", xin, xin.stride(0), n_sub, Hd, Hbuf, dtype_code(act), ldh)
+        else:
+            ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
         XL = torch.empty(n_sub, ldl, dtype=act, device=dev)
         XR = torch.empty(max(n_dst, 1), ldl, dtype=act, device=dev)
         ops.gemm(Hbuf, Wl, bias=bl, out=XL[:, :NL], M=n_sub, N=NL, K=Hd)
@@ -241,9 +247,9 @@ class EncoderGATv2Fn(torch.autograd.Function):
         alpha = torch.empty(max(graph.n_slots, 1) * NC * heads, dtype=torch.float32, device=dev)
         call("nc_gatv2_fwd", XL, XR, dtype_code(act), ldl, att, bias_out, graph.rowptr, graph.col, n_dst,
              seg, HostPtr(seg_host), NC, heads, graph.max_deg, 0.2, out, out.stride(0), alpha)
-        ctx.save_for_backward(x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr)
+        ctx.save_for_backward(None if pre else x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr)
         ctx.meta = (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
-                    [tuple(t.shape) for t in tensors], tuple(W1.shape))
+                    [tuple(t.shape) for t in tensors], None if pre else tuple(W1.shape), act)
         ctx.params = (W1, b1, conv, tight)          # arena residents receive their gradients in place
         return out
 
@@ -251,8 +257,9 @@ class EncoderGATv2Fn(torch.autograd.Function):
     def backward(ctx, dout):
         x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr = ctx.saved_tensors
         (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
-         shapes, w1_shape) = ctx.meta
-        act, dev = x_enc.dtype, x_enc.device
+         shapes, w1_shape, act) = ctx.meta
+        pre = W1p is None
+        dev = Hbuf.device
         n_sub, n_dst = graph.n_nodes, graph.n_dst
         dout = dout.contiguous().float()
         rptr, rdst, rslot = graph.reverse()
@@ -262,16 +269,16 @@ class EncoderGATv2Fn(torch.autograd.Function):
             dXL[:, NL:].zero_()
             dXR[:, NL:].zero_()
         W1, b1, conv, tight = ctx.params
-        need = ctx.needs_input_grad          # (x_enc, graph, n_feat, heads, offs, width, key, W1, b1, *tensors)
-        need_c = [need[9 + 6 * c:15 + 6 * c] for c in range(NC)]
+        need = ctx.needs_input_grad          # (x_enc, graph, n_feat, heads, offs, width, key, act, W1, b1, *tensors)
+        need_c = [need[10 + 6 * c:16 + 6 * c] for c in range(NC)]
 
         def gv(slot):
             return grad_view([cv[slot] for cv in conv], [nc[slot] for nc in need_c])
         g_bl, g_br, g_att = gv(1), gv(3), gv(4)
         g_Wl, g_Wr = (gv(0), gv(2)) if Hd % 4 == 0 else (None, None)       # GEMM C rows must stay 16-byte aligned
         g_bias = gv(5) if tight else None
-        g_W1 = grad_view([W1], [need[7]]) if (n_feat == W1.size(1) and n_feat % 4 == 0) else None
-        g_b1 = grad_view([b1], [need[8]])
+        g_W1 = grad_view([W1], [need[8]]) if (not pre and n_feat == W1.size(1) and n_feat % 4 == 0) else None
+        g_b1 = None if pre else grad_view([b1], [need[9]])
         datt = g_att if g_att is not None else torch.zeros(ldl, dtype=torch.float32, device=dev)
         dbias = g_bias if g_bias is not None else torch.zeros(out_width, dtype=torch.float32, device=dev)
         ds = torch.empty_like(alpha)
@@ -301,13 +308,16 @@ class EncoderGATv2Fn(torch.autograd.Function):
             ops.gemm(dXR, Wr, trans_b=True, out=dH[:n_dst, :Hd], accumulate=True, M=n_dst, N=Hd, K=NL)
         dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
         call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
-        if g_W1 is not None:
+        if pre:
+            dW1 = db1 = None
+        elif g_W1 is not None:
             ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out=g_W1.view(Hd, n_feat), accumulate=True,
                      M=Hd, N=n_feat, K=n_sub)
             dW1 = None
         else:
             dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
-        db1 = _col_sum(dHp, Hd, out=g_b1)
+        if not pre:
+            db1 = _col_sum(dHp, Hd, out=g_b1)
         grads: List[Optional[torch.Tensor]] = []
         for c in range(NC):
             sl = slice(offs[c], offs[c] + widths[c])
@@ -322,13 +332,15 @@ class EncoderGATv2Fn(torch.autograd.Function):
         if dW1 is not None and dW1.shape != w1_shape:
             dW1 = dW1.contiguous()
         dx = None
-        if ctx.needs_input_grad[0]:
+        if pre:
+            dx = dHp[:, :Hd].float() if ctx.needs_input_grad[0] else None      # d relu(x): gradient of conv_l1's output
+        elif ctx.needs_input_grad[0]:
             # only the trailing (embedding) columns of the encoder input can require grad
             dxf = ops.gemm(dHp, W1p, trans_b=True, out_dtype=torch.float32, M=n_sub, N=n_feat, K=Hd)
             dx = torch.zeros_like(x_enc, dtype=torch.float32)
             dx[:, :n_feat] = dxf
             dx = dx.to(x_enc.dtype)
-        return (dx, None, None, None, None, None, None, dW1, db1, *grads)
+        return (dx, None, None, None, None, None, None, None, dW1, db1, *grads)
 
 
 # --------------------------------------------------------------------------- latent plumbing
@@ -805,35 +817,42 @@ class EncoderGCNFn(torch.autograd.Function):
     per conv in output-column order."""
 
     @staticmethod
-    def forward(ctx, x_enc, graph: SubgraphCSR, n_feat: int, out_offsets, out_width: int, cache_key, W1, b1,
+    def forward(ctx, x_enc, graph: SubgraphCSR, n_feat: int, out_offsets, out_width: int, cache_key, act, W1, b1,
                 *tensors):
+        """``W1 is None``: second conv layer of the 2-layer encoder (see ``EncoderGATv2Fn.forward``)."""
         NC = len(tensors) // 2
         Ws, bs = [tensors[2 * c] for c in range(NC)], [tensors[2 * c + 1] for c in range(NC)]
-        act, dev = x_enc.dtype, x_enc.device
+        pre = W1 is None
+        dev = x_enc.device
         n_sub, n_dst = graph.n_nodes, graph.n_dst
-        Hd = W1.size(0)
+        Hd = x_enc.size(1) if pre else W1.size(0)
         Cs = [w.size(0) for w in Ws]
         assert list(out_offsets) == [sum(Cs[:c]) for c in range(NC)] and sum(Cs) == out_width
-        W1p = pack_rows((cache_key, "W1"), [W1], act, W1.size(1))
+        W1p = None if pre else pack_rows((cache_key, "W1"), [W1], act, W1.size(1))
         Wall = pack_rows((cache_key, "Wgcn"), Ws, act, Hd)
         bias_out = _cat_f32(bs)
         ldh = pad8(Hd)
         Hbuf = torch.zeros(n_sub, ldh, dtype=act, device=dev)
-        ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
+        if pre:
+            xin = x_enc.detach().float().contiguous()
+            call("nc_relu_cast", xin, xin.stride(0), n_sub, Hd, Hbuf, dtype_code(act), ldh)
+        else:
+            ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
         ldw = pad8(out_width)
         XW = torch.zeros(n_sub, ldw, dtype=act, device=dev)
         ops.gemm(Hbuf, Wall, out=XW[:, :out_width], M=n_sub, N=out_width, K=Hd)
         w, wself = graph.gcn_weights(use_out_degree=False)
         out = ops.spmm_csr(XW, graph.rowptr, graph.col, w, wself, True, n_dst, bias=bias_out, n_cols=out_width)
-        ctx.save_for_backward(x_enc, Hbuf, W1p, Wall, w, wself)
-        ctx.meta = (graph, n_feat, out_width, NC, Cs, Hd, [tuple(t.shape) for t in tensors])
+        ctx.save_for_backward(None if pre else x_enc, Hbuf, W1p, Wall, w, wself)
+        ctx.meta = (graph, n_feat, out_width, NC, Cs, Hd, [tuple(t.shape) for t in tensors], act)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         x_enc, Hbuf, W1p, Wall, w, wself = ctx.saved_tensors
-        graph, n_feat, out_width, NC, Cs, Hd, shapes = ctx.meta
-        act, dev = x_enc.dtype, x_enc.device
+        graph, n_feat, out_width, NC, Cs, Hd, shapes, act = ctx.meta
+        pre = W1p is None
+        dev = Hbuf.device
         n_sub, n_dst = graph.n_nodes, graph.n_dst
         dout = dout.contiguous().float()
         rptr, rdst, rslot = graph.reverse()
@@ -850,16 +869,20 @@ class EncoderGCNFn(torch.autograd.Function):
         ops.gemm(dXW, Wall, trans_b=True, out=dH[:, :Hd], M=n_sub, N=Hd, K=out_width)
         dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
         call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
-        dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
-        db1 = _col_sum(dHp, Hd)
+        dW1 = db1 = None
+        if not pre:
+            dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
+            db1 = _col_sum(dHp, Hd)
         grads, r = [], 0
         for c in range(NC):
             grads += [dWall[r:r + Cs[c]], dbias[r:r + Cs[c]]]
             r += Cs[c]
         dx = None
-        if ctx.needs_input_grad[0]:
+        if pre:
+            dx = dHp[:, :Hd].float() if ctx.needs_input_grad[0] else None
+        elif ctx.needs_input_grad[0]:
             dxf = ops.gemm(dHp, W1p, trans_b=True, out_dtype=torch.float32, M=n_sub, N=n_feat, K=Hd)
             dx = torch.zeros_like(x_enc, dtype=torch.float32)
             dx[:, :n_feat] = dxf
             dx = dx.to(x_enc.dtype)
-        return (dx, None, None, None, None, None, dW1, db1, *grads)
+        return (dx, None, None, None, None, None, None, dW1, db1, *grads)

@@ -19,7 +19,8 @@ class Encoder(nn.Module):
 
     Parameters are those of the reference ``Encoder``; ``use_bn`` is accepted and unused
     exactly as there (nn/encoders.py:52-53 documents it, the body never reads it).
-    Round-1 kernel coverage: ``n_fc_layers == 1``, ``n_layers == 1``, ``dropout_rate == 0``.
+    Kernel coverage: ``n_fc_layers == 1``, ``n_layers`` 1 or 2 (``conv_l1`` over the whole sampled
+    sub-graph, ReLU, then the latent convs on the seed rows), ``dropout_rate == 0``.
     """
 
     def __init__(self,
@@ -43,9 +44,9 @@ class Encoder(nn.Module):
               f"n_fc_layers: {n_fc_layers}, n_layers: {n_layers}, conv_layer: {conv_layer}, "
               f"n_attention_heads: {n_attention_heads if conv_layer == 'gatv2conv' else '0'}, "
               f"dropout_rate: {dropout_rate}, ")
-        if n_fc_layers != 1 or n_layers != 1:
-            raise NotImplementedError("nichecompass_b200 kernels cover n_fc_layers=1, n_layers=1 "
-                                      "(the reference defaults); see DESIGN.md 'not yet covered'")
+        if n_fc_layers != 1 or n_layers not in (1, 2):
+            raise NotImplementedError("nichecompass_b200 kernels cover n_fc_layers=1 and n_layers in (1, 2); "
+                                      "see DESIGN.md 'not yet covered'")
         if dropout_rate != 0.:
             raise NotImplementedError("dropout in the encoder is not implemented in the CUDA path")
         if cat_covariates_embed_mode != "input" and n_cat_covariates_embed_input != 0:
@@ -63,6 +64,9 @@ class Encoder(nn.Module):
             else (lambda c: GCNConv(n_hidden, c))
         if conv_layer not in ("gatv2conv", "gcnconv"):
             raise ValueError(f"unknown conv_layer {conv_layer}")
+        if n_layers == 2:
+            self.conv_l1 = conv(n_hidden)                  # nn/encoders.py:106-108 / 123-127
+            self._key_l1 = new_cache_key()
         self.conv_mu = conv(n_latent)
         self.conv_logstd = conv(n_latent)
         if n_addon_latent != 0:
@@ -92,24 +96,43 @@ class Encoder(nn.Module):
         that the stacked matrices, their bf16 shadows and their gradients are views."""
         convs = [c for c, _ in self._convs()]
         if self.conv_layer == "gatv2conv":
-            return [[c.lin_l.weight for c in convs], [c.lin_r.weight for c in convs],
-                    [c.lin_l.bias for c in convs], [c.lin_r.bias for c in convs],
-                    [c.att for c in convs], [c.bias for c in convs], [self.fc_l1.weight], [self.fc_l1.bias]]
-        return [[c.lin.weight for c in convs], [c.bias for c in convs], [self.fc_l1.weight], [self.fc_l1.bias]]
+            groups = [[c.lin_l.weight for c in convs], [c.lin_r.weight for c in convs],
+                      [c.lin_l.bias for c in convs], [c.lin_r.bias for c in convs],
+                      [c.att for c in convs], [c.bias for c in convs], [self.fc_l1.weight], [self.fc_l1.bias]]
+            if self.n_layers == 2:
+                groups += [[t] for t in self.conv_l1.param_tuple()]
+            return groups
+        groups = [[c.lin.weight for c in convs], [c.bias for c in convs], [self.fc_l1.weight], [self.fc_l1.bias]]
+        if self.n_layers == 2:
+            groups += [[self.conv_l1.lin.weight], [self.conv_l1.bias]]
+        return groups
 
     def encode(self, x_enc: torch.Tensor, graph: SubgraphCSR) -> torch.Tensor:
         """``x_enc``: [n_sub, pad8(n_input)] in ``compute_dtype`` (log1p counts ++ optional
         embedding, zero padded).  Returns (mu | logstd) [graph.n_dst, 2 * n_gps] fp32."""
         convs = self._convs()
         offs = [o for _, o in convs]
-        if self.conv_layer == "gatv2conv":
+        act = self.compute_dtype
+        gat = self.conv_layer == "gatv2conv"
+        W1, b1, n_in, key = self.fc_l1.weight, self.fc_l1.bias, self.n_input, self._key
+        if self.n_layers == 2:
+            # hidden = relu(conv_l1(relu(fc_l1(x)))) for EVERY node of the sampled sub-graph (nn/encoders.py:191-194);
+            # the latent convs then start from that fp32 tensor (``W1 = None``: relu + cast inside the function)
+            Hd = self.fc_l1.weight.size(0)
+            g_all = SubgraphCSR(graph.rowptr, graph.col, graph.n_nodes, graph.n_nodes, graph.max_deg)
+            if gat:
+                x_enc = EncoderGATv2Fn.apply(x_enc, g_all, n_in, self.n_attention_heads, [0], Hd, self._key_l1, act,
+                                             W1, b1, *self.conv_l1.param_tuple())
+            else:
+                x_enc = EncoderGCNFn.apply(x_enc, g_all, n_in, [0], Hd, self._key_l1, act, W1, b1,
+                                           self.conv_l1.lin.weight, self.conv_l1.bias)
+            W1, b1, n_in = None, None, Hd
+        if gat:
             tensors = [t for c, _ in convs for t in c.param_tuple()]
-            return EncoderGATv2Fn.apply(x_enc, graph, self.n_input, self.n_attention_heads, offs,
-                                        2 * self.n_gps, self._key, self.fc_l1.weight, self.fc_l1.bias,
-                                        *tensors)
+            return EncoderGATv2Fn.apply(x_enc, graph, n_in, self.n_attention_heads, offs, 2 * self.n_gps, key, act,
+                                        W1, b1, *tensors)
         tensors = [t for c, _ in convs for t in (c.lin.weight, c.bias)]
-        return EncoderGCNFn.apply(x_enc, graph, self.n_input, offs, 2 * self.n_gps, self._key,
-                                  self.fc_l1.weight, self.fc_l1.bias, *tensors)
+        return EncoderGCNFn.apply(x_enc, graph, n_in, offs, 2 * self.n_gps, key, act, W1, b1, *tensors)
 
     def pack_input(self, x: torch.Tensor, cat_covariates_embed: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Dense fp32 [n, F] (already log-transformed) (+ embedding) -> padded compute-dtype tile."""

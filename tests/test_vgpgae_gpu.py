@@ -25,7 +25,7 @@ LAM = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lamb
 def build_module(cfg, params, conv_layer, node_label_method):
     from nichecompass_b200.modules import VGPGAE
     with contextlib.redirect_stdout(io.StringIO()):
-        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=cfg.get("n_layers", 1),
                    n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"],
                    n_addon_gp=cfg["n_addon_gp"], cat_covariates_embeds_nums=[],
                    n_output_genes=cfg["n_output_genes"],
@@ -52,10 +52,11 @@ def make_batches(adata, edge_bs=16, node_bs=8):
     return next(iter(nl)), next(iter(ll))
 
 
-def run_pair(conv_layer, node_label_method, n_addon, dtype, n_genes=40, use_only_active=False, train=True):
+def run_pair(conv_layer, node_label_method, n_addon, dtype, n_genes=40, use_only_active=False, train=True,
+             n_layers=1):
     adata = H.tiny_problem(n_cells=150, n_genes=n_genes, n_prior_gp=12)
     cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=n_addon, conv_layer=conv_layer,
-                                  node_label_method=node_label_method)
+                                  node_label_method=node_label_method, n_layers=n_layers)
     p32 = init_params(cfg, seed=3)
     if use_only_active:
         p32["running_mean_abs_mu"] = torch.rand(cfg["n_prior_gp"] + n_addon) ** 6
@@ -267,3 +268,31 @@ def test_bf16_covariates_and_atac_losses():
     for k in ("global_loss", "optim_loss", "edge_recon_loss", "gene_expr_recon_loss", "chrom_access_recon_loss",
               "kl_reg_loss"):
         assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(ol[k])) < 2e-3, k
+
+
+@pytest.mark.parametrize("conv_layer,dtype", [("gatv2conv", torch.float32), ("gcnconv", torch.float32),
+                                              ("gatv2conv", torch.bfloat16)])
+def test_two_layer_encoder(conv_layer, dtype):
+    """n_layers_encoder=2: conv_l1 over the whole sampled sub-graph, ReLU, latent convs on the seeds."""
+    orc, mod, (on, oe, ol), (cn, ce, cl), p64 = run_pair(conv_layer, "one-hop-norm", 4, dtype, n_layers=2)
+    assert any(k.startswith("encoder.conv_l1.") for k, _ in mod.named_parameters())
+    if dtype == torch.bfloat16:
+        for k in ("global_loss", "optim_loss", "edge_recon_loss", "gene_expr_recon_loss", "kl_reg_loss"):
+            assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(ol[k])) < 3e-3, k
+        return
+    tol = 1e-5
+    for k in ("mu", "logstd", "target_rna_nb_means", "source_rna_nb_means"):
+        assert H.rel_err(cn[k], on[k]) < tol, k
+    for k in ("mu", "logstd", "edge_recon_logits"):
+        assert H.rel_err(ce[k], oe[k]) < tol, k
+    for k, v in ol.items():
+        assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(v)) < tol, k
+    checked = 0
+    for k, p in mod.named_parameters():
+        ref = p64[k].grad
+        if ref is None:
+            continue
+        assert p.grad is not None, k
+        assert H.rel_err(p.grad, ref) < 3e-5, k
+        checked += 1
+    assert checked >= 12

@@ -51,3 +51,34 @@ torch.cuda.synchronize()
 st = pstats.Stats(pr)
 st.sort_stats("cumulative").print_stats(45)
 st.sort_stats("tottime").print_stats(30)
+
+# host time spent INSIDE the C-ABI calls (ctypes conversion + library host code + cudaLaunch), per entry point
+from nichecompass_b200 import _lib                                   # noqa: E402
+
+
+class _Hook:
+    def __init__(self):
+        self.t, self.n, self.t0 = {}, {}, 0.0
+
+    def before(self, name, args):
+        self.t0 = time.perf_counter()
+
+    def after(self, name, args):
+        dt = time.perf_counter() - self.t0
+        self.t[name] = self.t.get(name, 0.0) + dt
+        self.n[name] = self.n.get(name, 0) + 1
+
+
+hk = _Hook()
+_lib.set_call_hook(hk)
+N = 30
+t0 = time.perf_counter()
+bench.run_steps(tr, it, N)
+t1 = time.perf_counter()
+torch.cuda.synchronize()
+_lib.set_call_hook(None)
+tot = sum(hk.t.values())
+print(f"\nC-ABI calls: {sum(hk.n.values()) / N:.1f} per step, {1e3 * tot / N:.3f} ms/step inside the calls "
+      f"(of {1e3 * (t1 - t0) / N:.3f} ms/step host enqueue)")
+for k, v in sorted(hk.t.items(), key=lambda kv: -kv[1]):
+    print(f"  {k:28s} x{hk.n[k] / N:5.1f}  {1e6 * v / hk.n[k]:7.1f} us/call  {1e3 * v / N:.3f} ms/step")
