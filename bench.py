@@ -297,6 +297,26 @@ def ncu_traffic():
         return None
 
 
+def spmm_metric(tr):
+    """BASELINE.json's second metric, "SpMM HBM GB/s": the one-hop gcn-norm node-label aggregation
+    (nn/aggregators.py:176-213) of 16384 seed cells of THIS workload over their sampled neighbourhood,
+    algorithmic bytes / CUDA-event time with L2 flushed -- from dense fp32 / bf16 rows (the reference's
+    layout) and straight from the CSR count store (the product path).  tools/bench_spmm.py."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "tools"))
+    import bench_spmm
+    data = tr.node_masked_data
+    peaks = measured_peaks()
+    try:
+        r = bench_spmm.measure(data.store, data.device_graph(), n_rows=16384, verbose=False)
+    except Exception as e:                                  # noqa: BLE001 -- a side metric must not kill the line
+        return {"error": str(e)}
+    out = {"unit": "GB/s", "peak": peaks["hbm_gbs"], "shape": r["shape"]}
+    for k in ("dense_f32", "dense_bf16", "csr_store"):
+        out[k] = {"achieved": r[k]["gbs"], "frac": r[k]["gbs"] / peaks["hbm_gbs"], "ms": r[k]["ms"],
+                  "algorithmic_bytes": r[k]["algorithmic_bytes"]}
+    return out
+
+
 def run_steps(tr, it, n, read_loss=False):
     """n training iterations; returns the last loss dict (and host losses when read_loss)."""
     out = []
@@ -519,6 +539,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (nichecompass_b200 has no CPU path); "
                          "use --impl reference for the CPU baseline")
     res, (adata, wl, tr, rank, world) = run_ours(args)
+    if rank == 0 and world == 1:
+        res["spmm"] = spmm_metric(tr)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             import psutil

@@ -13,7 +13,14 @@ from nichecompass_b200.data.sampler import DeviceGraph, sample_subgraph  # noqa:
 from nichecompass_b200.data.datasets import adjacency_to_edge_index      # noqa: E402
 
 dev = torch.device("cuda")
-flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+_flush = []
+
+
+def _flush_buf():
+    if not _flush:
+        _flush.append(torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev))
+    return _flush[0]
+
 
 
 def timeit(fn, iters=10):
@@ -21,7 +28,7 @@ def timeit(fn, iters=10):
         fn()
     ts = []
     for _ in range(iters):
-        flush.zero_()
+        _flush_buf().zero_()
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record(); fn(); e.record(); torch.cuda.synchronize()
         ts.append(s.elapsed_time(e))
@@ -34,6 +41,14 @@ def main(n_cells=200_000, n_genes=5000, n_rows=16384):
     store = CSRFeatureStore.from_scipy(adata.X.tocsr(), dev)
     ei = adjacency_to_edge_index(adata.obsp["spatial_connectivities"])
     g = DeviceGraph(ei, n_cells, dev)
+    return measure(store, g, n_rows)
+
+
+def measure(store, g, n_rows=16384, verbose=True):
+    """-> {"dense_f32" | "dense_bf16" | "csr_store": {"ms", "algorithmic_bytes", "gbs"}}"""
+    n_cells, n_genes = g.num_nodes, store.n_cols
+    res = {}
+    say = print if verbose else (lambda *a, **k: None)
     seeds = torch.randperm(n_cells, device=dev)[:n_rows].to(torch.int32).sort().values
     n_id, graph = sample_subgraph(g, seeds, n_rows, [-1])
     n_sub = graph.n_nodes
@@ -41,13 +56,14 @@ def main(n_cells=200_000, n_genes=5000, n_rows=16384):
     deg = (graph.rowptr[1:n_rows + 1] - graph.rowptr[:n_rows]).float()
     entries = float(deg.sum()) + n_rows                         # gathered rows incl. the self term
     nnz_row = store.nnz / store.n_rows
-    print(f"n_rows {n_rows}, n_sub {n_sub}, gathered rows {entries:.0f} ({entries / n_rows:.2f}/row), store nnz/row {nnz_row:.1f}")
+    say(f"n_rows {n_rows}, n_sub {n_sub}, gathered rows {entries:.0f} ({entries / n_rows:.2f}/row), store nnz/row {nnz_row:.1f}")
     for dt, s in ((torch.float32, 4), (torch.bfloat16, 2)):
         x = ops.csr_gather_rows(store, n_id, n_sub, False, dt)
         out = torch.empty(n_rows, n_genes, dtype=torch.float32, device=dev)
         ms = timeit(lambda: ops.spmm_csr(x, graph.rowptr, graph.col, w, wself, True, n_rows, out=out))
         alg = entries * n_genes * s + n_rows * n_genes * 4 + entries * 8
-        print(f"dense x {dt}: {ms:.3f} ms, algorithmic {alg / 1e6:.0f} MB -> {alg / ms / 1e6:.0f} GB/s")
+        say(f"dense x {dt}: {ms:.3f} ms, algorithmic {alg / 1e6:.0f} MB -> {alg / ms / 1e6:.0f} GB/s")
+        res["dense_f32" if s == 4 else "dense_bf16"] = {"ms": ms, "algorithmic_bytes": alg, "gbs": alg / ms / 1e6}
     ms = timeit(lambda: ops.spmm_csr_store(store, n_id, graph.rowptr, graph.col, w, wself, True, n_rows))
     rp = store.rowptr
     ids = n_id.long()
@@ -55,7 +71,10 @@ def main(n_cells=200_000, n_genes=5000, n_rows=16384):
     live = torch.arange(graph.col.numel(), device=dev) < graph.rowptr[n_rows]
     gathered_nnz = float((nnz_n[graph.col.long()] * live).sum() + nnz_n[:n_rows].sum())
     alg = gathered_nnz * 8 + n_rows * n_genes * 4 + entries * 8
-    print(f"CSR store: {ms:.3f} ms, algorithmic {alg / 1e6:.0f} MB ({gathered_nnz:.0f} nnz) -> {alg / ms / 1e6:.0f} GB/s")
+    say(f"CSR store: {ms:.3f} ms, algorithmic {alg / 1e6:.0f} MB ({gathered_nnz:.0f} nnz) -> {alg / ms / 1e6:.0f} GB/s")
+    res["csr_store"] = {"ms": ms, "algorithmic_bytes": alg, "gbs": alg / ms / 1e6}
+    res["shape"] = {"n_rows": n_rows, "n_sub": n_sub, "gathered_rows": entries, "n_genes": n_genes}
+    return res
 
 
 if __name__ == "__main__":

@@ -21,23 +21,23 @@ it = bench.batch_stream(tr)
 bench.run_steps(tr, it, 5)
 torch.cuda.synchronize()
 STEPS = 4
-with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True) as prof:
+with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], with_stack=True,
+             experimental_config=torch._C._profiler._ExperimentalConfig(verbose=True)) as prof:
     bench.run_steps(tr, it, STEPS)
     torch.cuda.synchronize()
 rows = {}
-for e in prof.key_averages(group_by_stack_n=16):
-    dt = getattr(e, "self_device_time_total", 0) or getattr(e, "self_cuda_time_total", 0)
-    if not e.key.startswith("aten::"):
-        continue
-    site = next((f for f in e.stack if "nichecompass_b200/" in f or "bench.py" in f), "?")
-    site = site.split("nichecompass_b200/")[-1]
-    k = (e.key, site)
+for e in prof.events():
+    if not e.name.startswith("aten::") or e.cpu_parent is not None and e.cpu_parent.name.startswith("aten::"):
+        continue                                    # top-level aten ops only
+    site = next((f for f in (e.stack or []) if "nichecompass_b200/" in f or "bench.py" in f), "?")
+    site = site.split("nichecompass_b200/")[-1][:70]
+    k = (e.name, site)
     r = rows.setdefault(k, [0.0, 0.0, 0])
-    r[0] += dt / STEPS
-    r[1] += e.self_cpu_time_total / STEPS
-    r[2] += e.count / STEPS
+    r[0] += getattr(e, "device_time_total", 0) / STEPS
+    r[1] += e.cpu_time_total / STEPS
+    r[2] += 1 / STEPS
 tot_d = sum(r[0] for r in rows.values())
 tot_c = sum(r[1] for r in rows.values())
-print(f"aten ops: device {tot_d:.1f} us / step, host (self cpu) {tot_c:.1f} us / step")
-for (k, site), (d, c, n) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:70]:
-    print(f"dev {d:7.1f} us  cpu {c:7.1f} us  x{n:5.1f}  {k:26s} {site}")
+print(f"top-level aten ops: device {tot_d:.1f} us / step, host {tot_c:.1f} us / step, {sum(r[2] for r in rows.values()):.0f} ops / step")
+for (k, site), (d, c, n) in sorted(rows.items(), key=lambda kv: -kv[1][1])[:90]:
+    print(f"dev {d:7.1f} us  cpu {c:7.1f} us  x{n:5.1f}  {k:24s} {site}")

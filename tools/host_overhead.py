@@ -82,3 +82,49 @@ print(f"\nC-ABI calls: {sum(hk.n.values()) / N:.1f} per step, {1e3 * tot / N:.3f
       f"(of {1e3 * (t1 - t0) / N:.3f} ms/step host enqueue)")
 for k, v in sorted(hk.t.items(), key=lambda kv: -kv[1]):
     print(f"  {k:28s} x{hk.n[k] / N:5.1f}  {1e6 * v / hk.n[k]:7.1f} us/call  {1e3 * v / N:.3f} ms/step")
+
+# where does the link loader's host time go?  (statements of LinkLoader.__iter__, timed one by one while a
+# training step is in flight on the compute stream, as in the real loop)
+import math                                                           # noqa: E402
+from nichecompass_b200.data.sampler import sample_subgraph, unique_sorted   # noqa: E402
+ld = tr.edge_train_loader
+g = ld.data.device_graph()
+dev = g.device
+side = torch.cuda.Stream()
+order = torch.randperm(ld.pos.size(1)).to(dev)
+pos_dev = ld.pos.to(dev, torch.int32)
+acc = {}
+batches = [next(it) for _ in range(12)]
+torch.cuda.synchronize()
+
+
+def tick(name, t0):
+    t1 = time.perf_counter()
+    acc[name] = acc.get(name, 0.0) + (t1 - t0)
+    return t1
+
+
+for b in range(10):
+    tr.train_iteration(*batches[b])                                   # keeps the compute stream busy
+    with torch.cuda.stream(side):
+        t = time.perf_counter()
+        idx = order[b * ld.batch_size:(b + 1) * ld.batch_size]
+        t = tick("slice", t)
+        pos = pos_dev[:, idx]
+        t = tick("index pos[:, idx]", t)
+        pos2 = torch.index_select(pos_dev, 1, idx)
+        t = tick("index_select", t)
+        src_neg = torch.randint(g.num_nodes, (ld.batch_size,))
+        dst_neg = torch.randint(g.num_nodes, (ld.batch_size,))
+        neg = torch.stack((src_neg, dst_neg)).to(torch.int32).pin_memory().to(dev, non_blocking=True)
+        t = tick("negatives", t)
+        ids = torch.cat((pos[0], neg[0], pos[1], neg[1])).contiguous()
+        t = tick("cat", t)
+        seeds, inv, n_seed = unique_sorted(ids)
+        t = tick("unique_sorted (sync)", t)
+        n_id, graph = sample_subgraph(g, seeds.contiguous(), n_seed, ld.num_neighbors, 0, b)
+        t = tick("sample_subgraph (sync)", t)
+torch.cuda.synchronize()
+print("\nlink loader statements, host us per batch:")
+for k, v in acc.items():
+    print(f"  {k:26s} {1e5 * v:8.1f}")
