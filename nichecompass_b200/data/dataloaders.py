@@ -14,7 +14,10 @@ from typing import Iterator, List, Optional
 import torch
 
 from .dataprocessors import GraphData
-from .sampler import SampledBatch, sample_subgraph, unique_sorted
+from collections import deque
+
+from .sampler import (SampledBatch, sample_subgraph_finish, sample_subgraph_launch, unique_sorted_finish,
+                      unique_sorted_launch)
 
 
 def _epoch_permutation(n: int, shuffle: bool) -> torch.Tensor:
@@ -43,6 +46,14 @@ class NodeLoader:
         self._batch_counter = 0
         self._input_dev = None
         self.rank, self.world_size = 0, 1
+        self.pipeline = False
+
+    def set_pipeline(self, on: bool):
+        """Software pipelining of the sampler: the kernels of batch k + 1 are launched before the sizes
+        of batch k are read back, so the read-back never waits for the device (the sampling kernels
+        share the GPU with the training step and would otherwise finish late).  The host generators
+        are consumed in the same order, one batch earlier."""
+        self.pipeline = bool(on)
 
     def set_shard(self, rank: int, world_size: int):
         """Data parallelism: this process yields batches rank, rank + W, ... of the common
@@ -63,6 +74,7 @@ class NodeLoader:
             self._input_dev = self.input_nodes.to(dev, torch.int32)
         order = _epoch_permutation(self.input_nodes.numel(), self.shuffle).to(dev)
         cats = self.data.cats_device()
+        inflight, depth = deque(), (1 if self.pipeline else 0)
         for i in range(len(self)):
             b = (i * self.world_size + self.rank) % self.n_batches_total
             batch_id = self._batch_counter + self.rank
@@ -70,11 +82,20 @@ class NodeLoader:
             idx = order[b * self.batch_size:(b + 1) * self.batch_size]
             seeds = self._input_dev[idx].contiguous()
             n_seed = seeds.numel()
-            n_id, graph = sample_subgraph(g, seeds, n_seed, self.num_neighbors, self.rng_seed, batch_id)
-            batch = SampledBatch(self.data.store, n_id, graph, n_seed, cats)
-            batch.batch_size = n_seed
-            batch.input_id = idx
-            yield batch
+            inflight.append((sample_subgraph_launch(g, seeds, n_seed, self.num_neighbors, self.rng_seed, batch_id),
+                             n_seed, idx))
+            if len(inflight) > depth:
+                yield self._finish(inflight.popleft(), cats)
+        while inflight:
+            yield self._finish(inflight.popleft(), cats)
+
+    def _finish(self, rec, cats) -> SampledBatch:
+        handle, n_seed, idx = rec
+        n_id, graph = sample_subgraph_finish(handle)
+        batch = SampledBatch(self.data.store, n_id, graph, n_seed, cats)
+        batch.batch_size = n_seed
+        batch.input_id = idx
+        return batch
 
 
 class LinkLoader:
@@ -94,6 +115,12 @@ class LinkLoader:
         self._batch_counter = 0
         self._pos_dev = None
         self.rank, self.world_size = 0, 1
+        self.pipeline = False
+
+    def set_pipeline(self, on: bool):
+        """See ``NodeLoader.set_pipeline``.  A link batch has two dependent read-backs (number of unique
+        seeds, then the sub-graph sizes), hence three stages: unique(k + 2) | sample(k + 1) | finish(k)."""
+        self.pipeline = bool(on)
 
     def set_shard(self, rank: int, world_size: int):
         """See ``NodeLoader.set_shard``.  Every rank draws the negatives of ALL batches so that the
@@ -117,6 +144,7 @@ class LinkLoader:
         n_nodes = self.data.num_nodes
         n_total = self.n_batches_total
         n_round = len(self) * self.world_size
+        qa, qb, depth = deque(), deque(), (1 if self.pipeline else 0)
         for q in range(n_round):
             b = q % n_total
             n_pos_b = min(self.batch_size, self.pos.size(1) - b * self.batch_size)
@@ -135,14 +163,34 @@ class LinkLoader:
             if dev.type == "cuda":
                 neg = neg.pin_memory().to(dev, non_blocking=True)
             ids = torch.cat((pos[0], neg[0], pos[1], neg[1])).contiguous()
-            seeds, inv, n_seed = unique_sorted(ids)
-            n_id, graph = sample_subgraph(g, seeds.contiguous(), n_seed, self.num_neighbors, self.rng_seed,
-                                          batch_id)
-            batch = SampledBatch(self.data.store, n_id, graph, n_seed, cats)
-            batch.edge_label_index = inv.view(2, -1)
-            batch.edge_label = torch.cat((torch.ones(num_pos, device=dev), torch.zeros(num_neg, device=dev)))
-            batch.input_id = idx
-            yield batch
+            # stage A: unique seeds of batch q
+            qa.append((unique_sorted_launch(ids), batch_id, idx, num_pos, num_neg))
+            if len(qa) > depth:
+                qb.append(self._stage_b(qa.popleft(), g))
+            if len(qb) > depth:
+                yield self._stage_c(qb.popleft(), cats, dev)
+        while qa:
+            qb.append(self._stage_b(qa.popleft(), g))
+            if len(qb) > depth:
+                yield self._stage_c(qb.popleft(), cats, dev)
+        while qb:
+            yield self._stage_c(qb.popleft(), cats, dev)
+
+    def _stage_b(self, rec, g):
+        """Number of unique seeds is known -> launch the neighbourhood sampler."""
+        uh, batch_id, idx, num_pos, num_neg = rec
+        seeds, inv, n_seed = unique_sorted_finish(uh)
+        sh = sample_subgraph_launch(g, seeds.contiguous(), n_seed, self.num_neighbors, self.rng_seed, batch_id)
+        return sh, inv, n_seed, idx, num_pos, num_neg
+
+    def _stage_c(self, rec, cats, dev) -> SampledBatch:
+        sh, inv, n_seed, idx, num_pos, num_neg = rec
+        n_id, graph = sample_subgraph_finish(sh)
+        batch = SampledBatch(self.data.store, n_id, graph, n_seed, cats)
+        batch.edge_label_index = inv.view(2, -1)
+        batch.edge_label = torch.cat((torch.ones(num_pos, device=dev), torch.zeros(num_neg, device=dev)))
+        batch.input_id = idx
+        return batch
 
 
 def initialize_dataloaders(node_masked_data: GraphData,

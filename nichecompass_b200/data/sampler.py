@@ -85,23 +85,72 @@ class SampledBatch:
         return out
 
 
-def unique_sorted(ids: torch.Tensor):
-    """(unique sorted ids, inverse, n_unique) of an int32 device vector -- one kernel, one sync."""
+class _PinnedRing:
+    """A few pinned int32 slots for asynchronous read-backs (cudaHostAlloc once, not per batch)."""
+
+    def __init__(self, width: int, slots: int = 16):
+        self.buf = torch.empty(slots, width, dtype=torch.int32).pin_memory() if torch.cuda.is_available() \
+            else torch.empty(slots, width, dtype=torch.int32)
+        self.i = 0
+
+    def next(self) -> torch.Tensor:
+        self.i = (self.i + 1) % self.buf.size(0)
+        return self.buf[self.i]
+
+
+_RING = {}
+
+
+def _readback_async(t: torch.Tensor):
+    """Starts the D2H copy of a small int32 device vector on the current stream; returns (pinned view,
+    event).  ``event.synchronize()`` then costs nothing when the kernels were launched a step earlier."""
+    ring = _RING.get(t.numel())
+    if ring is None:
+        ring = _RING[t.numel()] = _PinnedRing(t.numel())
+    host = ring.next()
+    host.copy_(t, non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record()
+    return host, ev
+
+
+def unique_sorted_launch(ids: torch.Tensor):
+    """First half of ``unique_sorted``: the kernel and an asynchronous read-back of the count."""
     n = ids.numel()
     if n > 16384:
         u, inv = torch.unique(ids, return_inverse=True)          # plumbing for very large link batches
-        return u.to(torch.int32), inv.to(torch.int32), int(u.numel())
+        return ("done", u.to(torch.int32), inv.to(torch.int32), int(u.numel()))
     uniq = torch.empty(n, dtype=torch.int32, device=ids.device)
     inv = torch.empty(n, dtype=torch.int32, device=ids.device)
     cnt = torch.empty(1, dtype=torch.int32, device=ids.device)
     call("nc_unique_sorted_i32", ids, n, uniq, inv, cnt)
-    nu = int(cnt.item())
+    host, ev = _readback_async(cnt)
+    return ("pending", uniq, inv, host, ev, ids)
+
+
+def unique_sorted_finish(h):
+    if h[0] == "done":
+        return h[1], h[2], h[3]
+    _, uniq, inv, host, ev, _ids = h
+    ev.synchronize()
+    nu = int(host[0])
     return uniq[:nu], inv, nu
+
+
+def unique_sorted(ids: torch.Tensor):
+    """(unique sorted ids, inverse, n_unique) of an int32 device vector -- one kernel, one sync."""
+    return unique_sorted_finish(unique_sorted_launch(ids))
 
 
 def sample_subgraph(g: DeviceGraph, seeds: torch.Tensor, n_seed: int, num_neighbors: List[int],
                     rng_seed: int = 0, batch_id: int = 0):
     """Returns (n_id int32 [n_sub], SubgraphCSR with n_dst = n_seed)."""
+    return sample_subgraph_finish(sample_subgraph_launch(g, seeds, n_seed, num_neighbors, rng_seed, batch_id))
+
+
+def sample_subgraph_launch(g: DeviceGraph, seeds: torch.Tensor, n_seed: int, num_neighbors: List[int],
+                           rng_seed: int = 0, batch_id: int = 0):
+    """Launches the sampling kernels and the asynchronous read-back of the sub-graph sizes."""
     hops = len(num_neighbors)
     k = int(num_neighbors[0])
     if any(int(v) != k for v in num_neighbors):
@@ -124,7 +173,14 @@ def sample_subgraph(g: DeviceGraph, seeds: torch.Tensor, n_seed: int, num_neighb
     counts = torch.empty(8, dtype=torch.int32, device=dev)
     call("nc_sample_subgraph", g.rowptr, g.col, seeds, n_seed, hops, k, int(rng_seed), int(batch_id),
          g.slot_ws(), n_id, cap_nodes, rowptr, col, cap_edges, ws, cap_cand, counts)
-    c = counts.cpu()                                       # the one host sync of a batch
+    host, ev = _readback_async(counts)
+    return (n_id, rowptr, col, n_seed, host, ev, seeds, ws, counts)
+
+
+def sample_subgraph_finish(h):
+    n_id, rowptr, col, n_seed, host, ev = h[:6]
+    ev.synchronize()                                       # the one host wait of a batch
+    c = host.tolist()
     n_sub, e_sub, overflow, max_row = int(c[0]), int(c[1]), int(c[2]), int(c[3])
     if overflow:
         raise RuntimeError("nc_sample_subgraph: capacity overflow (graph degree bound violated)")

@@ -131,6 +131,7 @@ class Trainer(BaseTrainerMixin):
         self.store_location_ = kwargs.pop("store_location", "device")
         self.prefetch_ = kwargs.pop("prefetch", True)
         self.joint_encoder_ = kwargs.pop("joint_encoder", True)
+        self.pipeline_sampler_ = kwargs.pop("pipeline_sampler", True)
         kwargs.pop("latent_dtype", None)          # forwarded by NicheCompass.train, unused here (as in the reference)
         self.epoch = -1
         self.training_time = 0
@@ -198,6 +199,10 @@ class Trainer(BaseTrainerMixin):
         # data parallelism: the training loaders are strided over the ranks; validation is replicated
         for ld in (self.edge_train_loader, self.node_train_loader):
             ld.set_shard(self.rank_, self.world_size_)
+        # sampler kernels of the next batches are launched before the sizes of the current one are read back
+        for ld in (self.edge_train_loader, self.node_train_loader, self.edge_val_loader, self.node_val_loader):
+            if ld is not None:
+                ld.set_pipeline(self.pipeline_sampler_)
         self._side_streams = ([torch.cuda.Stream(), torch.cuda.Stream()] if self.prefetch_ else [None, None])
 
     # ------------------------------------------------------------------ one iteration

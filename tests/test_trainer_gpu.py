@@ -49,6 +49,9 @@ def _cpu_run(adata, cfg, p32, n_iters, edge_bs, **kw):
 def _gpu_run(adata, cfg, p32, eps, n_iters, edge_bs, conv="gatv2conv", dtype=torch.float32, **tkw):
     from nichecompass_b200.train import Trainer
     with contextlib.redirect_stdout(io.StringIO()):
+        # the CPU loop draws from the global host generator strictly on demand: compare without the
+        # sampler's software pipelining (same draws per loader, but interleaved one / two batches earlier)
+        tkw.setdefault("pipeline_sampler", False)
         tr = Trainer(adata, _module(cfg, p32, conv), edge_batch_size=edge_bs, seed=0, monitor=False,
                      compute_dtype=dtype, **tkw)
         tr.setup_training(lr=1e-3, **LAM)
@@ -190,3 +193,34 @@ def test_joint_encoder_pass_equals_separate_passes(dtype):
         for k in ss:
             if ss[k].is_floating_point():
                 assert float((sj[k] - ss[k]).abs().max()) <= 2 * 1e-3 * 3 + 1e-9, k
+
+
+def test_pipelined_sampler_yields_the_same_batches():
+    """Loaders with the software-pipelined sampler (kernels of batch k+1 / k+2 in flight while batch k is
+    finished) against the synchronous ones: identical batch sequences, each loader iterated on its own."""
+    from nichecompass_b200.data import initialize_dataloaders, prepare_data
+    adata = H.tiny_problem(n_cells=260, n_genes=30, n_prior_gp=8)
+    with contextlib.redirect_stdout(io.StringIO()):
+        dd = prepare_data(adata=adata, cat_covariates_label_encoders=[], edge_val_ratio=0.1, node_val_ratio=0.1,
+                          device=torch.device("cuda"))
+    out = {}
+    for pipe in (False, True):
+        torch.manual_seed(11)
+        lds = initialize_dataloaders(dd["node_masked_data"], dd["edge_train_data"], dd["edge_val_data"],
+                                     edge_batch_size=16, node_batch_size=8)
+        seqs = {}
+        for name in ("edge_train_loader", "node_train_loader"):
+            lds[name].set_pipeline(pipe)
+            seq = []
+            for b in lds[name]:
+                seq.append((b.n_id.cpu(), b.graph.rowptr.cpu(), b.graph.col.cpu(), b.n_seed, b.graph.max_deg,
+                            None if b.edge_label_index is None else b.edge_label_index.cpu()))
+            seqs[name] = seq
+        out[pipe] = seqs
+    for name in out[False]:
+        a, b = out[False][name], out[True][name]
+        assert len(a) == len(b) and len(a) > 3
+        for x, y in zip(a, b):
+            assert torch.equal(x[0], y[0]) and torch.equal(x[1], y[1]) and torch.equal(x[2], y[2])
+            assert x[3] == y[3] and x[4] == y[4]
+            assert (x[5] is None and y[5] is None) or torch.equal(x[5], y[5])
