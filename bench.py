@@ -292,8 +292,8 @@ def make_trainer(adata, wl, args, store_location="device"):
 
 def ncu_traffic():
     """DRAM bytes per GEMM launch (read + write) from the committed ncu capture of one C2-shaped step
-    (profiles/r1f_gemm_traffic.json, written from the launch list of tools/gpu_call5.sh); None if absent."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1f_gemm_traffic.json")
+    (profiles/r1k_gemm_traffic.json, written from the launch list of tools/gpu_call5.sh); None if absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1k_gemm_traffic.json")
     try:
         with open(path) as fh:
             return float(json.load(fh)["dram_bytes_per_launch"])
