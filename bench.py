@@ -29,7 +29,9 @@ Legs of the default arm ("ours"):
   cpu_baseline  (rank 0, N = 1) the CPU oracle's training loop (oracle/train_ref.py: a restatement
                 of the reference's PyTorch + PyG path) on the same data and batch sizes, timed on a
                 bounded number of steps.
---impl reference times that CPU loop alone with the same metric / config.
+--impl reference times that CPU loop alone with the same metric / config; one CPU step of the C2
+workload takes ~5 s, so the loop stops after --ref-wall-s seconds (default 150, at least 3 timed
+steps) and reports the steps it timed ("steps") beside the K asked for ("steps_requested").
 """
 import argparse
 import contextlib
@@ -84,6 +86,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ref-wall-s", type=float, default=150.0,
+                    help="--impl reference: stop the CPU loop after this many seconds (>= 3 timed steps); a CPU step of "
+                         "the C2 workload takes ~5 s, so K steps are a bounded sample of the epoch")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--edge-batch-size", type=int, default=256, help="reference default (NicheCompass.train)")
     ap.add_argument("--cells", type=int, default=None, help="override the number of cells (quick runs)")
@@ -515,7 +520,7 @@ def run_ours(args):
 
 
 # ----------------------------------------------------------------------------- CPU baseline / reference arm
-def cpu_reference(adata, wl, args, steps=None, warmup=1, budget_s=20.0):
+def cpu_reference(adata, wl, args, steps=None, warmup=1, budget_s=20.0, wall_s=None):
     """The reference's hot loop on the host cores: oracle/train_ref.py (PyTorch CPU restatement of the
     reference module + PyG semantics + loaders; the unmodified reference cannot be imported on the box --
     torch_geometric / torch_sparse / anndata / mlflow are not installed and /root/reference does not
@@ -534,17 +539,28 @@ def cpu_reference(adata, wl, args, steps=None, warmup=1, budget_s=20.0):
                         loss_kwargs={k: v for k, v in LAMBDAS.items()})
     log(f"[bench] cpu reference set-up {time.time() - t0:.1f} s, {cores} threads")
     it = zip(ref.edge_loader, TR.R.cycle_iterable(ref.node_loader))
+    t_start = time.perf_counter()
+    done_w = 0
     for _ in range(warmup):
         e, nb = next(it)
         t1 = time.perf_counter()
         ref.iteration(e, nb)
         first = time.perf_counter() - t1
+        done_w += 1
+        if wall_s is not None and time.perf_counter() - t_start > 0.2 * wall_s:
+            break                                      # a 5 s CPU step: the warm-up is bounded by the clock too
+    warmup = done_w
     if steps is None:
         steps = int(min(max(budget_s / max(first, 1e-3), 2), 50))
     t1 = time.perf_counter()
+    done = 0
     for _ in range(steps):
         e, nb = next(it)
         ref.iteration(e, nb)
+        done += 1
+        if wall_s is not None and done >= 3 and time.perf_counter() - t_start > wall_s:
+            break                                      # bounded sample: the per-step time is what the metric needs
+    steps = done
     sec_step = (time.perf_counter() - t1) / steps
     steps_per_epoch = math.ceil(ld.n_edges_train / args.edge_batch_size)
     value = wl["n_cells"] / (steps_per_epoch * sec_step)
@@ -562,10 +578,12 @@ def run_reference(args):
     if args.cells:
         wl["n_cells"] = args.cells
     adata = build_adata(wl, args.seed)
-    value, sec_step, steps, cores, sample = cpu_reference(adata, wl, args, steps=args.steps, warmup=max(args.warmup, 1))
+    value, sec_step, steps, cores, sample = cpu_reference(adata, wl, args, steps=args.steps, warmup=max(args.warmup, 1),
+                                                          wall_s=args.ref_wall_s)
     return {
         "impl": "reference", "metric": "training cells/sec per epoch", "value": value, "unit": "cells/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": max(args.warmup, 1), "ms_per_step": sec_step * 1e3,
+        "n_gpus": args.gpus, "steps": steps, "steps_requested": args.steps, "warmup": max(args.warmup, 1),
+        "ms_per_step": sec_step * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["name"], "n_cells": wl["n_cells"], "n_genes": wl["n_genes"], "k": wl["k"],
                    "edge_batch_size": args.edge_batch_size},
