@@ -194,6 +194,11 @@ def _col_sum(x: torch.Tensor, n_cols: int, out: Optional[torch.Tensor] = None) -
 
 
 # --------------------------------------------------------------------------- GATv2 encoder
+# ``W1`` value of the encoder functions meaning "``x_enc`` is the hidden tensor itself" (fc_l2 + BatchNorm in
+# front of the convs, nn/encoders.py:180-182): no ReLU between the input and the message passing.
+HIDDEN_INPUT = "hidden"
+
+
 class EncoderGATv2Fn(torch.autograd.Function):
     """fc_l1 + ReLU + the four GATv2Conv heads of nn/encoders.py:144-208 (n_fc_layers=1,
     n_layers=1) for the first ``graph.n_dst`` nodes: returns [n_dst, 2P] = (mu | logstd) with
@@ -209,7 +214,9 @@ class EncoderGATv2Fn(torch.autograd.Function):
         ``conv_l1`` [n_sub, Hd] and hidden = relu(x_enc) (nn/encoders.py:191-194)."""
         NC = len(tensors) // 6
         conv = [tensors[6 * c:6 * c + 6] for c in range(NC)]
-        pre = W1 is None
+        ident = isinstance(W1, str)
+        pre = W1 is None or ident
+        ctx.ident = ident
         dev = x_enc.device
         n_sub, n_dst = graph.n_nodes, graph.n_dst
         assert x_enc.size(0) == n_sub and (pre or x_enc.dtype == act)
@@ -236,7 +243,10 @@ class EncoderGATv2Fn(torch.autograd.Function):
         Hbuf = torch.zeros(n_sub, ldh, dtype=act, device=dev) if ldh != Hd else torch.empty(n_sub, ldh, dtype=act, device=dev)
         if pre:
             xin = x_enc.detach().float().contiguous()
-            call("nc_relu_cast", xin, xin.stride(0), n_sub, Hd, Hbuf, dtype_code(act), ldh)
+            if ident:
+                Hbuf[:, :Hd].copy_(xin)
+            else:
+                call("nc_relu_cast", xin, xin.stride(0), n_sub, Hd, Hbuf, dtype_code(act), ldh)
         else:
             ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
         XL = torch.empty(n_sub, ldl, dtype=act, device=dev)
@@ -250,7 +260,7 @@ class EncoderGATv2Fn(torch.autograd.Function):
         ctx.save_for_backward(None if pre else x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr)
         ctx.meta = (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
                     [tuple(t.shape) for t in tensors], None if pre else tuple(W1.shape), act)
-        ctx.params = (W1, b1, conv, tight)          # arena residents receive their gradients in place
+        ctx.params = (None if pre else W1, b1, conv, tight)          # arena residents receive their gradients in place
         return out
 
     @staticmethod
@@ -306,8 +316,10 @@ class EncoderGATv2Fn(torch.autograd.Function):
         ops.gemm(dXL, Wl, trans_b=True, out=dH[:, :Hd], M=n_sub, N=Hd, K=NL)
         if n_dst > 0:
             ops.gemm(dXR, Wr, trans_b=True, out=dH[:n_dst, :Hd], accumulate=True, M=n_dst, N=Hd, K=NL)
-        dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
-        call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
+        dHp = None
+        if not ctx.ident:
+            dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
+            call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
         if pre:
             dW1 = db1 = None
         elif g_W1 is not None:
@@ -333,7 +345,8 @@ class EncoderGATv2Fn(torch.autograd.Function):
             dW1 = dW1.contiguous()
         dx = None
         if pre:
-            dx = dHp[:, :Hd].float() if ctx.needs_input_grad[0] else None      # d relu(x): gradient of conv_l1's output
+            if ctx.needs_input_grad[0]:      # d relu(x): gradient of conv_l1's output (or of the hidden tensor itself)
+                dx = dH[:, :Hd].contiguous() if ctx.ident else dHp[:, :Hd].float()
         elif ctx.needs_input_grad[0]:
             # only the trailing (embedding) columns of the encoder input can require grad
             dxf = ops.gemm(dHp, W1p, trans_b=True, out_dtype=torch.float32, M=n_sub, N=n_feat, K=Hd)
@@ -341,6 +354,47 @@ class EncoderGATv2Fn(torch.autograd.Function):
             dx[:, :n_feat] = dxf
             dx = dx.to(x_enc.dtype)
         return (dx, None, None, None, None, None, None, None, dW1, db1, *grads)
+
+
+class LinearActFn(torch.autograd.Function):
+    """``relu?(x @ W.T + b)`` as fp32 [n, N] for the fully connected layers in front of the convs when the
+    encoder is not the single fused pass (n_fc_layers == 2 or dropout, nn/encoders.py:179-182).  ``x``:
+    [n, >= K] in the compute dtype (padding columns ignored) or fp32 (cast here)."""
+
+    @staticmethod
+    def forward(ctx, x, W, b, act, relu, cache_key):
+        n, (N, K) = x.size(0), W.shape
+        xa = x.detach()
+        if xa.dtype != act or xa.stride(1) != 1 or xa.stride(0) % 8:
+            buf = torch.zeros(n, pad8(K), dtype=act, device=x.device)
+            buf[:, :K] = xa[:, :K]
+            xa = buf
+        Wp = pack_rows((cache_key, "W"), [W], act, K)
+        out = ops.gemm(xa, Wp, bias=b.detach().float(), relu=relu, out_dtype=torch.float32, M=n, N=N, K=K)
+        ctx.save_for_backward(xa, Wp, out if relu else None)
+        ctx.meta = (act, K, N, x.dtype, x.size(1))
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        xa, Wp, out = ctx.saved_tensors
+        act, K, N, x_dtype, x_cols = ctx.meta
+        n = xa.size(0)
+        d = dout.float()
+        if out is not None:
+            d = d * (out > 0)
+        da = torch.zeros(n, pad8(N), dtype=act, device=d.device)
+        da[:, :N] = d
+        dW = ops.gemm(da, xa, trans_a=True, trans_b=True, out_dtype=torch.float32, M=N, N=K, K=n) \
+            if ctx.needs_input_grad[1] else None
+        db = d.sum(0) if ctx.needs_input_grad[2] else None
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dxf = ops.gemm(da, Wp, trans_b=True, out_dtype=torch.float32, M=n, N=K, K=N)
+            dx = torch.zeros(n, x_cols, dtype=torch.float32, device=d.device)
+            dx[:, :K] = dxf
+            dx = dx.to(x_dtype)
+        return dx, (None if dW is None else dW.contiguous()), db, None, None, None
 
 
 # --------------------------------------------------------------------------- latent plumbing
@@ -822,7 +876,9 @@ class EncoderGCNFn(torch.autograd.Function):
         """``W1 is None``: second conv layer of the 2-layer encoder (see ``EncoderGATv2Fn.forward``)."""
         NC = len(tensors) // 2
         Ws, bs = [tensors[2 * c] for c in range(NC)], [tensors[2 * c + 1] for c in range(NC)]
-        pre = W1 is None
+        ident = isinstance(W1, str)
+        pre = W1 is None or ident
+        ctx.ident = ident
         dev = x_enc.device
         n_sub, n_dst = graph.n_nodes, graph.n_dst
         Hd = x_enc.size(1) if pre else W1.size(0)
@@ -835,7 +891,10 @@ class EncoderGCNFn(torch.autograd.Function):
         Hbuf = torch.zeros(n_sub, ldh, dtype=act, device=dev)
         if pre:
             xin = x_enc.detach().float().contiguous()
-            call("nc_relu_cast", xin, xin.stride(0), n_sub, Hd, Hbuf, dtype_code(act), ldh)
+            if ident:
+                Hbuf[:, :Hd].copy_(xin)
+            else:
+                call("nc_relu_cast", xin, xin.stride(0), n_sub, Hd, Hbuf, dtype_code(act), ldh)
         else:
             ops.gemm(x_enc, W1p, bias=b1.detach().float(), relu=True, out=Hbuf[:, :Hd], M=n_sub, N=Hd, K=n_feat)
         ldw = pad8(out_width)
@@ -867,8 +926,10 @@ class EncoderGCNFn(torch.autograd.Function):
         dWall = ops.gemm(dXW, Hbuf, trans_a=True, trans_b=True, out_dtype=torch.float32, M=out_width, N=Hd, K=n_sub)
         dH = torch.empty(n_sub, pad8(Hd), dtype=torch.float32, device=dev)
         ops.gemm(dXW, Wall, trans_b=True, out=dH[:, :Hd], M=n_sub, N=Hd, K=out_width)
-        dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
-        call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
+        dHp = None
+        if not ctx.ident:
+            dHp = torch.empty(n_sub, Hbuf.size(1), dtype=act, device=dev)
+            call("nc_relu_bwd", dH, dH.stride(0), Hbuf, dtype_code(act), Hbuf.stride(0), n_sub, Hd, dHp, dHp.stride(0))
         dW1 = db1 = None
         if not pre:
             dW1 = ops.gemm(dHp, x_enc, trans_a=True, trans_b=True, out_dtype=torch.float32, M=Hd, N=n_feat, K=n_sub)
@@ -879,7 +940,8 @@ class EncoderGCNFn(torch.autograd.Function):
             r += Cs[c]
         dx = None
         if pre:
-            dx = dHp[:, :Hd].float() if ctx.needs_input_grad[0] else None
+            if ctx.needs_input_grad[0]:
+                dx = dH[:, :Hd].contiguous() if ctx.ident else dHp[:, :Hd].float()
         elif ctx.needs_input_grad[0]:
             dxf = ops.gemm(dHp, W1p, trans_b=True, out_dtype=torch.float32, M=n_sub, N=n_feat, K=Hd)
             dx = torch.zeros_like(x_enc, dtype=torch.float32)

@@ -449,6 +449,7 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
         store = getattr(node_batch, "store", None)
         return (store is not None and getattr(edge_batch, "store", None) is store
                 and self.encoder.conv_layer == "gatv2conv" and self.encoder.n_layers == 1
+                and self.encoder.n_fc_layers == 1     # BatchNorm statistics are per encoder pass in the reference
                 and not (self.n_cat_covariates_ > 0 and "encoder" in self.cat_covariates_embeds_injection_))
 
     def forward_joint(self, node_batch, edge_batch, use_only_active_gps: bool = False):

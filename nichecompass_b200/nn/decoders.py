@@ -19,11 +19,12 @@ class CosineSimGraphDecoder(nn.Module):
     def __init__(self, dropout_rate: float = 0.):
         super().__init__()
         print(f"COSINE SIM GRAPH DECODER -> dropout_rate: {dropout_rate}")
-        if dropout_rate != 0.:
-            raise NotImplementedError("graph-decoder dropout is not implemented in the CUDA path")
         self.dropout_rate = dropout_rate
+        self.dropout = nn.Dropout(dropout_rate)
 
     def forward(self, z: torch.Tensor) -> torch.Tensor:
+        if self.dropout_rate != 0.:
+            z = self.dropout(z)                     # nn/decoders.py:56 (identity in eval mode)
         return CosineFn.apply(z.float())
 
 

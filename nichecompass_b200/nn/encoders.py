@@ -8,7 +8,7 @@ from typing import Literal, Optional, Tuple
 import torch
 import torch.nn as nn
 
-from ..functional import EncoderGATv2Fn, EncoderGCNFn, SubgraphCSR, new_cache_key
+from ..functional import HIDDEN_INPUT, EncoderGATv2Fn, EncoderGCNFn, LinearActFn, SubgraphCSR, new_cache_key
 from ..ops import pad8
 from .conv import GATv2Conv, GCNConv
 
@@ -19,8 +19,10 @@ class Encoder(nn.Module):
 
     Parameters are those of the reference ``Encoder``; ``use_bn`` is accepted and unused
     exactly as there (nn/encoders.py:52-53 documents it, the body never reads it).
-    Kernel coverage: ``n_fc_layers == 1``, ``n_layers`` 1 or 2 (``conv_l1`` over the whole sampled
-    sub-graph, ReLU, then the latent convs on the seed rows), ``dropout_rate == 0``.
+    Kernel coverage: ``n_layers`` 1 or 2 (``conv_l1`` over the whole sampled sub-graph, ReLU, then the
+    latent convs on the seed rows).  ``n_fc_layers == 1`` with ``dropout_rate == 0`` (the defaults) is ONE
+    fused function; ``n_fc_layers == 2`` (fc_l2 + BatchNorm1d, nn/encoders.py:93-96,180-182) or dropout
+    composes the same kernels layer by layer (``_encode_composed``), the convs reading the hidden tensor as is.
     """
 
     def __init__(self,
@@ -44,11 +46,8 @@ class Encoder(nn.Module):
               f"n_fc_layers: {n_fc_layers}, n_layers: {n_layers}, conv_layer: {conv_layer}, "
               f"n_attention_heads: {n_attention_heads if conv_layer == 'gatv2conv' else '0'}, "
               f"dropout_rate: {dropout_rate}, ")
-        if n_fc_layers != 1 or n_layers not in (1, 2):
-            raise NotImplementedError("nichecompass_b200 kernels cover n_fc_layers=1 and n_layers in (1, 2); "
-                                      "see DESIGN.md 'not yet covered'")
-        if dropout_rate != 0.:
-            raise NotImplementedError("dropout in the encoder is not implemented in the CUDA path")
+        if n_fc_layers not in (1, 2) or n_layers not in (1, 2):
+            raise NotImplementedError("nichecompass_b200 kernels cover n_fc_layers in (1, 2) and n_layers in (1, 2)")
         if cat_covariates_embed_mode != "input" and n_cat_covariates_embed_input != 0:
             raise NotImplementedError("cat_covariates_embed_mode='hidden' is not implemented")
         self.n_latent = n_latent
@@ -59,7 +58,15 @@ class Encoder(nn.Module):
         self.n_attention_heads = n_attention_heads
         self.cat_covariates_embed_mode = cat_covariates_embed_mode
         self.n_input = n_input + n_cat_covariates_embed_input
-        self.fc_l1 = nn.Linear(self.n_input, n_hidden)
+        if n_fc_layers == 2:                               # nn/encoders.py:93-96
+            self.fc_l1 = nn.Linear(self.n_input, int(self.n_input / 2))
+            self.fc_l2 = nn.Linear(int(self.n_input / 2), n_hidden)
+            self.fc_l2_bn = nn.BatchNorm1d(n_hidden)
+            self._key_fc = (new_cache_key(), new_cache_key())
+        else:
+            self.fc_l1 = nn.Linear(self.n_input, n_hidden)
+        self.dropout_rate = dropout_rate
+        self.dropout = nn.Dropout(dropout_rate)
         conv = (lambda c: GATv2Conv(n_hidden, c, heads=n_attention_heads)) if conv_layer == "gatv2conv" \
             else (lambda c: GCNConv(n_hidden, c))
         if conv_layer not in ("gatv2conv", "gcnconv"):
@@ -95,6 +102,13 @@ class Encoder(nn.Module):
         """Parameters the fused kernels consume stacked: laid out back to back by ``FlatAdam`` so
         that the stacked matrices, their bf16 shadows and their gradients are views."""
         convs = [c for c, _ in self._convs()]
+        if not self.fused:
+            # composed path: fc weights are ordinary parameters of the arena, the conv stacks as below
+            if self.conv_layer == "gatv2conv":
+                return [[c.lin_l.weight for c in convs], [c.lin_r.weight for c in convs],
+                        [c.lin_l.bias for c in convs], [c.lin_r.bias for c in convs],
+                        [c.att for c in convs], [c.bias for c in convs]]
+            return [[c.lin.weight for c in convs], [c.bias for c in convs]]
         if self.conv_layer == "gatv2conv":
             groups = [[c.lin_l.weight for c in convs], [c.lin_r.weight for c in convs],
                       [c.lin_l.bias for c in convs], [c.lin_r.bias for c in convs],
@@ -107,9 +121,48 @@ class Encoder(nn.Module):
             groups += [[self.conv_l1.lin.weight], [self.conv_l1.bias]]
         return groups
 
+    @property
+    def fused(self) -> bool:
+        """fc_l1 + ReLU + convs in one autograd function (the default configuration)."""
+        return self.n_fc_layers == 1 and self.dropout_rate == 0.
+
+    def _encode_composed(self, x_enc: torch.Tensor, graph: SubgraphCSR) -> torch.Tensor:
+        """nn/encoders.py:179-207 layer by layer: fc_l1 -> ReLU -> dropout [-> fc_l2 -> ReLU -> dropout ->
+        BatchNorm1d] [-> conv_l1 -> ReLU -> dropout] -> latent convs.  GEMMs and message passing are the
+        library's kernels; dropout and BatchNorm (batch statistics over the sampled sub-graph's nodes in
+        training, running statistics in eval) are torch element-wise / reduction ops on [n_sub, Hd] fp32."""
+        convs = self._convs()
+        offs = [o for _, o in convs]
+        act = self.compute_dtype
+        gat = self.conv_layer == "gatv2conv"
+        k1 = self._key_fc[0] if self.n_fc_layers == 2 else self._key
+        h = self.dropout(LinearActFn.apply(x_enc, self.fc_l1.weight, self.fc_l1.bias, act, True, (k1, "fc1")))
+        if self.n_fc_layers == 2:
+            h = self.dropout(LinearActFn.apply(h, self.fc_l2.weight, self.fc_l2.bias, act, True,
+                                               (self._key_fc[1], "fc2")))
+            h = self.fc_l2_bn(h)
+        Hd = h.size(1)
+        if self.n_layers == 2:
+            g_all = SubgraphCSR(graph.rowptr, graph.col, graph.n_nodes, graph.n_nodes, graph.max_deg)
+            if gat:
+                h = EncoderGATv2Fn.apply(h, g_all, Hd, self.n_attention_heads, [0], Hd, self._key_l1, act,
+                                         HIDDEN_INPUT, None, *self.conv_l1.param_tuple())
+            else:
+                h = EncoderGCNFn.apply(h, g_all, Hd, [0], Hd, self._key_l1, act, HIDDEN_INPUT, None,
+                                       self.conv_l1.lin.weight, self.conv_l1.bias)
+            h = self.dropout(torch.relu(h))
+        if gat:
+            tensors = [t for c, _ in convs for t in c.param_tuple()]
+            return EncoderGATv2Fn.apply(h, graph, Hd, self.n_attention_heads, offs, 2 * self.n_gps, self._key, act,
+                                        HIDDEN_INPUT, None, *tensors)
+        tensors = [t for c, _ in convs for t in (c.lin.weight, c.bias)]
+        return EncoderGCNFn.apply(h, graph, Hd, offs, 2 * self.n_gps, self._key, act, HIDDEN_INPUT, None, *tensors)
+
     def encode(self, x_enc: torch.Tensor, graph: SubgraphCSR) -> torch.Tensor:
         """``x_enc``: [n_sub, pad8(n_input)] in ``compute_dtype`` (log1p counts ++ optional
         embedding, zero padded).  Returns (mu | logstd) [graph.n_dst, 2 * n_gps] fp32."""
+        if not self.fused:
+            return self._encode_composed(x_enc, graph)
         convs = self._convs()
         offs = [o for _, o in convs]
         act = self.compute_dtype

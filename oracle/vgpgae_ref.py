@@ -131,11 +131,20 @@ class VGPGAERef:
         return pyg.gcn_conv(h, edge_index, p[f"encoder.{name}.lin.weight"], p[f"encoder.{name}.bias"])
 
     def encoder(self, x_enc, edge_index, embed=None):
-        """nn/encoders.py:144-208 (n_fc_layers == 1; dropout 0)."""
+        """nn/encoders.py:144-208 (dropout 0).  ``n_fc_layers`` 2: fc_l2 -> ReLU -> BatchNorm1d (:180-182), batch
+        statistics (biased variance, eps 1e-5) and the momentum-0.1 update of the running buffers in training,
+        the running statistics in eval (torch.nn.BatchNorm1d defaults, nn/encoders.py:96)."""
         c = self.cfg
         if embed is not None and c.get("cat_covariates_embed_mode", "input") == "input":
             x_enc = torch.cat((x_enc, embed), dim=1)
         h = torch.relu(F.linear(x_enc, self.p["encoder.fc_l1.weight"], self.p["encoder.fc_l1.bias"]))
+        if c.get("n_fc_layers", 1) == 2:
+            h = torch.relu(F.linear(h, self.p["encoder.fc_l2.weight"], self.p["encoder.fc_l2.bias"]))
+            bn = "encoder.fc_l2_bn."
+            if self.training:
+                self.p[bn + "num_batches_tracked"] += 1
+            h = F.batch_norm(h, self.p[bn + "running_mean"], self.p[bn + "running_var"], self.p[bn + "weight"],
+                             self.p[bn + "bias"], self.training, 0.1, 1e-5)
         if embed is not None and c.get("cat_covariates_embed_mode", "input") == "hidden":
             h = torch.cat((h, embed), dim=1)
         if c.get("n_layers", 1) == 2:
@@ -437,8 +446,20 @@ def init_params(cfg: dict, seed: int = 0, dtype=torch.float32) -> Dict[str, torc
         return uni(shape, (6.0 / (shape[-2] + shape[-1])) ** 0.5)
 
     enc_in = F_in + (n_emb if "encoder" in inj else 0)
-    p["encoder.fc_l1.weight"] = uni((Hd, enc_in), 1 / math.sqrt(enc_in))
-    p["encoder.fc_l1.bias"] = uni((Hd,), 1 / math.sqrt(enc_in))
+    if cfg.get("n_fc_layers", 1) == 2:                       # nn/encoders.py:93-96
+        mid = int(enc_in / 2)
+        p["encoder.fc_l1.weight"] = uni((mid, enc_in), 1 / math.sqrt(enc_in))
+        p["encoder.fc_l1.bias"] = uni((mid,), 1 / math.sqrt(enc_in))
+        p["encoder.fc_l2.weight"] = uni((Hd, mid), 1 / math.sqrt(mid))
+        p["encoder.fc_l2.bias"] = uni((Hd,), 1 / math.sqrt(mid))
+        p["encoder.fc_l2_bn.weight"] = 1 + uni((Hd,), 0.2)         # off the 1 / 0 defaults to exercise both
+        p["encoder.fc_l2_bn.bias"] = uni((Hd,), 0.1)
+        p["encoder.fc_l2_bn.running_mean"] = torch.zeros(Hd, dtype=dtype)
+        p["encoder.fc_l2_bn.running_var"] = torch.ones(Hd, dtype=dtype)
+        p["encoder.fc_l2_bn.num_batches_tracked"] = torch.zeros((), dtype=torch.int64)
+    else:
+        p["encoder.fc_l1.weight"] = uni((Hd, enc_in), 1 / math.sqrt(enc_in))
+        p["encoder.fc_l1.bias"] = uni((Hd,), 1 / math.sqrt(enc_in))
     convs = [("conv_mu", Pp), ("conv_logstd", Pp)]
     if cfg.get("n_layers", 1) == 2:
         convs.insert(0, ("conv_l1", Hd))
@@ -490,7 +511,7 @@ def init_params(cfg: dict, seed: int = 0, dtype=torch.float32) -> Dict[str, torc
     return p
 
 
-NON_TRAINABLE_SUFFIXES = (".mask", "running_mean_abs_mu")
+NON_TRAINABLE_SUFFIXES = (".mask", "running_mean_abs_mu", ".running_mean", ".running_var", ".num_batches_tracked")
 
 
 def trainable_keys(params: Dict[str, torch.Tensor]) -> List[str]:

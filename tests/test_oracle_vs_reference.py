@@ -342,3 +342,82 @@ def test_two_layer_encoder_matches_reference(conv_layer):
         assert H.rel_err(params[k].grad, p.grad) < 1e-9, k
         n_l1 += k.startswith("encoder.conv_l1.")
     assert n_l1 >= 2
+
+
+@pytest.mark.parametrize("conv_layer", ["gatv2conv", "gcnconv"])
+def test_two_fc_layers_with_batchnorm_match_reference(conv_layer):
+    """n_fc_layers_encoder=2 (nn/encoders.py:93-96,180-182): fc_l1 [F/2, F] -> fc_l2 -> ReLU -> BatchNorm1d.
+    Training mode (batch statistics + update of the running buffers), then eval mode (running statistics)."""
+    ref = load_reference()
+    adata = H.tiny_problem(seed=7)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=3, conv_layer=conv_layer, n_fc_layers=2)
+    torch.manual_seed(8)
+    feat = copy.deepcopy(cfg["features_idx_dict"])
+    with quiet():
+        m = ref.modules.VGPGAE(
+            n_input=cfg["n_input"], n_fc_layers_encoder=2, n_layers_encoder=1,
+            n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"], n_addon_gp=3,
+            cat_covariates_embeds_nums=[], n_output_genes=cfg["n_output_genes"],
+            target_rna_decoder_mask=cfg["target_rna_mask"], source_rna_decoder_mask=cfg["source_rna_mask"],
+            features_idx_dict=feat, features_scale_factors=torch.ones(2 * cfg["n_output_genes"]),
+            conv_layer_encoder=conv_layer, encoder_n_attention_heads=cfg["heads"],
+            node_label_method="one-hop-norm", active_gp_thresh_ratio=0.01,
+            include_cat_covariates_contrastive_loss=False).double()
+    m.train()
+    with torch.no_grad():
+        for k, p in m.named_parameters():
+            if k.endswith("bias"):
+                p.uniform_(-0.1, 0.1)
+        m.encoder.fc_l2_bn.weight.uniform_(0.8, 1.2)
+    sd = m.state_dict()
+    assert sd["encoder.fc_l1.weight"].shape == (cfg["n_input"] // 2, cfg["n_input"])
+    assert "encoder.fc_l2_bn.running_var" in sd
+    non_param = ("mask", "running_mean_abs_mu", "running_mean", "running_var", "num_batches_tracked")
+    params = {k: v.detach().clone().requires_grad_(v.dtype.is_floating_point and not k.endswith(non_param))
+              for k, v in sd.items()}
+    orc = VGPGAERef(cfg, params)
+    node_b, edge_b = make_batches(adata)
+    P = cfg["n_prior_gp"] + 3
+    g = torch.Generator().manual_seed(5)
+    eps_n = torch.randn(node_b.batch_size, P, generator=g, dtype=torch.float64)
+    eps_e = torch.randn(2 * edge_b.edge_label_index.size(1), P, generator=g, dtype=torch.float64)
+    draws = [eps_n, eps_e]
+    real = torch.randn_like
+    torch.randn_like = lambda t, *a, **k: draws.pop(0)
+    try:
+        rn = m(data_batch=node_b, decoder="omics")
+        re_ = m(data_batch=edge_b, decoder="graph")
+    finally:
+        torch.randn_like = real
+    lam = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lambda_l1_addon=30.,
+               lambda_group_lasso=2., lambda_gene_expr_recon=300., lambda_edge_recon=500000.)
+    rl = m.loss(edge_model_output=re_, node_model_output=rn, **lam)
+    rl["optim_loss"].backward()
+    on = orc.forward(node_b, "omics", eps=eps_n)
+    oe = orc.forward(edge_b, "graph", eps=eps_e)
+    ol = orc.loss(oe, on, **lam)
+    ol["optim_loss"].backward()
+    for k in ("mu", "logstd", "target_rna_nb_means", "source_rna_nb_means"):
+        assert H.rel_err(on[k], rn[k]) < 1e-10, k
+    assert H.rel_err(oe["edge_recon_logits"], re_["edge_recon_logits"]) < 1e-10
+    for k, v in rl.items():
+        assert H.rel_err(torch.as_tensor(ol[k]), torch.as_tensor(v)) < 1e-10, k
+    n_fc = 0
+    for k, p in m.named_parameters():
+        if p.grad is None:
+            continue
+        assert H.rel_err(params[k].grad, p.grad) < 1e-9, k
+        n_fc += k.startswith(("encoder.fc_l2", "encoder.fc_l1"))
+    assert n_fc == 6                                        # fc_l1, fc_l2, fc_l2_bn: weight + bias each
+    # the running buffers after two training passes (node batch, edge batch)
+    sd2 = m.state_dict()
+    for k in ("running_mean", "running_var"):
+        assert H.rel_err(params[f"encoder.fc_l2_bn.{k}"], sd2[f"encoder.fc_l2_bn.{k}"]) < 1e-12, k
+    assert int(params["encoder.fc_l2_bn.num_batches_tracked"]) == int(sd2["encoder.fc_l2_bn.num_batches_tracked"]) == 2
+    # eval mode: running statistics
+    m.eval()
+    orc.training = False
+    with torch.no_grad():
+        mu_r = m.get_latent_representation(node_batch=node_b, only_active_gps=False)
+    mu_o = orc.get_latent_representation(node_b, only_active_gps=False)
+    assert H.rel_err(mu_o, mu_r) < 1e-10

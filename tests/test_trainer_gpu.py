@@ -25,7 +25,7 @@ LAM = dict(lambda_l1_masked=0., lambda_l1_addon=30., lambda_group_lasso=1.5, lam
 def _module(cfg, p32, conv="gatv2conv"):
     from nichecompass_b200.modules import VGPGAE
     with contextlib.redirect_stdout(io.StringIO()):
-        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=cfg.get("n_fc_layers", 1), n_layers_encoder=1,
                    n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"], n_addon_gp=cfg["n_addon_gp"],
                    cat_covariates_embeds_nums=[], n_output_genes=cfg["n_output_genes"],
                    target_rna_decoder_mask=cfg["target_rna_mask"], source_rna_decoder_mask=cfg["source_rna_mask"],
@@ -63,6 +63,28 @@ def _gpu_run(adata, cfg, p32, eps, n_iters, edge_bs, conv="gatv2conv", dtype=tor
         if i + 1 == n_iters:
             break
     return tr, logs
+
+
+def test_training_iterations_with_two_fc_layers_match_cpu_loop():
+    """n_fc_layers_encoder=2: three Adam iterations through the Trainer (fc_l2 / BatchNorm parameters in the
+    flat arena, running statistics updated by both encoder passes of every iteration)."""
+    adata = H.tiny_problem(n_cells=220, n_genes=44, n_prior_gp=12)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=4, n_fc_layers=2)
+    p32 = init_params(cfg, seed=3)
+    ref, ref_logs, p64 = _cpu_run(adata, cfg, p32, 3, 24)
+    tr, logs = _gpu_run(adata, cfg, p32, ref.noise_log, 3, 24)
+    for it, (a, b) in enumerate(zip(logs, ref_logs)):
+        for k in b:
+            assert abs(a[k] - b[k]) <= 5e-5 * abs(b[k]) * (1 + it) + 1e-12, (it, k, a[k], b[k])
+    sd = tr.model.state_dict()
+    assert int(sd["encoder.fc_l2_bn.num_batches_tracked"]) == 6
+    for k in ("running_mean", "running_var"):
+        # Adam moves an element whose gradient sits at fp32 rounding level by +-lr per step (see below)
+        assert H.rel_err(sd[f"encoder.fc_l2_bn.{k}"], p64[f"encoder.fc_l2_bn.{k}"]) < 2e-2, k
+    for k in ("encoder.fc_l2.weight", "encoder.fc_l2_bn.weight", "encoder.fc_l1.bias"):
+        d = (sd[k].double().cpu() - p64[k].detach()).abs()
+        assert float(d.max()) <= 2 * 1e-3 * 3 + 1e-9, k
+        assert float((sd[k].double().cpu() - p32[k].double()).abs().max()) > 0, k      # the optimiser moved it
 
 
 @pytest.mark.parametrize("conv", ["gatv2conv", "gcnconv"])

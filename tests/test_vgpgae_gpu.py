@@ -25,7 +25,10 @@ LAM = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lamb
 def build_module(cfg, params, conv_layer, node_label_method):
     from nichecompass_b200.modules import VGPGAE
     with contextlib.redirect_stdout(io.StringIO()):
-        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=cfg.get("n_layers", 1),
+        m = VGPGAE(n_input=cfg["n_input"], n_fc_layers_encoder=cfg.get("n_fc_layers", 1),
+                   n_layers_encoder=cfg.get("n_layers", 1),
+                   dropout_rate_encoder=cfg.get("dropout_rate_encoder", 0.),
+                   dropout_rate_graph_decoder=cfg.get("dropout_rate_graph_decoder", 0.),
                    n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"],
                    n_addon_gp=cfg["n_addon_gp"], cat_covariates_embeds_nums=[],
                    n_output_genes=cfg["n_output_genes"],
@@ -36,7 +39,8 @@ def build_module(cfg, params, conv_layer, node_label_method):
                    conv_layer_encoder=conv_layer, encoder_n_attention_heads=cfg["heads"],
                    node_label_method=node_label_method, active_gp_thresh_ratio=0.01,
                    include_cat_covariates_contrastive_loss=False)
-    missing, unexpected = m.load_state_dict({k: v.float() for k, v in params.items()}, strict=True)
+    missing, unexpected = m.load_state_dict({k: (v.float() if v.is_floating_point() else v)
+                                             for k, v in params.items()}, strict=True)
     return m.to(DEV)
 
 
@@ -52,16 +56,19 @@ def make_batches(adata, edge_bs=16, node_bs=8):
     return next(iter(nl)), next(iter(ll))
 
 
+NON_PARAM = ("mask", "abs_mu", "running_mean", "running_var", "num_batches_tracked")
+
+
 def run_pair(conv_layer, node_label_method, n_addon, dtype, n_genes=40, use_only_active=False, train=True,
-             n_layers=1):
+             n_layers=1, **cfg_extra):
     adata = H.tiny_problem(n_cells=150, n_genes=n_genes, n_prior_gp=12)
     cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=n_addon, conv_layer=conv_layer,
-                                  node_label_method=node_label_method, n_layers=n_layers)
+                                  node_label_method=node_label_method, n_layers=n_layers, **cfg_extra)
     p32 = init_params(cfg, seed=3)
     if use_only_active:
         p32["running_mean_abs_mu"] = torch.rand(cfg["n_prior_gp"] + n_addon) ** 6
-    p64 = {k: v.double().clone().requires_grad_(v.is_floating_point() and not k.endswith(("mask", "abs_mu")))
-           for k, v in p32.items()}
+    p64 = {k: (v.double() if v.is_floating_point() else v).clone().requires_grad_(
+               v.is_floating_point() and not k.endswith(NON_PARAM)) for k, v in p32.items()}
     orc = VGPGAERef(cfg, p64)
     orc.training = train
     mod = build_module(cfg, p32, conv_layer, node_label_method).set_compute_dtype(dtype)
@@ -296,3 +303,65 @@ def test_two_layer_encoder(conv_layer, dtype):
         assert H.rel_err(p.grad, ref) < 3e-5, k
         checked += 1
     assert checked >= 12
+
+
+@pytest.mark.parametrize("conv_layer,n_layers,dtype", [("gatv2conv", 1, torch.float32), ("gcnconv", 1, torch.float32),
+                                                       ("gatv2conv", 2, torch.float32), ("gatv2conv", 1, torch.bfloat16)])
+def test_two_fc_layers_with_batchnorm(conv_layer, n_layers, dtype):
+    """n_fc_layers_encoder=2 (nn/encoders.py:93-96,180-182): fc_l1 -> fc_l2 -> ReLU -> BatchNorm1d in front of the
+    convs -- training pass (batch statistics, gradients of all six fc tensors, running buffers), then eval."""
+    orc, mod, (on, oe, ol), (cn, ce, cl), p64 = run_pair(conv_layer, "one-hop-norm", 4, dtype, n_layers=n_layers,
+                                                         n_fc_layers=2)
+    assert not mod.encoder.fused
+    if dtype == torch.bfloat16:
+        for k in ("global_loss", "optim_loss", "edge_recon_loss", "gene_expr_recon_loss", "kl_reg_loss"):
+            assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(ol[k])) < 5e-3, k
+        return
+    tol = 2e-5
+    for k in ("mu", "logstd", "target_rna_nb_means", "source_rna_nb_means"):
+        assert H.rel_err(cn[k], on[k]) < tol, k
+    for k in ("mu", "logstd", "edge_recon_logits"):
+        assert H.rel_err(ce[k], oe[k]) < tol, k
+    for k, v in ol.items():
+        assert H.rel_err(torch.as_tensor(cl[k]), torch.as_tensor(v)) < tol, k
+    n_fc = 0
+    for k, p in mod.named_parameters():
+        ref = p64[k].grad
+        if ref is None:
+            continue
+        assert p.grad is not None, k
+        assert H.rel_err(p.grad, ref) < 1e-4, k
+        n_fc += k.startswith(("encoder.fc_l1", "encoder.fc_l2"))
+    assert n_fc == 6
+    sd = mod.state_dict()
+    for k in ("running_mean", "running_var"):
+        assert H.rel_err(sd[f"encoder.fc_l2_bn.{k}"], p64[f"encoder.fc_l2_bn.{k}"]) < 1e-5, k
+    assert int(sd["encoder.fc_l2_bn.num_batches_tracked"]) == 2
+    # eval mode: running statistics
+    mod.eval()
+    orc.training = False
+    adata = H.tiny_problem(n_cells=150, n_genes=40, n_prior_gp=12)
+    node_b, _ = make_batches(adata)
+    with torch.no_grad():
+        mu_c = mod.get_latent_representation(node_batch=H.batch_to(node_b, torch.float32, DEV), only_active_gps=False)
+    mu_o = orc.get_latent_representation(node_b, only_active_gps=False)
+    assert H.rel_err(mu_c, mu_o) < tol
+
+
+def test_dropout_is_identity_in_eval_and_unbiased_in_training():
+    """dropout_rate_encoder / dropout_rate_graph_decoder (nn/encoders.py:179-194, nn/decoders.py:56): eval mode
+    equals the dropout-free model bit for bit; in training the dropped model's mu differs, stays finite, the
+    gradients reach fc_l1, and the mean over many draws approaches the dropout-free hidden layer's effect."""
+    orc, mod0, _, (cn0, ce0, _), _ = run_pair("gatv2conv", "one-hop-norm", 4, torch.float32, train=False)
+    orc, mod1, _, (cn1, ce1, _), _ = run_pair("gatv2conv", "one-hop-norm", 4, torch.float32, train=False,
+                                              dropout_rate_encoder=0.3, dropout_rate_graph_decoder=0.2)
+    assert not mod1.encoder.fused and mod0.encoder.fused
+    assert H.rel_err(cn1["mu"], cn0["mu"]) < 1e-6 and H.rel_err(ce1["edge_recon_logits"], ce0["edge_recon_logits"]) < 1e-6
+    torch.manual_seed(0)
+    orc, mod2, _, (cn2, ce2, cl2), _ = run_pair("gatv2conv", "one-hop-norm", 4, torch.float32, train=True,
+                                                dropout_rate_encoder=0.3, dropout_rate_graph_decoder=0.2)
+    assert torch.isfinite(cn2["mu"]).all() and torch.isfinite(cl2["optim_loss"])
+    orc, mod3, _, (cn3, _, _), _ = run_pair("gatv2conv", "one-hop-norm", 4, torch.float32, train=True)
+    assert H.rel_err(cn2["mu"], cn3["mu"]) > 1e-3                       # units were dropped
+    g = mod2.encoder.fc_l1.weight.grad
+    assert g is not None and torch.isfinite(g).all() and g.abs().sum() > 0
