@@ -37,6 +37,9 @@ CASES = {
     "gcn_sum_addon3": ("gcnconv", "one-hop-sum", 3, 40, False),
     "gatv2_attention_addon0": ("gatv2conv", "one-hop-attention", 0, 40, False),
     "gatv2_norm_active_gps": ("gatv2conv", "one-hop-norm", 3, 41, True),
+    # (+ n_fc_layers_encoder, n_layers_encoder): fc_l2 + BatchNorm1d, conv_l1
+    "gatv2_fc2_bn_two_gnn_layers": ("gatv2conv", "one-hop-norm", 3, 40, False, 2, 2),
+    "gcn_fc2_bn": ("gcnconv", "one-hop-norm", 3, 40, False, 2, 1),
 }
 
 
@@ -50,7 +53,7 @@ def batch_arrays(prefix, b, out):
         out[f"{prefix}/batch_size"] = np.int64(b.batch_size)
 
 
-def make_case(name, conv_layer, node_label_method, n_addon, n_genes, only_active):
+def make_case(name, conv_layer, node_label_method, n_addon, n_genes, only_active, n_fc=1, n_gnn=1):
     ref = load_reference()
     import torch_sparse
     torch_sparse.DEFAULT_DTYPE = torch.float64
@@ -60,7 +63,7 @@ def make_case(name, conv_layer, node_label_method, n_addon, n_genes, only_active
     torch.manual_seed(1)
     with quiet():
         m = ref.modules.VGPGAE(
-            n_input=cfg["n_input"], n_fc_layers_encoder=1, n_layers_encoder=1,
+            n_input=cfg["n_input"], n_fc_layers_encoder=n_fc, n_layers_encoder=n_gnn,
             n_hidden_encoder=cfg["n_hidden"], n_prior_gp=cfg["n_prior_gp"], n_addon_gp=n_addon,
             cat_covariates_embeds_nums=[], n_output_genes=cfg["n_output_genes"],
             target_rna_decoder_mask=cfg["target_rna_mask"], source_rna_decoder_mask=cfg["source_rna_mask"],
@@ -74,6 +77,8 @@ def make_case(name, conv_layer, node_label_method, n_addon, n_genes, only_active
         for k, p in m.named_parameters():
             if k.endswith("bias"):
                 p.uniform_(-0.1, 0.1)           # PyG zero-initialises biases: make them count
+        if n_fc == 2:
+            m.encoder.fc_l2_bn.weight.uniform_(0.8, 1.2)
         if only_active:
             m.running_mean_abs_mu.copy_(torch.rand(cfg["n_prior_gp"] + n_addon, dtype=torch.float64) ** 6)
     out = {}
@@ -84,7 +89,7 @@ def make_case(name, conv_layer, node_label_method, n_addon, n_genes, only_active
     for k, v in cfg["features_idx_dict"].items():
         out[f"cfg/features_idx/{k}"] = np.asarray(v, dtype=np.int64)
     out["cfg/meta"] = np.array([conv_layer, node_label_method, str(n_addon), str(cfg["n_hidden"]),
-                                str(cfg["heads"]), str(int(only_active))])
+                                str(cfg["heads"]), str(int(only_active)), str(n_fc), str(n_gnn)])
 
     torch.manual_seed(0)
     x = H.dense_x(adata, torch.float64)
@@ -124,6 +129,9 @@ def make_case(name, conv_layer, node_label_method, n_addon, n_genes, only_active
         if p.grad is not None:
             out[f"grad/{k}"] = p.grad.numpy().copy()
     out["after/running_mean_abs_mu"] = m.running_mean_abs_mu.numpy().copy()
+    if n_fc == 2:
+        out["after/fc_l2_bn.running_mean"] = m.encoder.fc_l2_bn.running_mean.numpy().copy()
+        out["after/fc_l2_bn.running_var"] = m.encoder.fc_l2_bn.running_var.numpy().copy()
     m.eval()
     out["after/active_gp_mask"] = m.get_active_gp_mask().numpy()
     with torch.no_grad():
@@ -254,8 +262,11 @@ def make_case_mm(name, with_atac, with_cov, conv_layer, injection):
 
 if __name__ == "__main__":
     only_mm = "--mm-only" in sys.argv
+    only = sys.argv[sys.argv.index("--only") + 1:] if "--only" in sys.argv else None     # --only NAME [NAME ...]
     if not only_mm:
         for name, args in CASES.items():
-            make_case(name, *args)
+            if only is None or name in only:
+                make_case(name, *args)
     for name, args in CASES_MM.items():
-        make_case_mm(name, *args)
+        if only is None or name in only:
+            make_case_mm(name, *args)

@@ -26,18 +26,21 @@ LAM_MM = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, l
               lambda_group_lasso=2., lambda_gene_expr_recon=300., lambda_chrom_access_recon=100.,
               lambda_edge_recon=500000., lambda_cat_covariates_contrastive=1000.,
               contrastive_logits_pos_ratio=0.25, contrastive_logits_neg_ratio=0.25)
+NON_PARAM = ("mask", "abs_mu", "running_mean", "running_var", "num_batches_tracked")
 LAM = dict(lambda_l1_masked=3., l1_targets_mask=None, l1_sources_mask=None, lambda_l1_addon=30.,
            lambda_group_lasso=2., lambda_gene_expr_recon=300., lambda_edge_recon=500000.)
 
 
 def load_case(name):
     z = np.load(os.path.join(GOLDEN_DIR, f"{name}.npz"))
-    conv_layer, method, n_addon, n_hidden, heads, only_active = [str(s) for s in z["cfg/meta"]]
+    meta = [str(s) for s in z["cfg/meta"]]
+    conv_layer, method, n_addon, n_hidden, heads, only_active = meta[:6]
+    n_fc, n_gnn = (int(meta[6]), int(meta[7])) if len(meta) > 6 else (1, 1)
     tm, sm = torch.from_numpy(z["cfg/target_rna_mask"]), torch.from_numpy(z["cfg/source_rna_mask"])
     feat = {k[len("cfg/features_idx/"):]: z[k].tolist() for k in z.files if k.startswith("cfg/features_idx/")}
     F = tm.shape[1]
     cfg = dict(n_input=F, n_output_genes=F, n_output_peaks=0, n_hidden=int(n_hidden), n_prior_gp=tm.shape[0],
-               n_addon_gp=int(n_addon), conv_layer=conv_layer, heads=int(heads), n_layers=1,
+               n_addon_gp=int(n_addon), conv_layer=conv_layer, heads=int(heads), n_layers=n_gnn, n_fc_layers=n_fc,
                node_label_method=method, log_variational=True, active_gp_thresh_ratio=0.01,
                active_gp_type="separate", include_edge_kl_loss=True, include_edge_recon_loss=True,
                include_gene_expr_recon_loss=True, include_chrom_access_recon_loss=True,
@@ -63,7 +66,7 @@ def test_golden_files_present():
 @pytest.mark.parametrize("name", CASES)
 def test_oracle_reproduces_reference_golden(name):
     z, cfg, state, node_b, edge_b, only_active = load_case(name)
-    params = {k: v.clone().requires_grad_(v.dtype.is_floating_point and not k.endswith(("mask", "abs_mu")))
+    params = {k: v.clone().requires_grad_(v.dtype.is_floating_point and not k.endswith(NON_PARAM))
               for k, v in state.items()}
     orc = VGPGAERef(cfg, params)
     on = orc.forward(node_b, "omics", use_only_active_gps=only_active, eps=torch.from_numpy(z["eps/node"]))
@@ -90,6 +93,9 @@ def test_oracle_reproduces_reference_golden(name):
             n_grads += 1
     assert n_grads >= 10
     assert H.rel_err(orc.running_mean_abs_mu, torch.from_numpy(z["after/running_mean_abs_mu"])) < 1e-12
+    for k in ("running_mean", "running_var"):
+        if f"after/fc_l2_bn.{k}" in z.files:
+            assert H.rel_err(params[f"encoder.fc_l2_bn.{k}"], torch.from_numpy(z[f"after/fc_l2_bn.{k}"])) < 1e-12, k
     orc.training = False
     assert np.array_equal(orc.get_active_gp_mask().numpy(), z["after/active_gp_mask"])
     with torch.no_grad():
@@ -132,6 +138,9 @@ def test_cuda_reproduces_reference_golden(name):
             checked += 1
     assert checked >= 8
     assert H.rel_err(mod.running_mean_abs_mu, torch.from_numpy(z["after/running_mean_abs_mu"])) < tol
+    for k in ("running_mean", "running_var"):
+        if f"after/fc_l2_bn.{k}" in z.files:
+            assert H.rel_err(getattr(mod.encoder.fc_l2_bn, k), torch.from_numpy(z[f"after/fc_l2_bn.{k}"])) < tol, k
     mod.eval()
     assert np.array_equal(mod.get_active_gp_mask().cpu().numpy(), z["after/active_gp_mask"])
     with torch.no_grad():
