@@ -258,8 +258,6 @@ def dist_setup(n_gpus: int):
     torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"        # keep NCCL's version banner off stdout: ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if world != n_gpus:
         log(f"[bench] WARNING --gpus {n_gpus} but WORLD_SIZE {world}: using WORLD_SIZE")
@@ -593,12 +591,22 @@ def run_reference(args):
     }
 
 
+def emit(res, fd):
+    """The ONE JSON line, written to the process's original stdout."""
+    os.write(fd, (json.dumps(res) + "\n").encode())
+
+
 def main():
     args = parse_args()
+    # Libraries write to fd 1 behind Python's back (NCCL prints "NCCL version ..." at NCCL_DEBUG=VERSION and
+    # =WARN): everything but the result line goes to stderr.
+    sys.stdout.flush()
+    out_fd = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         res = run_reference(args)
         if res is not None:
-            print(json.dumps(res), flush=True)
+            emit(res, out_fd)
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (nichecompass_b200 has no CPU path); "
@@ -622,7 +630,7 @@ def main():
             res["cpu_baseline"] = {"value": value, "unit": "cells/s", "cores": cores, "kind": "port",
                                    "sample": sample, "ms_per_step": sec_step * 1e3}
     if rank == 0:
-        print(json.dumps(res), flush=True)
+        emit(res, out_fd)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
