@@ -475,8 +475,9 @@ def run_ours(args):
         blk_ms_step = ms_blk / args.steps
         e2e = {"value": wl["n_cells"] / (global_steps_per_epoch * e2e_ms_step * 1e-3), "unit": "cells/s",
                "ms_per_step": e2e_ms_step, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "how": "Trainer.train_iteration via the public Trainer API; CSR count matrix in pinned host memory "
-                      "read zero-copy by the gather/SpMM kernels each step, negatives drawn on the host and copied "
+               "how": "Trainer.train_iteration via the public Trainer API; CSR count matrix in pinned host memory, "
+                      "the rows of every step pulled over the host link by the gather/SpMM kernels (those of step "
+                      "i+1 on a side stream while step i computes), negatives drawn on the host and copied "
                       "H2D, sampler sizes + global_loss copied D2H each step; the loss of step i is copied to a "
                       "pinned buffer and read on the host while step i+1 is enqueued (every step's value is read "
                       "inside the timed region, LossReader); blocking_read = the same with a blocking .item() "

@@ -95,6 +95,12 @@ int nc_spmm_csr_store(const int64_t* x_rowptr, const int32_t* x_col, const float
 int nc_csr_gather_rows(const int64_t* x_rowptr, const int32_t* x_col, const float* x_val,
                        int32_t n_cols, const int32_t* n_id, int32_t n_rows, int apply_log1p,
                        void* out, int out_dtype, int64_t ldo, void* stream);
+/* Same result as nc_csr_gather_rows from a kernel that can run BESIDE the compute stream: no shared memory,
+ * at most max_ctas CTAs (<= 0: one per two SMs) striding over the rows -- used to stage the next iteration's
+ * encoder input from a store in pinned host memory while the current iteration computes.      */
+int nc_csr_gather_rows_bg(const int64_t* x_rowptr, const int32_t* x_col, const float* x_val,
+                          int32_t n_cols, const int32_t* n_id, int32_t n_rows, int apply_log1p,
+                          void* out, int out_dtype, int64_t ldo, int32_t max_ctas, void* stream);
 int nc_dense_gather_rows(const float* x, int64_t ldx, int32_t n_cols, const int32_t* n_id,
                          int32_t n_rows, int apply_log1p, void* out, int out_dtype,
                          int64_t ldo, void* stream);

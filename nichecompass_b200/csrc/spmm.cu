@@ -403,6 +403,67 @@ extern "C" int nc_csr_gather_rows(const int64_t* x_rowptr, const int32_t* x_col,
     return NC_OK;
 }
 
+// Background variant for a side stream: no shared memory and a grid of at most `max_ctas` CTAs that stride over
+// the rows, so that the persistent GEMM CTAs of the compute stream (one per SM, ~all of its shared memory)
+// can still be scheduled next to it.  With the store in pinned host memory the loads are bound by the host
+// link; 74 CTAs x 256 threads x 4 loads keep ~600 KB in flight.  A row is zeroed, then its non-zeros are scattered.
+template <typename TO>
+__global__ void __launch_bounds__(256)
+k_csr_gather_rows_bg(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict__ x_col,
+                     const float* __restrict__ x_val, int32_t n_rows, const int32_t* __restrict__ n_id,
+                     int apply_log1p, TO* __restrict__ out, int64_t ldo) {
+    const int tid = threadIdx.x;
+    const int width = (int)ldo;
+    for (int r = blockIdx.x; r < n_rows; r += gridDim.x) {
+        const int64_t g = n_id ? (int64_t)n_id[r] : (int64_t)r;
+        const int64_t p0 = x_rowptr[g], p1 = x_rowptr[g + 1];
+        // issue the (slow) loads first, zero the row while they are in flight
+        float v[4];
+        int32_t c[4];
+        int64_t p = p0 + tid;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t q = p + (int64_t)u * 256;
+            c[u] = q < p1 ? __ldg(x_col + q) : -1;
+            v[u] = q < p1 ? __ldg(x_val + q) : 0.f;
+        }
+        TO* orow = out + (int64_t)r * ldo;
+        if ((width & 3) == 0 && ((uintptr_t)orow % (sizeof(TO) * 4) == 0)) {
+            for (int k = tid * 4; k < width; k += 256 * 4) Elem<TO>::st4(orow + k, make_float4(0.f, 0.f, 0.f, 0.f));
+        } else {
+            for (int k = tid; k < width; k += 256) Elem<TO>::st(orow + k, 0.f);
+        }
+        __syncthreads();                       // zeros of this CTA are ordered before its scattered values
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (c[u] >= 0) Elem<TO>::st(orow + c[u], apply_log1p ? logf(1.0f + v[u]) : v[u]);
+        for (p += 4 * 256; p < p1; p += 256) {
+            const float w = __ldg(x_val + p);
+            Elem<TO>::st(orow + __ldg(x_col + p), apply_log1p ? logf(1.0f + w) : w);
+        }
+    }
+}
+
+extern "C" int nc_csr_gather_rows_bg(const int64_t* x_rowptr, const int32_t* x_col, const float* x_val,
+                                     int32_t n_cols, const int32_t* n_id, int32_t n_rows, int apply_log1p,
+                                     void* out, int out_dtype, int64_t ldo, int32_t max_ctas, void* stream) {
+    NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldo >= n_cols, NC_ESHAPE,
+               "nc_csr_gather_rows_bg: bad shape n_rows=%d n_cols=%d ldo=%lld", n_rows, n_cols, (long long)ldo);
+    if (n_rows == 0) return NC_OK;
+    if (max_ctas <= 0) max_ctas = nc_num_sms() / 2;      // measured: 74 or 148 CTAs leave the step undisturbed, 296 do not
+    const int grid = n_rows < max_ctas ? n_rows : max_ctas;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (out_dtype == NC_F32)
+        k_csr_gather_rows_bg<float><<<grid, 256, 0, s>>>(x_rowptr, x_col, x_val, n_rows, n_id, apply_log1p, (float*)out, ldo);
+    else if (out_dtype == NC_BF16)
+        k_csr_gather_rows_bg<__nv_bfloat16><<<grid, 256, 0, s>>>(x_rowptr, x_col, x_val, n_rows, n_id, apply_log1p, (__nv_bfloat16*)out, ldo);
+    else
+        NC_REQUIRE(false, NC_EINVAL, "nc_csr_gather_rows_bg: unknown dtype %d", out_dtype);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_csr_gather_rows_bg");
+    return NC_OK;
+}
+
 template <typename TO>
 __global__ void __launch_bounds__(256)
 k_dense_gather_rows(const float* __restrict__ x, int64_t ldx, int32_t n_cols,

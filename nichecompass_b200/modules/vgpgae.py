@@ -346,7 +346,7 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
                 use_only_active_gps: bool = False,
                 return_agg_weights: bool = False,
                 update_atac_dynamic_decoder_mask: bool = False,
-                _latent=None) -> dict:
+                _latent=None, _labels=None) -> dict:
         """``_latent`` (internal, ``forward_joint``): (encoder output of a merged batch, first row of this
         batch's seeds in it) -- the encoder is then not run here."""
         graph, x_enc, target_rows, neighbor_rows, embed = self._prepare(data_batch, decoder, _latent is None)
@@ -414,8 +414,11 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
                         setattr(self, f"{ent}_atac_dynamic_decoder_mask", dm & active[:, None])
                 self._mask_version += 1
         Fg = self.n_output_genes_
-        x_t = target_rows(nb)
-        x_n = neighbor_rows(nb)
+        if _labels is not None:
+            x_t, x_n = _labels                                   # staged with the joint encoder input
+        else:
+            x_t = target_rows(nb)
+            x_n = neighbor_rows(nb)
         emb_b = embed[:nb] if embed is not None else None
         if "atac" in self.modalities_ and update_atac_dynamic_decoder_mask:
             self._update_atac_dynamic_masks()
@@ -452,11 +455,8 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
                 and self.encoder.n_fc_layers == 1     # BatchNorm statistics are per encoder pass in the reference
                 and not (self.n_cat_covariates_ > 0 and "encoder" in self.cat_covariates_embeds_injection_))
 
-    def forward_joint(self, node_batch, edge_batch, use_only_active_gps: bool = False):
-        """``(forward(node_batch, "omics"), forward(edge_batch, "graph"))`` with the two encoder passes merged:
-        ``nc_merge_subgraphs`` builds the block-diagonal problem [node seeds | edge seeds | others], the count
-        rows are gathered once, every encoder GEMM / attention kernel (forward and backward) runs once on
-        the union instead of once per batch."""
+    def _joint_input(self, node_batch, edge_batch, background: bool = False):
+        """Block-diagonal union of the two sampled sub-graphs + the gathered (log1p) count rows of its nodes."""
         gn, ge = node_batch.graph, edge_batch.graph
         a_seed, a_sub, b_seed, b_sub = gn.n_dst, gn.n_nodes, ge.n_dst, ge.n_nodes
         dev = gn.rowptr.device
@@ -467,9 +467,50 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
              edge_batch.n_id, b_seed, b_sub, m_rowptr, m_col, m_nid)
         gm = SubgraphCSR(m_rowptr, m_col, a_sub + b_sub, a_seed + b_seed, max(gn.max_deg, ge.max_deg))
         x_enc = ops.csr_gather_rows(node_batch.store, m_nid, a_sub + b_sub, self.log_variational_,
-                                    self.compute_dtype, pad8(self.encoder.n_input))
+                                    self.compute_dtype, pad8(self.encoder.n_input), background=background)
+        return gm, x_enc
+
+    stage_labels = True
+
+    def stage_joint_input(self, node_batch, edge_batch, stream: "torch.cuda.Stream"):
+        """Build the joint encoder input of a FUTURE iteration on ``stream`` while the compute stream runs the
+        current one.  With the count store in pinned host memory the row gather is bound by the host link
+        (~20 MB per iteration at C2); staged one iteration ahead it leaves the critical path.
+        ``forward_joint`` picks the staged input up (and waits for its event) when it is given the same pair."""
+        main = torch.cuda.current_stream()
+        stream.wait_stream(main)                  # the batches' tensors were produced / published on ``main``
+        with torch.cuda.stream(stream):
+            gm, x_enc = self._joint_input(node_batch, edge_batch, background=True)
+            labels = None
+            if self.stage_labels and self.node_label_method_ != "one-hop-attention":   # parameter-free: a pure function of the batch
+                nb = int(node_batch.batch_size)
+                labels = (ops.csr_gather_rows(node_batch.store, node_batch.n_id, nb, False, torch.float32,
+                                              background=True),
+                          self.rna_node_label_aggregator.forward_store(node_batch.store, node_batch.n_id,
+                                                                       node_batch.graph, nb))
+            ev = torch.cuda.Event()
+            ev.record(stream)
+        cached = [t for v in node_batch.graph._norm.values() for t in v if t is not None]   # gcn_weights cache
+        for t in (gm.rowptr, gm.col, x_enc) + (labels or ()) + tuple(cached):
+            t.record_stream(main)
+        edge_batch._joint_input = (node_batch, gm, x_enc, ev, labels)
+
+    def forward_joint(self, node_batch, edge_batch, use_only_active_gps: bool = False):
+        """``(forward(node_batch, "omics"), forward(edge_batch, "graph"))`` with the two encoder passes merged:
+        ``nc_merge_subgraphs`` builds the block-diagonal problem [node seeds | edge seeds | others], the count
+        rows are gathered once, every encoder GEMM / attention kernel (forward and backward) runs once on
+        the union instead of once per batch."""
+        staged = getattr(edge_batch, "_joint_input", None)
+        if staged is not None and staged[0] is node_batch:
+            _, gm, x_enc, ev, labels = staged
+            torch.cuda.current_stream().wait_event(ev)          # staged on a side stream (``stage_joint_input``)
+            edge_batch._joint_input = None
+        else:
+            gm, x_enc = self._joint_input(node_batch, edge_batch)
+            labels = None
+        a_seed = node_batch.graph.n_dst
         ml_u = self.encoder.encode(x_enc, gm)
-        node_out = self.forward(node_batch, "omics", use_only_active_gps, _latent=(ml_u, 0))
+        node_out = self.forward(node_batch, "omics", use_only_active_gps, _latent=(ml_u, 0), _labels=labels)
         edge_out = self.forward(edge_batch, "graph", use_only_active_gps, _latent=(ml_u, a_seed))
         return node_out, edge_out
 

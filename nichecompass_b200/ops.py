@@ -77,9 +77,18 @@ def spmm_csr_store(store, n_id, rowptr, col, w, wself, skip_self: bool, n_rows: 
     return out
 
 
-def csr_gather_rows(store, n_id, n_rows: int, log1p: bool, dtype: torch.dtype, ld: Optional[int] = None):
+BG_MAX_CTAS = 0         # grid bound of the side-stream gather (0: the library's default, one CTA per two SMs)
+
+
+def csr_gather_rows(store, n_id, n_rows: int, log1p: bool, dtype: torch.dtype, ld: Optional[int] = None,
+                    background: bool = False):
+    """``background``: the low-footprint kernel for a side stream (``nc_csr_gather_rows_bg``)."""
     ld = store.n_cols if ld is None else ld
     out = torch.empty(n_rows, ld, dtype=dtype, device=store.device)
+    if background:
+        call("nc_csr_gather_rows_bg", store.rowptr, store.col, store.val, store.n_cols, n_id, n_rows,
+             int(log1p), out, dtype_code(dtype), ld, BG_MAX_CTAS)
+        return out
     call("nc_csr_gather_rows", store.rowptr, store.col, store.val, store.n_cols, n_id, n_rows,
          int(log1p), out, dtype_code(dtype), ld)
     return out

@@ -132,6 +132,8 @@ class Trainer(BaseTrainerMixin):
         self.prefetch_ = kwargs.pop("prefetch", True)
         self.joint_encoder_ = kwargs.pop("joint_encoder", True)
         self.pipeline_sampler_ = kwargs.pop("pipeline_sampler", True)
+        # None: stage the next iteration's encoder input on a side stream when the count store lives in host memory
+        self.stage_inputs_ = kwargs.pop("stage_inputs", None)
         kwargs.pop("latent_dtype", None)          # forwarded by NicheCompass.train, unused here (as in the reference)
         self.epoch = -1
         self.training_time = 0
@@ -267,7 +269,30 @@ class Trainer(BaseTrainerMixin):
         """zip(edge loader, cycled node loader) with both samplers running one batch ahead."""
         e = _Prefetcher(edge_loader, self._side_streams[0])
         n = _Prefetcher(node_loader, self._side_streams[1])
-        return zip(e, _cycle_iterable(n))
+        pairs = zip(e, _cycle_iterable(n))
+        stage = self.stage_inputs_
+        if stage is None:
+            store = getattr(getattr(self, "node_masked_data", None), "store", None)
+            stage = store is not None and store.location == "host"
+        if not (stage and self.joint_encoder_ and self.prefetch_ and hasattr(self.model, "stage_joint_input")):
+            return pairs
+        return self._staged_pairs(pairs)
+
+    def _staged_pairs(self, pairs):
+        """One pair of look-ahead: the joint encoder input of iteration k + 1 (sub-graph merge + gather of the count
+        rows over the host link) is built on a third stream while iteration k computes."""
+        if len(self._side_streams) < 3:
+            self._side_streams.append(torch.cuda.Stream())
+        side = self._side_streams[2]
+        prev = None
+        for eb, nb in pairs:
+            if self.model.training and self.model.joint_supported(nb, eb):
+                self.model.stage_joint_input(nb, eb, side)
+            if prev is not None:
+                yield prev
+            prev = (eb, nb)
+        if prev is not None:
+            yield prev
 
     # ------------------------------------------------------------------ training
     def train(self,

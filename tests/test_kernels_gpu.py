@@ -81,6 +81,20 @@ def test_gather_rows(dtype):
     assert torch.equal(out2, out)
     out3 = ops.csr_gather_rows(store, None, 10, False, torch.float32)
     assert torch.equal(out3.cpu(), H.dense_x(adata)[:10])
+    # the side-stream variant (no shared memory, bounded grid) and a store in pinned host memory: same bits
+    def n_diff(a, b):
+        return int((a.float() != b.float()).sum())
+    out4 = ops.csr_gather_rows(store, n_id, n_id.numel(), True, dtype, ld, background=True)
+    assert n_diff(out4, out) == 0, "side-stream variant, device store"
+    host = CSRFeatureStore.from_scipy(adata.X, DEV, location="host")
+    torch.cuda.synchronize()
+    out5 = ops.csr_gather_rows(host, n_id, n_id.numel(), True, dtype, ld, background=True)
+    assert n_diff(out5, out) == 0, "side-stream variant, host store"
+    out5b = ops.csr_gather_rows(host, n_id, n_id.numel(), True, dtype, ld)
+    assert n_diff(out5b, out) == 0, "standard kernel, host store"
+    big = torch.arange(adata.n_obs, device=DEV, dtype=torch.int32).repeat(9)       # more rows than CTAs
+    out6 = ops.csr_gather_rows(store, big, big.numel(), True, dtype, ld, background=True)
+    assert n_diff(out6, ops.csr_gather_rows(store, big, big.numel(), True, dtype, ld)) == 0, "rows > CTAs"
 
 
 def test_reverse_csr():

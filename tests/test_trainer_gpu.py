@@ -118,7 +118,14 @@ def test_host_resident_store_gives_identical_losses():
     p32 = init_params(cfg, seed=3)
     ref, _, _ = _cpu_run(adata, cfg, p32, 2, 24)
     _, dev_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24)
-    _, host_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24, store_location="host")
+    tr_h, host_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24, store_location="host")
+    # host store: the joint encoder input of iteration k + 1 is staged on a side stream during iteration k
+    assert len(tr_h._side_streams) == 3
+    _, plain_logs = _gpu_run(adata, cfg, p32, ref.noise_log, 2, 24, store_location="host", stage_inputs=False)
+    assert plain_logs[0] == host_logs[0]
+    for a, b in zip(plain_logs, host_logs):
+        for k in a:
+            assert abs(a[k] - b[k]) <= 1e-6 * abs(b[k]), (k, a[k], b[k])
     # same kernels, same inputs: the first iteration is bit-identical; later ones may differ in the last
     # ulp because a few gradients (att / bias / scatter-add) are accumulated with float atomics
     assert dev_logs[0] == host_logs[0]
