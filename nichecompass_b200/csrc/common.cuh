@@ -41,24 +41,6 @@ static inline int nc_num_sms() {
 
 static inline int64_t nc_cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
-// Is `p` (pinned) host memory that kernels read over the host link?  L2 may hold STALE lines of system memory
-// (e.g. from an earlier use of a recycled pinned block): such operands are read with ld.global.cv, which
-// discards a matching L2 line and fetches again (nc_ld_store below).
-static inline bool nc_is_host_ptr(const void* p) {
-    cudaPointerAttributes a;
-    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
-        cudaGetLastError();
-        return false;
-    }
-    return a.type == cudaMemoryTypeHost;
-}
-#ifdef __CUDACC__
-template <typename T>
-static __device__ __forceinline__ T nc_ld_store(const T* p, bool fresh) {
-    return fresh ? __ldcv(p) : __ldg(p);
-}
-#endif
-
 // ---------------------------------------------------------------------------- element access
 // Rows are stored either as fp32 or bf16; kernels compute in fp32.
 template <typename T> struct Elem;

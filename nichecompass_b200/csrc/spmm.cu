@@ -296,7 +296,7 @@ k_spmm_csr_store(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict
                  const float* __restrict__ x_val, int32_t n_cols, const int32_t* __restrict__ n_id,
                  const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
                  const float* __restrict__ w, const float* __restrict__ wself, int skip_self,
-                 float* __restrict__ out, int64_t ldo, bool fresh) {
+                 float* __restrict__ out, int64_t ldo) {
     extern __shared__ float s_row[];
     const int i = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int c = tid; c < n_cols; c += STORE_T) s_row[c] = 0.f;
@@ -318,7 +318,7 @@ k_spmm_csr_store(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict
         const int64_t g = n_id ? (int64_t)n_id[j] : (int64_t)j;
         const int64_t p0 = x_rowptr[g], p1 = x_rowptr[g + 1];
         for (int64_t p = p0 + lane; p < p1; p += 32)
-            atomicAdd(&s_row[nc_ld_store(x_col + p, fresh)], wt * nc_ld_store(x_val + p, fresh));
+            atomicAdd(&s_row[__ldg(x_col + p)], wt * __ldg(x_val + p));
     }
     __syncthreads();
     float* orow = out + (int64_t)i * ldo;
@@ -342,7 +342,7 @@ extern "C" int nc_spmm_csr_store(const int64_t* x_rowptr, const int32_t* x_col, 
         attr_set = true;
     }
     k_spmm_csr_store<<<n_rows, STORE_T, smem, (cudaStream_t)stream>>>(
-        x_rowptr, x_col, x_val, n_cols, n_id, rowptr, col, w, wself, skip_self, out, ldo, nc_is_host_ptr(x_val));
+        x_rowptr, x_col, x_val, n_cols, n_id, rowptr, col, w, wself, skip_self, out, ldo);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_spmm_csr_store");
     return NC_OK;
@@ -353,7 +353,7 @@ template <typename TO>
 __global__ void __launch_bounds__(256)
 k_csr_gather_rows(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict__ x_col,
                   const float* __restrict__ x_val, int32_t n_cols, const int32_t* __restrict__ n_id,
-                  int apply_log1p, TO* __restrict__ out, int64_t ldo, bool fresh) {
+                  int apply_log1p, TO* __restrict__ out, int64_t ldo) {
     extern __shared__ float s_row[];
     const int r = blockIdx.x, tid = threadIdx.x;
     const int width = (int)ldo;
@@ -362,8 +362,8 @@ k_csr_gather_rows(const int64_t* __restrict__ x_rowptr, const int32_t* __restric
     const int64_t g = n_id ? (int64_t)n_id[r] : (int64_t)r;
     const int64_t p0 = x_rowptr[g], p1 = x_rowptr[g + 1];
     for (int64_t p = p0 + tid; p < p1; p += 256) {
-        float v = nc_ld_store(x_val + p, fresh);
-        s_row[nc_ld_store(x_col + p, fresh)] = apply_log1p ? logf(1.0f + v) : v;
+        float v = __ldg(x_val + p);
+        s_row[__ldg(x_col + p)] = apply_log1p ? logf(1.0f + v) : v;
     }
     __syncthreads();
     TO* orow = out + (int64_t)r * ldo;
@@ -392,11 +392,10 @@ extern "C" int nc_csr_gather_rows(const int64_t* x_rowptr, const int32_t* x_col,
         attr_set = true;
     }
     cudaStream_t s = (cudaStream_t)stream;
-    const bool fresh = nc_is_host_ptr(x_val);
     if (out_dtype == NC_F32)
-        k_csr_gather_rows<float><<<n_rows, 256, smem, s>>>(x_rowptr, x_col, x_val, n_cols, n_id, apply_log1p, (float*)out, ldo, fresh);
+        k_csr_gather_rows<float><<<n_rows, 256, smem, s>>>(x_rowptr, x_col, x_val, n_cols, n_id, apply_log1p, (float*)out, ldo);
     else if (out_dtype == NC_BF16)
-        k_csr_gather_rows<__nv_bfloat16><<<n_rows, 256, smem, s>>>(x_rowptr, x_col, x_val, n_cols, n_id, apply_log1p, (__nv_bfloat16*)out, ldo, fresh);
+        k_csr_gather_rows<__nv_bfloat16><<<n_rows, 256, smem, s>>>(x_rowptr, x_col, x_val, n_cols, n_id, apply_log1p, (__nv_bfloat16*)out, ldo);
     else
         NC_REQUIRE(false, NC_EINVAL, "nc_csr_gather_rows: unknown dtype %d", out_dtype);
     nc_count_launch(1);
@@ -412,7 +411,7 @@ template <typename TO>
 __global__ void __launch_bounds__(256)
 k_csr_gather_rows_bg(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict__ x_col,
                      const float* __restrict__ x_val, int32_t n_rows, const int32_t* __restrict__ n_id,
-                     int apply_log1p, TO* __restrict__ out, int64_t ldo, bool fresh) {
+                     int apply_log1p, TO* __restrict__ out, int64_t ldo) {
     const int tid = threadIdx.x;
     const int width = (int)ldo;
     for (int r = blockIdx.x; r < n_rows; r += gridDim.x) {
@@ -425,8 +424,8 @@ k_csr_gather_rows_bg(const int64_t* __restrict__ x_rowptr, const int32_t* __rest
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int64_t q = p + (int64_t)u * 256;
-            c[u] = q < p1 ? nc_ld_store(x_col + q, fresh) : -1;
-            v[u] = q < p1 ? nc_ld_store(x_val + q, fresh) : 0.f;
+            c[u] = q < p1 ? __ldg(x_col + q) : -1;
+            v[u] = q < p1 ? __ldg(x_val + q) : 0.f;
         }
         TO* orow = out + (int64_t)r * ldo;
         if ((width & 3) == 0 && ((uintptr_t)orow % (sizeof(TO) * 4) == 0)) {
@@ -439,8 +438,8 @@ k_csr_gather_rows_bg(const int64_t* __restrict__ x_rowptr, const int32_t* __rest
         for (int u = 0; u < 4; ++u)
             if (c[u] >= 0) Elem<TO>::st(orow + c[u], apply_log1p ? logf(1.0f + v[u]) : v[u]);
         for (p += 4 * 256; p < p1; p += 256) {
-            const float w = nc_ld_store(x_val + p, fresh);
-            Elem<TO>::st(orow + nc_ld_store(x_col + p, fresh), apply_log1p ? logf(1.0f + w) : w);
+            const float w = __ldg(x_val + p);
+            Elem<TO>::st(orow + __ldg(x_col + p), apply_log1p ? logf(1.0f + w) : w);
         }
     }
 }
@@ -454,11 +453,10 @@ extern "C" int nc_csr_gather_rows_bg(const int64_t* x_rowptr, const int32_t* x_c
     if (max_ctas <= 0) max_ctas = nc_num_sms() / 2;      // measured: 74 or 148 CTAs leave the step undisturbed, 296 do not
     const int grid = n_rows < max_ctas ? n_rows : max_ctas;
     cudaStream_t s = (cudaStream_t)stream;
-    const bool fresh = nc_is_host_ptr(x_val);
     if (out_dtype == NC_F32)
-        k_csr_gather_rows_bg<float><<<grid, 256, 0, s>>>(x_rowptr, x_col, x_val, n_rows, n_id, apply_log1p, (float*)out, ldo, fresh);
+        k_csr_gather_rows_bg<float><<<grid, 256, 0, s>>>(x_rowptr, x_col, x_val, n_rows, n_id, apply_log1p, (float*)out, ldo);
     else if (out_dtype == NC_BF16)
-        k_csr_gather_rows_bg<__nv_bfloat16><<<grid, 256, 0, s>>>(x_rowptr, x_col, x_val, n_rows, n_id, apply_log1p, (__nv_bfloat16*)out, ldo, fresh);
+        k_csr_gather_rows_bg<__nv_bfloat16><<<grid, 256, 0, s>>>(x_rowptr, x_col, x_val, n_rows, n_id, apply_log1p, (__nv_bfloat16*)out, ldo);
     else
         NC_REQUIRE(false, NC_EINVAL, "nc_csr_gather_rows_bg: unknown dtype %d", out_dtype);
     nc_count_launch(1);
