@@ -566,7 +566,7 @@ def cpu_reference(adata, wl, args, steps=None, warmup=1, budget_s=20.0, wall_s=N
     sample = (f"{steps} hot-loop steps (after {warmup} warm-up) of the same workload: edge batch "
               f"{args.edge_batch_size}, node batch {ld.node_batch_size}, {steps_per_epoch} steps/epoch; sampling + "
               f"dense row slicing + forward/backward/Adam, fp32, extrapolated to the epoch")
-    return value, sec_step, steps, cores, sample
+    return value, sec_step, (steps, warmup), cores, sample
 
 
 def run_reference(args):
@@ -577,11 +577,12 @@ def run_reference(args):
     if args.cells:
         wl["n_cells"] = args.cells
     adata = build_adata(wl, args.seed)
-    value, sec_step, steps, cores, sample = cpu_reference(adata, wl, args, steps=args.steps, warmup=max(args.warmup, 1),
-                                                          wall_s=args.ref_wall_s)
+    value, sec_step, (steps, warm), cores, sample = cpu_reference(adata, wl, args, steps=args.steps,
+                                                                  warmup=max(args.warmup, 1), wall_s=args.ref_wall_s)
     return {
         "impl": "reference", "metric": "training cells/sec per epoch", "value": value, "unit": "cells/s",
-        "n_gpus": args.gpus, "steps": steps, "steps_requested": args.steps, "warmup": max(args.warmup, 1),
+        "n_gpus": args.gpus, "steps": steps, "steps_requested": args.steps, "warmup": warm,
+        "warmup_requested": args.warmup,
         "ms_per_step": sec_step * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["name"], "n_cells": wl["n_cells"], "n_genes": wl["n_genes"], "k": wl["k"],
@@ -627,7 +628,7 @@ def main():
         else:
             del tr
             torch.cuda.empty_cache()
-            value, sec_step, steps, cores, sample = cpu_reference(adata, wl, args, steps=args.cpu_steps)
+            value, sec_step, (steps, _), cores, sample = cpu_reference(adata, wl, args, steps=args.cpu_steps)
             res["cpu_baseline"] = {"value": value, "unit": "cells/s", "cores": cores, "kind": "port",
                                    "sample": sample, "ms_per_step": sec_step * 1e3}
     if rank == 0:
