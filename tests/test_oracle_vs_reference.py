@@ -421,3 +421,20 @@ def test_two_fc_layers_with_batchnorm_match_reference(conv_layer):
         mu_r = m.get_latent_representation(node_batch=node_b, only_active_gps=False)
     mu_o = orc.get_latent_representation(node_b, only_active_gps=False)
     assert H.rel_err(mu_o, mu_r) < 1e-10
+
+
+@pytest.mark.parametrize("conv_layer", ["gatv2conv", "gcnconv"])
+@pytest.mark.parametrize("n_fc,n_gnn,n_embed,dropout", [(1, 1, 0, 0.), (2, 1, 0, 0.), (1, 2, 3, 0.), (2, 2, 3, 0.2)])
+def test_encoder_state_dict_keys_and_shapes_match_reference(conv_layer, n_fc, n_gnn, n_embed, dropout):
+    """Checkpoint compatibility of the encoder: every constructor option gives the reference's
+    state_dict keys, shapes and dtypes (nn/encoders.py:84-140).  Construction only, no compute."""
+    ref = load_reference()
+    from nichecompass_b200.nn.encoders import Encoder
+    kw = dict(n_input=40, n_cat_covariates_embed_input=n_embed, n_hidden=16, n_latent=12, n_addon_latent=4,
+              n_fc_layers=n_fc, conv_layer=conv_layer, n_layers=n_gnn, n_attention_heads=4, dropout_rate=dropout)
+    with quiet():
+        theirs = ref.nn.Encoder(**kw).state_dict()
+        ours = Encoder(**kw).state_dict()
+    assert list(ours.keys()) == list(theirs.keys())
+    for k, v in theirs.items():
+        assert ours[k].shape == v.shape and ours[k].dtype == v.dtype, k
