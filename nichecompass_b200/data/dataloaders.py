@@ -31,6 +31,13 @@ def _epoch_permutation(n: int, shuffle: bool) -> torch.Tensor:
     return torch.randperm(n, generator=g)
 
 
+def shard_batch_ids(n_batches_total: int, rank: int, world_size: int) -> List[int]:
+    """Batches of the common epoch permutation that rank ``rank`` of ``world_size`` processes: rank, rank + W,
+    ... wrapping around so that every rank yields ceil(total / W) batches (the all-reduce needs equal counts)."""
+    per_rank = math.ceil(n_batches_total / world_size)
+    return [(i * world_size + rank) % n_batches_total for i in range(per_rank)]
+
+
 class NodeLoader:
     """NeighborLoader(data, num_neighbors=[n] * hops, batch_size, directed=False, shuffle,
     input_nodes=mask)."""
@@ -75,8 +82,7 @@ class NodeLoader:
         order = _epoch_permutation(self.input_nodes.numel(), self.shuffle).to(dev)
         cats = self.data.cats_device()
         inflight, depth = deque(), (1 if self.pipeline else 0)
-        for i in range(len(self)):
-            b = (i * self.world_size + self.rank) % self.n_batches_total
+        for b in shard_batch_ids(self.n_batches_total, self.rank, self.world_size):
             batch_id = self._batch_counter + self.rank
             self._batch_counter += self.world_size
             idx = order[b * self.batch_size:(b + 1) * self.batch_size]

@@ -123,3 +123,23 @@ def test_halo_exchange_and_grad_allreduce_world2():
         assert n_own == 300
         n_halo += nh
     assert 0 < n_halo < 200          # boundary only: the tiles are spatially compact
+
+
+def test_loader_shards_cover_every_batch_with_equal_counts():
+    """Data-parallel training: rank r takes batches r, r + W, ... of the common permutation; the
+    union over the ranks covers every batch, every rank yields the same number (the gradient all-reduce is
+    collective), and the link loader's round arithmetic (negatives drawn for ALL batches on every rank so the
+    host generators stay in lock-step; dataloaders.py LinkLoader.__iter__) selects the same batches."""
+    from nichecompass_b200.data.dataloaders import shard_batch_ids
+    import math
+    for total in (1, 2, 7, 16, 125, 16218):
+        for world in (1, 2, 3, 4, 8):
+            shards = [shard_batch_ids(total, r, world) for r in range(world)]
+            per = math.ceil(total / world)
+            assert all(len(s) == per for s in shards)
+            assert set(b for s in shards for b in s) == set(range(total))
+            if total % world == 0:
+                assert sorted(b for s in shards for b in s) == list(range(total))       # no batch twice
+            for r in range(world):                                                        # link-loader rounds
+                mine = [q % total for q in range(per * world) if q % world == r]
+                assert mine == shards[r]
