@@ -146,33 +146,47 @@ int nc_masked_sddmm(const float* dlT, int64_t lddl, const float* zT, int64_t ldz
  * CSR row among the n_dst targets.
  * alpha [(rowptr[n_dst] + n_dst) * n_conv * H]: attention coefficient of "slot" s (entry e of
  * row i -> s = e + i, appended self edge -> s = rowptr[i+1] + i), saved for the backward.
- * out [n_dst, ldo] fp32, conv c written at columns [out_off_c, out_off_c + C_c).           */
+ * out [n_dst, ldo] fp32, conv c written at columns [out_off_c, out_off_c + C_c).
+ * head_ws (nullable): fp32 [n_dst, ld] workspace.  When it is given, the rows are bf16 and every
+ * C_c / off_c / out_off_c is a multiple of 4 (n_conv * H <= 16 segments of <= 1536 columns), the
+ * ring kernels of csrc/gatv2_ring.cu run: persistent CTAs that stream whole x_l rows through a
+ * shared-memory ring (cp.async.bulk + mbarrier), one warp per (conv, head) segment.  head_ws then
+ * receives the per-head outputs sum_j alpha_ijh x_l[j, h, :] (before the head mean) and must be
+ * handed to nc_gatv2_bwd unchanged.  Otherwise the generic kernels run and head_ws is untouched. */
 int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
                  const float* bias, const int32_t* rowptr, const int32_t* col, int32_t n_dst,
                  const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
                  int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
-                 void* stream);
+                 float* head_ws, void* stream);
 /* Forward only, over a TILE of targets of a large resident graph (full-graph latent inference,
  * models/nichecompass.py:1264-1381 / modules/vgpgae.py:1368-1437 without the loader's per-batch
  * recomputation): targets are rows [dst_off, dst_off + n_dst) of rowptr and -- for the self edge --
  * of xl; xr [n_dst, ld] and out [n_dst, ldo] hold the tile only.  col indexes xl rows.  No
- * attention coefficients are stored.                                                          */
+ * attention coefficients are stored.  head_ws: as in nc_gatv2_fwd (scratch of the tile).      */
 int nc_gatv2_fwd_tile(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
                       const float* bias, const int32_t* rowptr, const int32_t* col, int32_t dst_off,
                       int32_t n_dst, const int32_t* seg, const int32_t* seg_host, int32_t n_conv,
                       int32_t H, int32_t max_deg, float neg_slope, float* out, int64_t ldo,
-                      void* stream);
+                      float* head_ws, void* stream);
 /* Backward of nc_gatv2_fwd.  rptr/rdst/rslot: nc_reverse_csr(..., add_self=1) of the same graph.
  * dxl [n_src, ld] and dxr [n_dst, ld] (same dtype as xl) are fully overwritten; datt (indexed
  * like att) and dbias (indexed like out columns, may be NULL) are ACCUMULATED with atomics.
- * ds_ws: fp32 workspace of the size of alpha.                                               */
+ * ds_ws: fp32 workspace of the size of alpha.
+ * head_ws: what nc_gatv2_fwd wrote (NULL: generic kernels).  bwd_ws / bwd_ws_bytes: scratch of
+ * nc_gatv2_bwd_ws_bytes(n_slots, n_dst, n_conv, H) bytes, 256-byte aligned (LeakyReLU sign bits of
+ * every (edge, element) + per-target softmax-backward constants); n_slots >= rowptr[n_dst] + n_dst.
+ * With both given (and the shape conditions of nc_gatv2_fwd) the ring kernels run: one streaming
+ * pass per target (d score, d x_r, d att, sign bits) and one pass per source that reads the sign
+ * bits instead of x_l[j] + x_r[i].                                                            */
 int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
                  const int32_t* rowptr, const int32_t* col, int32_t n_dst, int32_t n_src,
                  const int32_t* rptr, const int32_t* rdst, const int32_t* rslot,
                  const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
                  int32_t max_deg, float neg_slope, const float* dout, int64_t ldo,
                  const float* alpha, float* ds_ws, void* dxl, void* dxr, float* datt,
-                 float* dbias, void* stream);
+                 float* dbias, const float* head_ws, void* bwd_ws, int64_t bwd_ws_bytes,
+                 int64_t n_slots, void* stream);
+int64_t nc_gatv2_bwd_ws_bytes(int64_t n_slots, int64_t n_dst, int32_t n_conv, int32_t H);
 
 /* ------------------------------------------------------------------------------------------
  * Attention node-label aggregator (nn/aggregators.py:113-156).

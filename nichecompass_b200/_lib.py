@@ -48,8 +48,9 @@ def _parse_header(path: str) -> dict:
     return out
 
 
-SIGNATURES = {k: v for k, v in _parse_header(HEADER_PATH).items()
-              if k not in ("nc_last_error", "nc_version", "nc_launch_count")}
+# entry points that return a value instead of a status code (bound separately in ``_load``)
+VALUE_FUNCS = ("nc_last_error", "nc_version", "nc_launch_count", "nc_gatv2_bwd_ws_bytes")
+SIGNATURES = {k: v for k, v in _parse_header(HEADER_PATH).items() if k not in VALUE_FUNCS}
 
 _lib = None
 
@@ -75,6 +76,8 @@ def _load():
     lib.nc_last_error.restype = ctypes.c_char_p
     lib.nc_version.restype = ctypes.c_int
     lib.nc_launch_count.restype = ctypes.c_int64
+    lib.nc_gatv2_bwd_ws_bytes.restype = ctypes.c_int64
+    lib.nc_gatv2_bwd_ws_bytes.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32]
     for name, sig in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype = ctypes.c_int

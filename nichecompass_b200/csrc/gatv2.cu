@@ -11,6 +11,18 @@
 #include "common.cuh"
 
 extern void nc_count_launch(int n);
+// gatv2_ring.cu: the hot-path (bf16, vectorisable) kernels; return 1 when the shape is not theirs
+int gat_ring_fwd(const void* xl, const void* xr, int64_t ld, const float* att, const float* bias,
+                 const int32_t* rowptr, const int32_t* col, int32_t dst_off, int32_t n_dst, const int32_t* seg,
+                 const int32_t* seg_host, int32_t n_conv, int32_t H, int32_t max_deg, float slope, float* out,
+                 int64_t ldo, float* alpha, float* head_ws, void* stream);
+int64_t gat_ring_bwd_ws_bytes(int64_t n_slots, int64_t n_dst, int n_conv, int H);
+int gat_ring_bwd(const void* xl, const void* xr, int64_t ld, const float* att, const int32_t* rowptr,
+                 const int32_t* col, int32_t n_dst, int32_t n_src, const int32_t* rptr, const int32_t* rdst,
+                 const int32_t* rslot, const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
+                 int32_t max_deg, float slope, const float* dout, int64_t ldo, const float* alpha, float* ds_ws,
+                 void* dxl, void* dxr, float* datt, float* dbias, const float* head_ws, void* bwd_ws,
+                 int64_t n_slots, void* stream);
 
 namespace {
 constexpr int GT = 128;
@@ -648,10 +660,15 @@ static int gatv2_fwd_impl(const void* xl, const void* xr, int dtype, int64_t ld,
                           const float* bias, const int32_t* rowptr, const int32_t* col, int32_t dst_off, int32_t n_dst,
                           const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
                           int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
-                          void* stream) {
+                          float* head_ws, void* stream) {
     NC_REQUIRE(n_dst >= 0 && n_conv > 0 && H > 0 && max_deg >= 0, NC_ESHAPE, "nc_gatv2_fwd: bad sizes");
     NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_gatv2_fwd: bad dtype %d", dtype);
     if (n_dst == 0) return NC_OK;
+    if (dtype == NC_BF16 && head_ws != nullptr && out != nullptr) {
+        const int rc = gat_ring_fwd(xl, xr, ld, att, bias, rowptr, col, dst_off, n_dst, seg, seg_host, n_conv, H,
+                                    max_deg, neg_slope, out, ldo, alpha, head_ws, stream);
+        if (rc <= 0) return rc;
+    }
     const size_t smem = ((size_t)H * (max_deg + 1) + (max_deg + 1)) * 4;
     NC_REQUIRE(smem <= 48 * 1024, NC_EUNSUPPORTED, "nc_gatv2_fwd: max_deg=%d too large", max_deg);
     cudaStream_t s = (cudaStream_t)stream;
@@ -697,10 +714,10 @@ extern "C" int nc_gatv2_fwd(const void* xl, const void* xr, int dtype, int64_t l
                             const float* bias, const int32_t* rowptr, const int32_t* col, int32_t n_dst,
                             const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
                             int32_t max_deg, float neg_slope, float* out, int64_t ldo, float* alpha,
-                            void* stream) {
+                            float* head_ws, void* stream) {
     NC_REQUIRE(alpha != nullptr, NC_EINVAL, "nc_gatv2_fwd: alpha must be given (the backward consumes it)");
     return gatv2_fwd_impl(xl, xr, dtype, ld, att, bias, rowptr, col, 0, n_dst, seg, seg_host, n_conv, H, max_deg,
-                          neg_slope, out, ldo, alpha, stream);
+                          neg_slope, out, ldo, alpha, head_ws, stream);
 }
 
 // Inference over a tile of targets of a large resident graph: targets are rows
@@ -710,10 +727,10 @@ extern "C" int nc_gatv2_fwd_tile(const void* xl, const void* xr, int dtype, int6
                                  const float* bias, const int32_t* rowptr, const int32_t* col, int32_t dst_off,
                                  int32_t n_dst, const int32_t* seg, const int32_t* seg_host, int32_t n_conv,
                                  int32_t H, int32_t max_deg, float neg_slope, float* out, int64_t ldo,
-                                 void* stream) {
+                                 float* head_ws, void* stream) {
     NC_REQUIRE(dst_off >= 0 && out != nullptr, NC_EINVAL, "nc_gatv2_fwd_tile: bad dst_off / out");
     return gatv2_fwd_impl(xl, xr, dtype, ld, att, bias, rowptr, col, dst_off, n_dst, seg, seg_host, n_conv, H,
-                          max_deg, neg_slope, out, ldo, nullptr, stream);
+                          max_deg, neg_slope, out, ldo, nullptr, head_ws, stream);
 }
 
 extern "C" int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
@@ -722,10 +739,18 @@ extern "C" int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t l
                             const int32_t* seg, const int32_t* seg_host, int32_t n_conv, int32_t H,
                             int32_t max_deg, float neg_slope, const float* dout, int64_t ldo,
                             const float* alpha, float* ds_ws, void* dxl, void* dxr, float* datt,
-                            float* dbias, void* stream) {
+                            float* dbias, const float* head_ws, void* bwd_ws, int64_t bwd_ws_bytes,
+                            int64_t n_slots, void* stream) {
     NC_REQUIRE(n_dst >= 0 && n_src >= n_dst && n_conv > 0 && H > 0, NC_ESHAPE, "nc_gatv2_bwd: bad sizes");
     NC_REQUIRE(dtype == NC_F32 || dtype == NC_BF16, NC_EINVAL, "nc_gatv2_bwd: bad dtype %d", dtype);
     if (n_src == 0) return NC_OK;
+    if (dtype == NC_BF16 && head_ws != nullptr && bwd_ws != nullptr && n_dst > 0 && dout != nullptr &&
+        bwd_ws_bytes >= gat_ring_bwd_ws_bytes(n_slots, n_dst, n_conv, H)) {
+        const int rc = gat_ring_bwd(xl, xr, ld, att, rowptr, col, n_dst, n_src, rptr, rdst, rslot, seg, seg_host,
+                                    n_conv, H, max_deg, neg_slope, dout, ldo, alpha, ds_ws, dxl, dxr, datt, dbias,
+                                    head_ws, bwd_ws, n_slots, stream);
+        if (rc <= 0) return rc;
+    }
     const size_t smem = ((size_t)2 * H * (max_deg + 1) + (max_deg + 1)) * 4;
     NC_REQUIRE(smem <= 48 * 1024, NC_EUNSUPPORTED, "nc_gatv2_bwd: max_deg=%d too large", max_deg);
     cudaStream_t s = (cudaStream_t)stream;
@@ -826,6 +851,10 @@ k_agg_dalpha(const float* __restrict__ dout, int64_t ldo, const float* __restric
     if (threadIdx.x < H) dalpha[(int64_t)(rowptr[i + 1] + i) * H + threadIdx.x] = 0.f;   // unused self slot
 }
 }  // namespace
+
+extern "C" int64_t nc_gatv2_bwd_ws_bytes(int64_t n_slots, int64_t n_dst, int32_t n_conv, int32_t H) {
+    return gat_ring_bwd_ws_bytes(n_slots, n_dst, n_conv, H);
+}
 
 extern "C" int nc_attn_agg_fwd(const void* gl, const void* gr, int dtype, int64_t ld, const float* attn,
                                const int32_t* rowptr, const int32_t* col, int32_t n_dst, const int32_t* seg,

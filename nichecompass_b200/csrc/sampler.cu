@@ -18,7 +18,7 @@ extern void nc_count_launch(int n);
 
 namespace {
 constexpr int ST = 256;
-enum { C_NSUB = 0, C_ESUB = 1, C_OVERFLOW = 2, C_MAXROW = 3, C_FBEGIN = 4, C_FEND = 5, C_NCAND = 6, C_FLEN = 7, C_NCOUNTS = 8 };
+enum { C_NSUB = 0, C_ESUB = 1, C_OVERFLOW = 2, C_MAXROW = 3, C_FBEGIN = 4, C_EDST = 4 /* after the hops */, C_FEND = 5, C_NCAND = 6, C_FLEN = 7, C_NCOUNTS = 8 };
 
 __device__ __forceinline__ uint64_t mix64(uint64_t x) {
     x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ULL;
@@ -184,7 +184,7 @@ __global__ void k_row_count(const int32_t* __restrict__ g_rowptr, const int32_t*
 __global__ void k_row_fill(const int32_t* __restrict__ g_rowptr, const int32_t* __restrict__ g_col,
                            const int32_t* __restrict__ n_id, int32_t* __restrict__ counts,
                            const int32_t* __restrict__ slot, const int32_t* __restrict__ rowptr,
-                           int32_t* __restrict__ col, int cap_edges) {
+                           int32_t* __restrict__ col, int cap_edges, int n_seed) {
     const int n = counts[C_NSUB];
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
         const int v = n_id[t];
@@ -198,7 +198,10 @@ __global__ void k_row_fill(const int32_t* __restrict__ g_rowptr, const int32_t* 
             }
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) counts[C_ESUB] = rowptr[n];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        counts[C_ESUB] = rowptr[n];
+        counts[C_EDST] = rowptr[min(n_seed, n)];         // entries of the seed rows: the only rows a 1-layer encoder reads
+    }
 }
 
 __global__ void k_reset(const int32_t* __restrict__ n_id, const int32_t* __restrict__ counts, int32_t* __restrict__ slot) {
@@ -345,7 +348,7 @@ extern "C" int nc_sample_subgraph(const int32_t* g_rowptr, const int32_t* g_col,
     }
     k_row_count<<<gn, ST, 0, s>>>(g_rowptr, g_col, n_id, counts, slot_ws, deg);
     k_scan_dev_n<<<1, 1024, 0, s>>>(deg, rowptr, counts + C_NSUB, 0, cap_nodes);
-    k_row_fill<<<gn, ST, 0, s>>>(g_rowptr, g_col, n_id, counts, slot_ws, rowptr, col, cap_edges);
+    k_row_fill<<<gn, ST, 0, s>>>(g_rowptr, g_col, n_id, counts, slot_ws, rowptr, col, cap_edges, n_seed);
     k_reset<<<gn, ST, 0, s>>>(n_id, counts, slot_ws);
     nc_count_launch(launches + 4);
     NC_CHECK_LAUNCH("nc_sample_subgraph");

@@ -185,5 +185,5 @@ def sample_subgraph_finish(h):
     if overflow:
         raise RuntimeError("nc_sample_subgraph: capacity overflow (graph degree bound violated)")
     graph = SubgraphCSR(rowptr[:n_sub + 1], col[:max(e_sub, 1)][:e_sub] if e_sub > 0 else col[:0], n_sub,
-                        n_seed, max_row)
+                        n_seed, max_row, e_dst=int(c[4]))
     return n_id[:n_sub], graph

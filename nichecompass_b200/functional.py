@@ -20,9 +20,13 @@ class SubgraphCSR:
     """Induced subgraph in dst-CSR form (int32, device).  ``n_dst``: the leading rows whose
     outputs are consumed (the seeds); ``max_deg``: upper bound of their row lengths."""
 
-    def __init__(self, rowptr, col, n_nodes: int, n_dst: Optional[int] = None, max_deg: Optional[int] = None):
+    def __init__(self, rowptr, col, n_nodes: int, n_dst: Optional[int] = None, max_deg: Optional[int] = None,
+                 e_dst: Optional[int] = None):
+        """``e_dst``: rowptr[n_dst] when the caller knows it on the host (the sampler reads it back with the
+        sizes); bounds the attention slots by the LIVE entries instead of ``col.numel()``."""
         self.rowptr, self.col, self.n_nodes = rowptr, col, int(n_nodes)
         self.n_dst = self.n_nodes if n_dst is None else int(n_dst)
+        self.e_dst = col.numel() if e_dst is None else min(int(e_dst), col.numel())
         if max_deg is None:
             max_deg = int((rowptr[1:] - rowptr[:-1]).max().item()) if self.n_nodes > 0 else 0
         self.max_deg = int(max_deg)
@@ -36,8 +40,9 @@ class SubgraphCSR:
 
     @property
     def n_slots(self) -> int:
-        """Upper bound of the attention slots of the first n_dst rows (entries + self edges)."""
-        return self.col.numel() + self.n_dst
+        """Attention slots of the first n_dst rows (entries + self edges; an upper bound when ``e_dst`` is not
+        known)."""
+        return self.e_dst + self.n_dst
 
     def reverse(self):
         if self._rev is None:
@@ -255,9 +260,11 @@ class EncoderGATv2Fn(torch.autograd.Function):
         ops.gemm(Hbuf, Wr, bias=br, out=XR[:, :NL], M=n_dst, N=NL, K=Hd)
         out = torch.empty(n_dst, out_width, dtype=torch.float32, device=dev)
         alpha = torch.empty(max(graph.n_slots, 1) * NC * heads, dtype=torch.float32, device=dev)
+        # per-head outputs of the ring kernels (csrc/gatv2_ring.cu); untouched on the generic path
+        head_ws = torch.empty(max(n_dst, 1), ldl, dtype=torch.float32, device=dev) if act == torch.bfloat16 else None
         call("nc_gatv2_fwd", XL, XR, dtype_code(act), ldl, att, bias_out, graph.rowptr, graph.col, n_dst,
-             seg, HostPtr(seg_host), NC, heads, graph.max_deg, 0.2, out, out.stride(0), alpha)
-        ctx.save_for_backward(None if pre else x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr)
+             seg, HostPtr(seg_host), NC, heads, graph.max_deg, 0.2, out, out.stride(0), alpha, head_ws)
+        ctx.save_for_backward(None if pre else x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr, head_ws)
         ctx.meta = (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
                     [tuple(t.shape) for t in tensors], None if pre else tuple(W1.shape), act)
         ctx.params = (None if pre else W1, b1, conv, tight)          # arena residents receive their gradients in place
@@ -265,7 +272,7 @@ class EncoderGATv2Fn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dout):
-        x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr = ctx.saved_tensors
+        x_enc, Hbuf, XL, XR, alpha, att, seg, W1p, Wl, Wr, head_ws = ctx.saved_tensors
         (graph, n_feat, heads, out_offsets, out_width, NC, Cs, widths, offs, NL, ldl, Hd, seg_host,
          shapes, w1_shape, act) = ctx.meta
         pre = W1p is None
@@ -292,9 +299,13 @@ class EncoderGATv2Fn(torch.autograd.Function):
         datt = g_att if g_att is not None else torch.zeros(ldl, dtype=torch.float32, device=dev)
         dbias = g_bias if g_bias is not None else torch.zeros(out_width, dtype=torch.float32, device=dev)
         ds = torch.empty_like(alpha)
+        bwd_ws, ws_bytes = None, 0
+        if head_ws is not None:
+            ws_bytes = ops.gatv2_bwd_ws_bytes(graph.n_slots, n_dst, NC, heads)
+            bwd_ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         call("nc_gatv2_bwd", XL, XR, dtype_code(act), ldl, att, graph.rowptr, graph.col, n_dst, n_sub,
              rptr, rdst, rslot, seg, HostPtr(seg_host), NC, heads, graph.max_deg, 0.2, dout, dout.stride(0), alpha, ds,
-             dXL, dXR, datt, dbias)
+             dXL, dXR, datt, dbias, head_ws, bwd_ws, ws_bytes, graph.n_slots)
         # weight gradients of lin_l / lin_r (all convs in one GEMM each), bias gradients
         if g_Wl is not None:
             ops.gemm(dXL, Hbuf, trans_a=True, trans_b=True, out=g_Wl.view(NL, Hd), accumulate=True, M=NL, N=Hd, K=n_sub)

@@ -225,10 +225,12 @@ def encode_partition(module, store, lg: LocalGraph, own_old: torch.Tensor, bound
     XR = torch.empty(min(tile_rows, max(n_own, 1)), ldl, dtype=act, device=dev)
     if ldl != NL:
         XR[:, NL:].zero_()
+    # per-head outputs of the ring attention kernels (csrc/gatv2_ring.cu), scratch of one tile
+    head_ws = torch.empty(XR.size(0), ldl, dtype=torch.float32, device=dev) if act == torch.bfloat16 else None
     for t0 in range(0, n_own, tile_rows):
         t1 = min(n_own, t0 + tile_rows)
         ops.gemm(Hall[t0:t1], Wr, bias=br, out=XR[:t1 - t0, :NL], M=t1 - t0, N=NL, K=Hd)
         o = out[t0:t1]
         call("nc_gatv2_fwd_tile", XL, XR, dtype_code(act), ldl, att, bias_out, lg.rowptr, lg.col, t0, t1 - t0,
-             seg, HostPtr(seg_host), len(convs), heads, lg.max_deg, 0.2, o, o.stride(0))
+             seg, HostPtr(seg_host), len(convs), heads, lg.max_deg, 0.2, o, o.stride(0), head_ws)
     return out

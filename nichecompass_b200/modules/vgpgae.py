@@ -461,11 +461,12 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
         a_seed, a_sub, b_seed, b_sub = gn.n_dst, gn.n_nodes, ge.n_dst, ge.n_nodes
         dev = gn.rowptr.device
         m_rowptr = torch.empty(a_seed + b_seed + 1, dtype=torch.int32, device=dev)
-        m_col = torch.empty(max(gn.col.numel() + ge.col.numel(), 1), dtype=torch.int32, device=dev)
+        m_col = torch.empty(max(gn.e_dst + ge.e_dst, 1), dtype=torch.int32, device=dev)     # seed rows only
         m_nid = torch.empty(a_sub + b_sub, dtype=torch.int32, device=dev)
         call("nc_merge_subgraphs", gn.rowptr, gn.col, node_batch.n_id, a_seed, a_sub, ge.rowptr, ge.col,
              edge_batch.n_id, b_seed, b_sub, m_rowptr, m_col, m_nid)
-        gm = SubgraphCSR(m_rowptr, m_col, a_sub + b_sub, a_seed + b_seed, max(gn.max_deg, ge.max_deg))
+        gm = SubgraphCSR(m_rowptr, m_col, a_sub + b_sub, a_seed + b_seed, max(gn.max_deg, ge.max_deg),
+                         e_dst=gn.e_dst + ge.e_dst)
         x_enc = ops.csr_gather_rows(node_batch.store, m_nid, a_sub + b_sub, self.log_variational_,
                                     self.compute_dtype, pad8(self.encoder.n_input), background=background)
         return gm, x_enc

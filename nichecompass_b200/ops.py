@@ -57,6 +57,11 @@ def reverse_csr(rowptr, col, n_nodes: int, n_rows: int, add_self: bool, n_entrie
     return rptr, rdst, rslot
 
 
+def gatv2_bwd_ws_bytes(n_slots: int, n_dst: int, n_conv: int, heads: int) -> int:
+    """Scratch of ``nc_gatv2_bwd``'s ring kernels (sign bits per (edge, element) + per-target constants)."""
+    return int(_lib.lib().nc_gatv2_bwd_ws_bytes(int(n_slots), int(n_dst), int(n_conv), int(heads)))
+
+
 # --------------------------------------------------------------------------- SpMM / gathers
 def spmm_csr(x: torch.Tensor, rowptr, col, w, wself, skip_self: bool, n_rows: int,
              out_dtype: torch.dtype = torch.float32, out: Optional[torch.Tensor] = None,

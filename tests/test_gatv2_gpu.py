@@ -55,11 +55,19 @@ def torch_reference(xl, xr, att, bias, rowptr, col, n_dst, Cs, offs, out_offs, H
     return out
 
 
-@pytest.mark.parametrize("dtype,Cs", [(torch.bfloat16, [1500, 100, 1500, 100]), (torch.bfloat16, [24, 8]),
-                                      (torch.float32, [60, 12])])
-def test_gatv2_fwd_bwd_vs_torch(dtype, Cs):
+@pytest.mark.parametrize("dtype,Cs,ring,n_dst,max_deg", [
+    (torch.bfloat16, [1500, 100, 1500, 100], True, 120, 14),      # C2 widths: ring kernels <12, 1>
+    (torch.bfloat16, [1500, 100, 1500, 100], True, 333, 40),      # more targets than SMs, rows longer than a warp chunk
+    (torch.bfloat16, [1500, 100, 1500, 100], False, 120, 14),     # same shape on the generic / streaming kernels
+    (torch.bfloat16, [300, 100, 300, 100], True, 200, 9),         # C1 widths: <4, 1>
+    (torch.bfloat16, [1500, 1500], True, 64, 14),                 # no add-on programs: <12, 0>
+    (torch.bfloat16, [256, 256, 256, 256], True, 64, 5),          # equal segments: <4, 4>
+    (torch.bfloat16, [24, 8], True, 120, 14),
+    (torch.bfloat16, [24, 8], False, 120, 14),
+    (torch.float32, [60, 12], False, 120, 14)])
+def test_gatv2_fwd_bwd_vs_torch(dtype, Cs, ring, n_dst, max_deg):
     g = torch.Generator().manual_seed(0)
-    Hh, n_src, n_dst, max_deg = 4, 300, 120, 14
+    Hh, n_src = 4, max(300, n_dst)
     NC = len(Cs)
     widths = [Hh * C for C in Cs]
     offs = [sum(widths[:c]) for c in range(NC)]
@@ -77,8 +85,11 @@ def test_gatv2_fwd_bwd_vs_torch(dtype, Cs):
     n_slots = col.numel() + n_dst
     out = torch.empty(n_dst, out_w, device=DEV)
     alpha = torch.full((n_slots * NC * Hh,), 7.0, device=DEV)
+    head_ws = torch.full((n_dst, ldl), float("nan"), device=DEV) if ring else None
     call("nc_gatv2_fwd", xl, xr, dtype_code(dtype), ldl, att, bias, rowptr, col, n_dst, seg, HostPtr(seg_host), NC, Hh,
-         deg, 0.2, out, out.stride(0), alpha)
+         deg, 0.2, out, out.stride(0), alpha, head_ws)
+    if ring:        # the ring kernels ran (not the generic fallback): they filled the per-head outputs
+        assert bool(torch.isfinite(head_ws[:, :NL]).all())
     xl32 = xl.float().requires_grad_(True)
     xr32 = xr.float().requires_grad_(True)
     att32 = att.clone().requires_grad_(True)
@@ -99,8 +110,11 @@ def test_gatv2_fwd_bwd_vs_torch(dtype, Cs):
     datt = torch.zeros(ldl, device=DEV)
     dbias = torch.zeros(out_w, device=DEV)
     ds = torch.empty_like(alpha)
+    ws_bytes = ops.gatv2_bwd_ws_bytes(n_slots, n_dst, NC, Hh) if ring else 0
+    bwd_ws = torch.empty(ws_bytes, dtype=torch.uint8, device=DEV) if ring else None
     call("nc_gatv2_bwd", xl, xr, dtype_code(dtype), ldl, att, rowptr, col, n_dst, n_src, rptr, rdst, rslot, seg,
-         HostPtr(seg_host), NC, Hh, deg, 0.2, dout, dout.stride(0), alpha, ds, dxl, dxr, datt, dbias)
+         HostPtr(seg_host), NC, Hh, deg, 0.2, dout, dout.stride(0), alpha, ds, dxl, dxr, datt, dbias, head_ws, bwd_ws,
+         ws_bytes, n_slots)
     tol = 1e-2 if dtype == torch.bfloat16 else 2e-4
     assert H.rel_err(dxl[:, :NL].float(), xl32.grad[:, :NL]) < tol
     assert H.rel_err(dxr[:, :NL].float(), xr32.grad[:, :NL]) < tol
