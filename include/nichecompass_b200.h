@@ -41,6 +41,13 @@ int nc_version(void);
 /* number of kernels launched by this library in this process so far (bench.py gpu_launches) */
 int64_t nc_launch_count(void);
 
+/* Page-locked, device-mapped host memory for a count store that stays in host memory
+ * (data/store.py, location="host"; the reference keeps the dense count tensor in pageable host memory and
+ * slices it on the CPU, data/datasets.py:59-71).  The block is owned by the caller until nc_host_free, which
+ * waits for the device before unmapping; blocks are never recycled through a caching allocator.           */
+int nc_host_alloc(int64_t bytes, void** out_host);
+int nc_host_free(void* host);
+
 /* ------------------------------------------------------------------------------------------
  * Graph helpers on a dst-CSR (replaces torch_sparse SparseStorage sort / fill_diag / sum and
  * PyG add_remaining_self_loops + degree scatter: nn/aggregators.py:205-209, PyG gcn_norm)

@@ -9,6 +9,8 @@
 
 // ---------------------------------------------------------------------------- errors
 void nc_set_error(const char* fmt, ...);   // capi.cu
+// once per (kernel, device), result checked; `done_per_device`: bool[64] private to ONE kernel (capi.cu)
+int nc_set_max_smem(const void* func, int bytes, bool* done_per_device, const char* name);
 
 #define NC_REQUIRE(cond, code, ...)                \
     do {                                           \

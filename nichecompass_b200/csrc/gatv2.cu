@@ -685,11 +685,8 @@ static int gatv2_fwd_impl(const void* xl, const void* xr, int dtype, int64_t ld,
         if (nv <= 8 && sm <= 100 * 1024) {
 #define LS(NV)                                                                                                       \
     do {                                                                                                             \
-        static bool attr_set = false;                                                                                \
-        if (!attr_set) {                                                                                             \
-            cudaFuncSetAttribute(k_gatv2_fwd_stream<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);   \
-            attr_set = true;                                                                                         \
-        }                                                                                                            \
+        static bool attr_set[64] = {false};   /* one flag array per NV: the macro body is expanded per case */ \
+        if (int rc_ = nc_set_max_smem((const void*)k_gatv2_fwd_stream<NV>, 100 * 1024, attr_set, "k_gatv2_fwd_stream")) return rc_; \
         k_gatv2_fwd_stream<NV><<<grid, FS_NT, sm, s>>>((const __nv_bfloat16*)xl, (const __nv_bfloat16*)xr, ld, att, \
                                                        bias, rowptr, col, seg, n_conv, H, max_deg, seg_stride,       \
                                                        neg_slope, out, ldo, alpha, dst_off);                         \
@@ -775,11 +772,8 @@ extern "C" int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t l
             dim3 grid((unsigned)nc_cdiv(n_dst, TCH), (unsigned)(n_conv * (H / HG)));
 #define LBS(NV)                                                                                                      \
     do {                                                                                                             \
-        static bool attr_set = false;                                                                                \
-        if (!attr_set) {                                                                                             \
-            cudaFuncSetAttribute(k_gatv2_bwd_dst_stream<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024); \
-            attr_set = true;                                                                                         \
-        }                                                                                                            \
+        static bool attr_set[64] = {false};   /* one flag array per NV: the macro body is expanded per case */ \
+        if (int rc_ = nc_set_max_smem((const void*)k_gatv2_bwd_dst_stream<NV>, 100 * 1024, attr_set, "k_gatv2_bwd_dst_stream")) return rc_; \
         k_gatv2_bwd_dst_stream<NV><<<grid, BS_NT, sm, s>>>((const __nv_bfloat16*)xl, (const __nv_bfloat16*)xr, ld,  \
             att, rowptr, col, seg, n_conv, H, HG, TCH, n_dst, max_deg, seg_stride, neg_slope, dout, ldo, alpha,      \
             ds_ws, (__nv_bfloat16*)dxr, datt);                                                                       \

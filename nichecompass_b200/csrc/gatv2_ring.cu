@@ -643,9 +643,11 @@ bool ring_plan(const int32_t* seg_host, int n_conv, int H, int64_t ld, int max_d
     return cfg.smem <= (size_t)SMEM_MAX;
 }
 
-template <typename K>
+// TAG makes the per-device flag private to ONE kernel instantiation: every k_gat_ring_fwd<A, B> has the same
+// function type, so a flag keyed on the type alone would be shared by all of them (and only the first
+// instantiation launched would ever get its shared-memory limit raised -> "invalid argument" for the next).
+template <int TAG, typename K>
 bool ring_set_smem(K kernel) {
-    // per (kernel, device): the attribute is a property of the function on the current device
     static bool done[64] = {false};
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;
@@ -684,7 +686,7 @@ int gat_ring_fwd(const void* xl, const void* xr, int64_t ld, const float* att, c
     const int grid = n_dst < nc_num_sms() ? n_dst : nc_num_sms();
 #define CALL(A, B)                                                                                                   \
     do {                                                                                                             \
-        if (!ring_set_smem(k_gat_ring_fwd<A, B>)) return 1;                                                          \
+        if (!ring_set_smem<(A) * 16 + (B)>(k_gat_ring_fwd<A, B>)) return 1;                                                          \
         k_gat_ring_fwd<A, B><<<grid, P.n_warps * 32, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
             (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, dst_off, slope, head_ws, alpha);                  \
     } while (0)
@@ -722,7 +724,7 @@ int gat_ring_bwd(const void* xl, const void* xr, int64_t ld, const float* att, c
     const int grid = n_dst < nc_num_sms() ? n_dst : nc_num_sms();
 #define CALL(A, B)                                                                                                   \
     do {                                                                                                             \
-        if (!ring_set_smem(k_gat_ring_bwd<A, B>)) return 1;                                                          \
+        if (!ring_set_smem<1024 + (A) * 16 + (B)>(k_gat_ring_bwd<A, B>)) return 1;                                                          \
         k_gat_ring_bwd<A, B><<<grid, P.n_warps * 32, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
             (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, slope, invH, dout, ldo, alpha, Dbuf, ds_ws,       \
             (__nv_bfloat16*)dxr, datt, mask);                                                                        \

@@ -301,11 +301,8 @@ extern "C" int nc_unique_sorted_i32(const int32_t* ids, int32_t n, int32_t* uniq
     int npad = 1;
     while (npad < n) npad <<= 1;
     const size_t smem = (size_t)npad * 2 * sizeof(int32_t);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_unique_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 2 * 4);
-        attr_set = true;
-    }
+    static bool attr_set[64] = {false};
+    if (int rc = nc_set_max_smem((const void*)k_unique_sorted, 16384 * 2 * 4, attr_set, "nc_unique_sorted_i32")) return rc;
     k_unique_sorted<<<1, 1024, smem, (cudaStream_t)stream>>>(ids, n, npad, uniq, inverse, n_unique);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_unique_sorted_i32");

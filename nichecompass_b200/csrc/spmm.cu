@@ -336,11 +336,8 @@ extern "C" int nc_spmm_csr_store(const int64_t* x_rowptr, const int32_t* x_col, 
     NC_REQUIRE(smem <= 200 * 1024, NC_EUNSUPPORTED,
                "nc_spmm_csr_store: n_cols=%d needs %zu B of shared memory (> 200 KiB)", n_cols, smem);
     if (n_rows == 0) return NC_OK;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_spmm_csr_store, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
-    }
+    static bool attr_set[64] = {false};
+    if (int rc = nc_set_max_smem((const void*)k_spmm_csr_store, 200 * 1024, attr_set, "nc_spmm_csr_store")) return rc;
     k_spmm_csr_store<<<n_rows, STORE_T, smem, (cudaStream_t)stream>>>(
         x_rowptr, x_col, x_val, n_cols, n_id, rowptr, col, w, wself, skip_self, out, ldo);
     nc_count_launch(1);
@@ -385,12 +382,9 @@ extern "C" int nc_csr_gather_rows(const int64_t* x_rowptr, const int32_t* x_col,
     NC_REQUIRE(smem <= 200 * 1024, NC_EUNSUPPORTED,
                "nc_csr_gather_rows: ldo=%lld needs %zu B of shared memory (> 200 KiB)", (long long)ldo, smem);
     if (n_rows == 0) return NC_OK;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_csr_gather_rows<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        cudaFuncSetAttribute(k_csr_gather_rows<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
-    }
+    static bool attr_f32[64] = {false}, attr_bf16[64] = {false};
+    if (int rc = nc_set_max_smem((const void*)k_csr_gather_rows<float>, 200 * 1024, attr_f32, "nc_csr_gather_rows")) return rc;
+    if (int rc = nc_set_max_smem((const void*)k_csr_gather_rows<__nv_bfloat16>, 200 * 1024, attr_bf16, "nc_csr_gather_rows")) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     if (out_dtype == NC_F32)
         k_csr_gather_rows<float><<<n_rows, 256, smem, s>>>(x_rowptr, x_col, x_val, n_cols, n_id, apply_log1p, (float*)out, ldo);

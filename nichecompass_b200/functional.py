@@ -63,11 +63,21 @@ _PARAM_EPOCH = 0
 _KEY_COUNTER = [0]
 
 
-def new_cache_key() -> int:
+def _purge_cache_key(k: int):
+    for key in [q for q in _PACK_CACHE if q == k or (isinstance(q, tuple) and q and q[0] == k)]:
+        _PACK_CACHE.pop(key, None)
+
+
+def new_cache_key(owner=None) -> int:
     """Process-unique token for a module's packed-weight cache entries (``id()`` values are
-    recycled after garbage collection and would let a new module hit a dead module's entry)."""
+    recycled after garbage collection and would let a new module hit a dead module's entry).
+    ``owner``: the module; its packed copies are dropped from the cache when it is collected."""
     _KEY_COUNTER[0] += 1
-    return _KEY_COUNTER[0]
+    k = _KEY_COUNTER[0]
+    if owner is not None:
+        import weakref
+        weakref.finalize(owner, _purge_cache_key, k)
+    return k
 
 
 

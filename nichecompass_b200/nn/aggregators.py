@@ -80,7 +80,7 @@ class OneHopAttentionNodeLabelAggregator(nn.Module):
         self.linear_r_l = _Lin(n_input, n_input * n_heads, bias=False)
         self.attn = nn.Parameter(glorot_(torch.empty(1, n_heads, n_input)))
         self.compute_dtype = torch.float32
-        self._key = new_cache_key()
+        self._key = new_cache_key(self)
         print(f"ONE HOP ATTENTION {modality.upper()} NODE LABEL AGGREGATOR -> "
               f"n_input: {n_input}, n_heads: {n_heads}")
 

@@ -62,7 +62,7 @@ class Encoder(nn.Module):
             self.fc_l1 = nn.Linear(self.n_input, int(self.n_input / 2))
             self.fc_l2 = nn.Linear(int(self.n_input / 2), n_hidden)
             self.fc_l2_bn = nn.BatchNorm1d(n_hidden)
-            self._key_fc = (new_cache_key(), new_cache_key())
+            self._key_fc = (new_cache_key(self), new_cache_key(self))
         else:
             self.fc_l1 = nn.Linear(self.n_input, n_hidden)
         self.dropout_rate = dropout_rate
@@ -73,14 +73,14 @@ class Encoder(nn.Module):
             raise ValueError(f"unknown conv_layer {conv_layer}")
         if n_layers == 2:
             self.conv_l1 = conv(n_hidden)                  # nn/encoders.py:106-108 / 123-127
-            self._key_l1 = new_cache_key()
+            self._key_l1 = new_cache_key(self)
         self.conv_mu = conv(n_latent)
         self.conv_logstd = conv(n_latent)
         if n_addon_latent != 0:
             self.addon_conv_mu = conv(n_addon_latent)
             self.addon_conv_logstd = conv(n_addon_latent)
         self.compute_dtype = torch.float32
-        self._key = new_cache_key()
+        self._key = new_cache_key(self)
 
     # ------------------------------------------------------------------ fused path
     @property

@@ -26,7 +26,7 @@ class MaskedLinear(nn.Linear):
         self.register_buffer("mask", mask.t().to(self.weight.dtype).contiguous())
         self.weight.data *= self.mask
         self.compute_dtype = torch.float32
-        self._key = new_cache_key()
+        self._key = new_cache_key(self)
 
     def apply_dynamic_mask_(self, dynamic_mask: torch.Tensor) -> torch.Tensor:
         """``weight.data *= dynamic_mask.t()`` -- the permanent side effect of the reference

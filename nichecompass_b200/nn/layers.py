@@ -37,7 +37,7 @@ class AddOnMaskedLayer(nn.Module):
         self.activation = activation
         self.compute_dtype = torch.float32
         self._embed_mask = None
-        self._key = new_cache_key()
+        self._key = new_cache_key(self)
 
     def _embed_col_mask(self) -> Optional[torch.Tensor]:
         """Without add-on GPs the embedding only feeds the masked features (nn/layers.py:134-142)."""

@@ -11,8 +11,15 @@ from . import _lib
 from ._lib import call, dtype_code
 
 
-def _i32(t: torch.Tensor) -> torch.Tensor:
-    return t if t.dtype == torch.int32 else t.to(torch.int32)
+def _i32(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """Index argument of the C ABI: int32 and contiguous.  The sampler emits exactly that (no work here);
+    an int64 / strided index tensor of foreign (PyG-style) code is converted instead of being read as garbage
+    through its raw pointer."""
+    if t is None or (t.dtype == torch.int32 and t.is_contiguous()):
+        return t
+    if t.dtype not in (torch.int32, torch.int64, torch.int16, torch.uint8):
+        raise TypeError(f"index tensor of dtype {t.dtype}")
+    return t.to(torch.int32).contiguous()
 
 
 def pad8(n: int) -> int:
@@ -35,6 +42,7 @@ def coo_to_dst_csr(edge_index: torch.Tensor, n_nodes: int) -> Tuple[torch.Tensor
 
 
 def gcn_norm_weights(rowptr, col, n_nodes: int, n_rows: int, use_out_degree: bool):
+    rowptr, col = _i32(rowptr), _i32(col)
     dev = rowptr.device
     w = torch.empty(max(col.numel(), 1), dtype=torch.float32, device=dev)
     wself = torch.empty(max(n_rows, 1), dtype=torch.float32, device=dev)
@@ -45,6 +53,7 @@ def gcn_norm_weights(rowptr, col, n_nodes: int, n_rows: int, use_out_degree: boo
 
 def reverse_csr(rowptr, col, n_nodes: int, n_rows: int, add_self: bool, n_entries: Optional[int] = None):
     """``n_entries``: upper bound of the number of reverse entries (host int; avoids a sync)."""
+    rowptr, col = _i32(rowptr), _i32(col)
     dev = rowptr.device
     if n_entries is None:
         n_entries = col.numel() + (n_rows if add_self else 0)
@@ -67,6 +76,7 @@ def spmm_csr(x: torch.Tensor, rowptr, col, w, wself, skip_self: bool, n_rows: in
              out_dtype: torch.dtype = torch.float32, out: Optional[torch.Tensor] = None,
              bias: Optional[torch.Tensor] = None, n_cols: Optional[int] = None) -> torch.Tensor:
     assert x.dim() == 2 and x.stride(1) == 1
+    rowptr, col = _i32(rowptr), _i32(col)
     n_cols = x.size(1) if n_cols is None else n_cols
     if out is None:
         out = torch.empty(n_rows, n_cols, dtype=out_dtype, device=x.device)
@@ -76,6 +86,7 @@ def spmm_csr(x: torch.Tensor, rowptr, col, w, wself, skip_self: bool, n_rows: in
 
 
 def spmm_csr_store(store, n_id, rowptr, col, w, wself, skip_self: bool, n_rows: int) -> torch.Tensor:
+    n_id, rowptr, col = _i32(n_id), _i32(rowptr), _i32(col)
     out = torch.empty(n_rows, store.n_cols, dtype=torch.float32, device=rowptr.device)
     call("nc_spmm_csr_store", store.rowptr, store.col, store.val, store.n_cols, n_id, rowptr, col,
          w, wself, int(skip_self), n_rows, out, out.stride(0))
@@ -89,6 +100,7 @@ def csr_gather_rows(store, n_id, n_rows: int, log1p: bool, dtype: torch.dtype, l
                     background: bool = False):
     """``background``: the low-footprint kernel for a side stream (``nc_csr_gather_rows_bg``)."""
     ld = store.n_cols if ld is None else ld
+    n_id = _i32(n_id)
     out = torch.empty(n_rows, ld, dtype=dtype, device=store.device)
     if background:
         call("nc_csr_gather_rows_bg", store.rowptr, store.col, store.val, store.n_cols, n_id, n_rows,
@@ -103,6 +115,7 @@ def dense_gather_rows(x: torch.Tensor, n_id, n_rows: int, log1p: bool, dtype: to
                       ld: Optional[int] = None):
     assert x.dtype == torch.float32 and x.stride(1) == 1
     ld = x.size(1) if ld is None else ld
+    n_id = _i32(n_id)
     out = torch.empty(n_rows, ld, dtype=dtype, device=x.device)
     call("nc_dense_gather_rows", x, x.stride(0), x.size(1), n_id, n_rows, int(log1p), out,
          dtype_code(dtype), ld)
