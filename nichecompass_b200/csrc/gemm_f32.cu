@@ -46,6 +46,15 @@ k_gemm_f32(const float* __restrict__ A, int64_t lda, const float* __restrict__ B
             Bs[k][n] = v;
         }
         __syncthreads();
+        // two-level summation: the 16 products of a k-block are summed on their own and then added to the running
+        // total, so the rounding error grows with K / 16 + 16 instead of K (a plain running sum over K = 5000 loses
+        // ~1.5 digits against a blocked CPU SGEMM -- enough to flip the sign of near-zero GATv2 pre-activations
+        // ten times as often, which the 1e-5 parity tests see as O(1e-3) gradient outliers)
+        float part[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) part[i][j] = 0.f;
 #pragma unroll
         for (int k = 0; k < GB_K; ++k) {
             float a[4], b[4];
@@ -56,8 +65,12 @@ k_gemm_f32(const float* __restrict__ A, int64_t lda, const float* __restrict__ B
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+                for (int j = 0; j < 4; ++j) part[i][j] = fmaf(a[i], b[j], part[i][j]);
         }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] += part[i][j];
         __syncthreads();
     }
 #pragma unroll

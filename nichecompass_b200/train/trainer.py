@@ -242,6 +242,9 @@ class Trainer(BaseTrainerMixin):
         if self.world_size_ > 1:
             self.optimizer.all_reduce_grads()
             self._sync_running_stats()
+        hook = getattr(self, "after_backward", None)
+        if hook is not None:                 # parity tests: the gradients live in the arena until the Adam kernel clears them
+            hook(self, node_out, edge_out)
         self.optimizer.step(clip_value=self.grad_clip_value_)
         return loss_dict
 

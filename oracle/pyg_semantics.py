@@ -66,14 +66,19 @@ def gatv2_conv(x: torch.Tensor, edge_index: torch.Tensor,
                lin_r_w: torch.Tensor, lin_r_b: Optional[torch.Tensor],
                att: torch.Tensor, bias: Optional[torch.Tensor],
                heads: int, negative_slope: float = 0.2,
-               return_alpha: bool = False):
+               return_alpha: bool = False, round_fn=None):
     """GATv2Conv(in, C, heads=H, concat=False, add_self_loops=True, share_weights=False)
-    (SURVEY.md App. A.1).  Returns [n, C] (head mean + bias)."""
+    (SURVEY.md App. A.1).  Returns [n, C] (head mean + bias).
+    ``round_fn`` (oracle/bf16_emulation.py, tests of the bf16 mode only): applied to x_l and x_r, the two tensors
+    the CUDA tensor-core mode stores in bf16; ``None`` = the reference arithmetic."""
     n = x.size(0)
     H = heads
     C = lin_l_w.size(0) // H
-    x_l = F.linear(x, lin_l_w, lin_l_b).view(n, H, C)
-    x_r = F.linear(x, lin_r_w, lin_r_b).view(n, H, C)
+    x_l = F.linear(x, lin_l_w, lin_l_b)
+    x_r = F.linear(x, lin_r_w, lin_r_b)
+    if round_fn is not None:
+        x_l, x_r = round_fn(x_l), round_fn(x_r)
+    x_l, x_r = x_l.view(n, H, C), x_r.view(n, H, C)
     ei, _ = remove_self_loops(edge_index)
     ei, _ = add_self_loops(ei, num_nodes=n)
     j, i = ei[0], ei[1]

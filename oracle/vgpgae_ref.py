@@ -21,6 +21,7 @@ from typing import Dict, List, Optional
 import torch
 import torch.nn.functional as F
 
+from . import bf16_emulation as emu
 from . import pyg_semantics as pyg
 
 
@@ -124,6 +125,12 @@ class VGPGAERef:
     def _conv(self, name, h, edge_index):
         c, p = self.cfg, self.p
         if c["conv_layer"] == "gatv2conv":
+            if c.get("emulate_bf16", False):       # tests of the CUDA bf16 mode: oracle/bf16_emulation.py
+                return pyg.gatv2_conv(h, edge_index,
+                                      emu.round_fwd(p[f"encoder.{name}.lin_l.weight"]), p[f"encoder.{name}.lin_l.bias"],
+                                      emu.round_fwd(p[f"encoder.{name}.lin_r.weight"]), p[f"encoder.{name}.lin_r.bias"],
+                                      p[f"encoder.{name}.att"], p[f"encoder.{name}.bias"], c["heads"],
+                                      round_fn=emu.round_both)
             return pyg.gatv2_conv(h, edge_index,
                                   p[f"encoder.{name}.lin_l.weight"], p[f"encoder.{name}.lin_l.bias"],
                                   p[f"encoder.{name}.lin_r.weight"], p[f"encoder.{name}.lin_r.bias"],
@@ -137,7 +144,15 @@ class VGPGAERef:
         c = self.cfg
         if embed is not None and c.get("cat_covariates_embed_mode", "input") == "input":
             x_enc = torch.cat((x_enc, embed), dim=1)
-        h = torch.relu(F.linear(x_enc, self.p["encoder.fc_l1.weight"], self.p["encoder.fc_l1.bias"]))
+        if c.get("emulate_bf16", False):
+            # bf16 operands (x_enc, W1 shadow), exact accumulation; d hidden rounded after the ReLU mask,
+            # hidden itself stored in bf16 (oracle/bf16_emulation.py; single fc layer, GATv2 only)
+            assert c.get("n_fc_layers", 1) == 1 and c.get("n_layers", 1) == 1 and c["conv_layer"] == "gatv2conv"
+            pre = F.linear(emu.round_fwd(x_enc), emu.round_fwd(self.p["encoder.fc_l1.weight"]),
+                           self.p["encoder.fc_l1.bias"])
+            h = emu.round_fwd(torch.relu(emu.round_bwd(pre)))
+        else:
+            h = torch.relu(F.linear(x_enc, self.p["encoder.fc_l1.weight"], self.p["encoder.fc_l1.bias"]))
         if c.get("n_fc_layers", 1) == 2:
             h = torch.relu(F.linear(h, self.p["encoder.fc_l2.weight"], self.p["encoder.fc_l2.bias"]))
             bn = "encoder.fc_l2_bn."
@@ -178,6 +193,10 @@ class VGPGAERef:
 
         def masked_linear(key, inp, dyn):
             w, m = p[f"{pre}.{key}.weight"], p[f"{pre}.{key}.mask"]
+            if c.get("emulate_bf16", False):
+                assert dyn is None and embed is None
+                all_ones = bool((m == 1).all())
+                return emu.MaskedLinearBF16.apply(inp, w * m, all_ones or not emu.mask_is_sparse(m))
             if dyn is not None:
                 dyn_t = dyn.t().to(w.dtype)
                 with torch.no_grad():

@@ -116,6 +116,8 @@ def test_gatv2_fwd_bwd_vs_torch(dtype, Cs, ring, n_dst, max_deg):
          HostPtr(seg_host), NC, Hh, deg, 0.2, dout, dout.stride(0), alpha, ds, dxl, dxr, datt, dbias, head_ws, bwd_ws,
          ws_bytes, n_slots)
     tol = 1e-2 if dtype == torch.bfloat16 else 2e-4
+    print(f"gatv2 {dtype} Cs={Cs} ring={ring}: out {H.rel_err(out, ref):.2e} dxl {H.rel_err(dxl[:, :NL].float(), xl32.grad[:, :NL]):.2e} "
+          f"dxr {H.rel_err(dxr[:, :NL].float(), xr32.grad[:, :NL]):.2e} datt {H.rel_err(datt[:NL], att32.grad[:NL]):.2e}")
     assert H.rel_err(dxl[:, :NL].float(), xl32.grad[:, :NL]) < tol
     assert H.rel_err(dxr[:, :NL].float(), xr32.grad[:, :NL]) < tol
     assert H.rel_err(datt[:NL], att32.grad[:NL]) < 2e-4
