@@ -232,6 +232,13 @@ int nc_nb_loss_fused(const float* logits, int64_t ldl, const float* x, int64_t l
                      float scale, float* means, int64_t ldm, double* loss_sum, float* dlogits,
                      int64_t lddl, float* dtheta, float* dx, int64_t lddx, void* stream);
 
+/* Negative-binomial loss on given means, as the reference exports it (modules/losses.py:169-212
+ * compute_omics_recon_nb_loss(x, mu, theta, eps)): loss_sum += scale * sum_{r,c} -ll (fp64); dmu / dtheta
+ * (nullable; dtheta is accumulated) = scale * d(sum -ll)/d.  theta: positive inverse dispersion [F].   */
+int nc_nb_loss_means(const float* x, int64_t ldx, const float* mu, int64_t ldmu, const float* theta,
+                     int32_t n_rows, int32_t F, float eps, float scale, double* loss_sum, float* dmu,
+                     int64_t lddmu, float* dtheta, void* stream);
+
 /* Cosine-similarity graph decoder (nn/decoders.py:56-62, nn/utils.py:8-36): rows [0,n_pairs)
  * of z against rows [n_pairs, 2*n_pairs).  norms: fp32[2*n_pairs] saved for the backward.   */
 int nc_cosine_fwd(const float* z, int64_t ldz, int32_t P, int32_t n_pairs, float* logits,

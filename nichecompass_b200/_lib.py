@@ -50,6 +50,8 @@ def _parse_header(path: str) -> dict:
 
 # entry points that return a value instead of a status code (bound separately in ``_load``)
 VALUE_FUNCS = ("nc_last_error", "nc_version", "nc_launch_count", "nc_gatv2_bwd_ws_bytes")
+# synchronous host-side entry points (no stream argument; called through ``lib()`` directly, not ``call``)
+HOST_FUNCS = ("nc_host_alloc", "nc_host_free")
 SIGNATURES = {k: v for k, v in _parse_header(HEADER_PATH).items() if k not in VALUE_FUNCS}
 
 _lib = None

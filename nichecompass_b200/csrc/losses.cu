@@ -134,6 +134,32 @@ k_nb_fused(const float* __restrict__ logits, int64_t ldl, const float* __restric
     }
 }
 
+// ------------------------------------------------------------------------- NB loss on given means
+// modules/losses.py:169-212 as the reference exports it: x, mu [R, F], theta [F] (already positive).
+// loss_sum += scale * sum -ll (fp64); dmu / dtheta (nullable) = scale * d(sum -ll)/d.
+__global__ void __launch_bounds__(256)
+k_nb_means(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu, int64_t ldmu,
+           const float* __restrict__ theta, int R, int F, float eps_f, float scale, double* __restrict__ loss_sum,
+           float* __restrict__ dmu, int64_t lddmu, float* __restrict__ dtheta) {
+    __shared__ double redd[32];
+    const double eps = (double)eps_f;
+    double loss = 0.0;
+    const int64_t total = (int64_t)R * F;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(q / F), c = (int)(q - (int64_t)r * F);
+        const double xv = (double)x[(int64_t)r * ldx + c], m = (double)mu[(int64_t)r * ldmu + c], th = (double)theta[c];
+        const double ltm = log(th + m + eps);
+        loss -= th * (log(th + eps) - ltm) + xv * (log(m + eps) - ltm) + lgamma(xv + th) - lgamma(th) - lgamma(xv + 1.0);
+        if (dmu) dmu[(int64_t)r * lddmu + c] = (float)(-(double)scale * (xv / (m + eps) - (xv + th) / (th + m + eps)));
+        if (dtheta) {
+            const double d = log(th + eps) + th / (th + eps) - ltm - (th + xv) / (th + m + eps) + digamma_d(xv + th) - digamma_d(th);
+            atomicAdd(dtheta + c, (float)(-(double)scale * d));
+        }
+    }
+    loss = block_sum_d(loss, redd);
+    if (threadIdx.x == 0) atomicAdd(loss_sum, loss * (double)scale);
+}
+
 // ------------------------------------------------------------------------- cosine decoder
 // pair e: a = z[e], b = z[n_pairs + e]; logits[e] = <a/max(|a|,eps), b/max(|b|,eps)>
 __global__ void __launch_bounds__(128)
@@ -308,5 +334,19 @@ extern "C" int nc_kl_fwd_bwd(const float* mu, int64_t ldmu, const float* logstd,
     k_kl<<<blocks, 256, 0, (cudaStream_t)stream>>>(mu, ldmu, logstd, ldls, R, P, scale, sum_out, dmu, lddmu, dlogstd, lddls);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_kl_fwd_bwd");
+    return NC_OK;
+}
+
+extern "C" int nc_nb_loss_means(const float* x, int64_t ldx, const float* mu, int64_t ldmu, const float* theta,
+                                int32_t n_rows, int32_t F, float eps, float scale, double* loss_sum, float* dmu,
+                                int64_t lddmu, float* dtheta, void* stream) {
+    NC_REQUIRE(n_rows > 0 && F > 0 && ldx >= F && ldmu >= F && (dmu == nullptr || lddmu >= F), NC_ESHAPE,
+               "nc_nb_loss_means: bad shape n_rows=%d F=%d", n_rows, F);
+    const int64_t total = (int64_t)n_rows * F;
+    int blocks = (int)std::min<int64_t>(nc_cdiv(total, 256), 4 * nc_num_sms());
+    k_nb_means<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, ldx, mu, ldmu, theta, n_rows, F, eps, scale, loss_sum, dmu,
+                                                         lddmu, dtheta);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_nb_loss_means");
     return NC_OK;
 }

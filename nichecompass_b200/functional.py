@@ -730,6 +730,27 @@ class NBLossFusedFn(torch.autograd.Function):
         return dlog * g, dth * g, dx, None
 
 
+class NBLossMeansFn(torch.autograd.Function):
+    """modules/losses.py:169-212 on precomputed means: mean over rows of the summed NB negative log-likelihood."""
+
+    @staticmethod
+    def forward(ctx, x, mu, theta, eps):
+        R, F = mu.shape
+        xd, md, td = x.detach().float().contiguous(), mu.detach().float().contiguous(), theta.detach().float().contiguous()
+        acc = torch.zeros(1, dtype=torch.float64, device=mu.device)
+        dmu = torch.empty(R, F, dtype=torch.float32, device=mu.device) if ctx.needs_input_grad[1] else None
+        dth = torch.zeros(F, dtype=torch.float32, device=mu.device) if ctx.needs_input_grad[2] else None
+        call("nc_nb_loss_means", xd, xd.stride(0), md, md.stride(0), td, R, F, float(eps), 1.0 / R, acc, dmu,
+             F if dmu is not None else 0, dth)
+        ctx.save_for_backward(dmu, dth)
+        return acc.float().reshape(())
+
+    @staticmethod
+    def backward(ctx, g):
+        dmu, dth = ctx.saved_tensors
+        return None, (dmu * g if dmu is not None else None), (dth * g if dth is not None else None), None
+
+
 # --------------------------------------------------------------------------- weight regularisers
 class WeightRegFn(torch.autograd.Function):
     """sum over the given decoder weights of  l1 * sum |W * l1mask|  +  gl * sum_c sqrt(cnt_c) ||W[:,c]||_2

@@ -12,6 +12,7 @@ import numpy as np
 import scipy.sparse as sp
 import torch
 
+from .. import ops
 from ..data import initialize_dataloaders, prepare_data
 from ..modules import VGPGAE
 from ..train import Trainer
@@ -585,14 +586,147 @@ class NicheCompass(BaseModelMixin):
     def compute_gp_peak_importances(self, *a, **k):
         self._out_of_scope("compute_gp_peak_importances")
 
-    def get_omics_decoder_outputs(self, *a, **k):
-        self._out_of_scope("get_omics_decoder_outputs")
+    # ------------------------------------------------------------------ post-hoc retrieval on the hot-path kernels
+    def _full_node_loader(self, adata, adata_atac, node_batch_size: int):
+        device = next(self.model.parameters()).device
+        data_dict = prepare_data(
+            adata=adata, cat_covariates_label_encoders=self.model.cat_covariates_label_encoders_,
+            adata_atac=adata_atac, counts_key=self.counts_key_, adj_key=self.adj_key_,
+            cat_covariates_keys=self.cat_covariates_keys_, edge_val_ratio=0., edge_test_ratio=0.,
+            node_val_ratio=0., node_test_ratio=0., device=device)
+        return initialize_dataloaders(node_masked_data=data_dict["node_masked_data"], edge_train_data=None,
+                                      edge_val_data=None, edge_batch_size=None, node_batch_size=node_batch_size,
+                                      shuffle=False)["node_train_loader"]
 
-    def get_recon_edge_probs(self, *a, **k):
-        self._out_of_scope("get_recon_edge_probs")
+    @torch.no_grad()
+    def get_omics_decoder_outputs(self, adata=None, adata_atac=None, only_active_gps: bool = True,
+                                  node_batch_size: int = 64) -> dict:
+        """Negative-binomial means of the target / source decoders for every observation over all output
+        features (models/nichecompass.py:1383-1470): ``{target,source}_{rna,atac}_nb_means`` as float64 arrays
+        [n_obs, n_features].  The walk over consecutive blocks of ``node_batch_size`` nodes is the reference's
+        (with the default one-hop-norm labels the source library size depends on the sampled block, SURVEY.md
+        App. B-6); every block runs encoder GEMMs + GATv2 kernels + decoder GEMM + ``nc_nb_loss_fused``."""
+        self._check_if_trained(warn=False)
+        if adata is None:
+            adata = self.adata
+        if adata_atac is None and hasattr(self, "adata_atac"):
+            adata_atac = self.adata_atac
+        loader = self._full_node_loader(adata, adata_atac, node_batch_size)
+        device = next(self.model.parameters()).device
+        n_obs = adata.shape[0]
+        keys = [f"{ent}_{mod}_nb_means" for mod in self.model.modalities_ for ent in ("target", "source")]
+        width = {"rna": self.n_output_genes_, "atac": getattr(self, "n_output_peaks_", 0)}
+        outs = {k: torch.empty(n_obs, width[k.split("_")[1]], dtype=torch.float32, device=device) for k in keys}
+        was_training = self.model.training
+        self.model.eval()
+        lo = 0
+        for node_batch in loader:
+            hi = lo + int(node_batch.batch_size)
+            res = self.model.get_omics_decoder_outputs(node_batch=node_batch, only_active_gps=only_active_gps)
+            for k in keys:
+                outs[k][lo:hi] = res[k]
+            lo = hi
+        self.model.train(was_training)
+        return {k: v.cpu().numpy().astype(np.float64) for k, v in outs.items()}
 
-    def get_neighbor_importances(self, *a, **k):
-        self._out_of_scope("get_neighbor_importances")
+    @torch.no_grad()
+    def get_neighbor_importances(self, node_batch_size: Optional[int] = None) -> sp.csr_matrix:
+        """Aggregation weights of the node-label aggregator as a sparse [n_obs, n_obs] matrix: entry (i, j) is the
+        weight observation i gives to its neighbour j (models/nichecompass.py:1600-1686; mean over the heads for
+        ``one-hop-attention``).  The reference reads ``self.model.node_label_aggregator`` (the attribute is
+        ``rna_node_label_aggregator``) and pairs SparseTensor-ordered weights with loader-ordered edges; this is
+        the documented intent: one weight per (target, neighbour) pair of the sampled block, the self pair
+        carrying the fill_diag weight.  ``one-hop-sum`` has unit weights."""
+        self._check_if_trained(warn=False)
+        if node_batch_size is None:
+            node_batch_size = self.node_batch_size_
+        loader = self._full_node_loader(self.adata, getattr(self, "adata_atac", None), node_batch_size)
+        method = self.model.node_label_method_
+        agg = self.model.rna_node_label_aggregator
+        gi, gj, gv = [], [], []
+        for b in loader:
+            nb, g = int(b.batch_size), b.graph
+            n_id = b.n_id.long()
+            rp = g.rowptr[:nb + 1].long()
+            E = int(rp[-1])
+            if E == 0:
+                continue
+            rows = torch.repeat_interleave(torch.arange(nb, device=rp.device), rp[1:] - rp[:-1])
+            cols = g.col[:E].long()
+            if method == "one-hop-norm":
+                w, wself = g.gcn_weights(use_out_degree=True, n_rows=nb)
+                val = torch.where(cols == rows, wself[rows], w[:E])
+            elif method == "one-hop-sum":
+                val = torch.ones(E, dtype=torch.float32, device=rp.device)
+            else:
+                x = ops.csr_gather_rows(b.store, b.n_id, g.n_nodes, False, torch.float32)[:, :agg.n_input]
+                _, alpha = agg(x, g, return_agg_weights=True, n_rows=nb)
+                val = alpha[:E].mean(dim=-1)
+            gi.append(n_id[rows]); gj.append(n_id[cols]); gv.append(val)
+        n = self.adata.shape[0]
+        if not gi:
+            return sp.csr_matrix((n, n))
+        gi, gj, gv = (torch.cat(t).cpu().numpy() for t in (gi, gj, gv))
+        return sp.csr_matrix((gv.astype(np.float64), (gi, gj)), shape=(n, n))
+
+    @torch.no_grad()
+    def get_recon_edge_probs(self, node_batch_size: int = 2048, device: Optional[str] = None,
+                             edge_thresh: Optional[float] = None, n_neighbors: Optional[int] = None,
+                             return_edge_probs: bool = False, compute_dtype: torch.dtype = torch.float32
+                             ) -> Union[sp.csr_matrix, torch.Tensor]:
+        """Reconstructed adjacency (or the dense edge-probability matrix) from the stored latent representation
+        (models/nichecompass.py:1473-1597): p_ij = sigmoid(cosine(z_i, z_j)) with the inactive gene programs put
+        back as zeros; an edge wherever p_ij >= ``edge_thresh``, or >= the row's k-th largest probability with
+        k = ``n_neighbors`` (result symmetrised) / the row's degree in the input graph (not symmetrised).
+        (The reference passes ``reduced_obs_start_idx`` to a graph decoder whose ``forward`` no longer takes it,
+        nn/decoders.py:39-62, so the call fails as shipped; this is the behaviour its docstring describes.)
+        One row block = one GEMM of normalised rows, ``nc_gemm_f32`` or (``compute_dtype=torch.bfloat16``) the
+        tcgen05 kernel; thresholds by a device sort; only the edges found leave the device."""
+        self._check_if_trained(warn=False)
+        if self.latent_key_ not in self.adata.obsm:
+            raise ValueError(f"Please first store the latent representations in adata.obsm['{self.latent_key_}']. "
+                             "They can be retrieved via 'model.get_latent_representation()'.")
+        dev = next(self.model.parameters()).device if device is None else torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("get_recon_edge_probs runs on the CUDA kernels (nichecompass_b200 has no CPU path)")
+        z = torch.as_tensor(np.asarray(self.adata.obsm[self.latent_key_]), dtype=torch.float32, device=dev)
+        active = self.model.get_active_gp_mask().to(dev)
+        zf = torch.zeros(z.size(0), active.numel(), dtype=torch.float32, device=dev)
+        zf[:, active] = z
+        # nn/utils.py:8-36: rows scaled by 1 / max(|z|, eps); padded to a TMA-legal pitch
+        zn = zf / zf.norm(dim=1, keepdim=True).clamp_min(1e-8)
+        P = zn.size(1)
+        zp = torch.zeros(zn.size(0), ops.pad8(P), dtype=compute_dtype, device=dev)
+        zp[:, :P] = zn
+        n = zp.size(0)
+
+        def block_probs(lo, hi):
+            logits = ops.gemm(zp[lo:hi], zp, out_dtype=torch.float32, M=hi - lo, N=n, K=zp.size(1))
+            return torch.sigmoid(logits)
+        if return_edge_probs:
+            return torch.cat([block_probs(lo, min(lo + node_batch_size, n)) for lo in range(0, n, node_batch_size)])
+        deg = None
+        if edge_thresh is None and n_neighbors is None:
+            deg = torch.as_tensor(np.asarray(self.adata.obsp[self.adj_key_].sum(axis=1)).flatten().astype(np.int64),
+                                  device=dev)
+        ri, ci = [], []
+        for lo in range(0, n, node_batch_size):
+            hi = min(lo + node_batch_size, n)
+            probs = block_probs(lo, hi)
+            if edge_thresh is not None:
+                keep = probs >= edge_thresh
+            else:
+                k = deg[lo:hi] if deg is not None else torch.full((hi - lo,), int(n_neighbors), device=dev)
+                srt = probs.sort(dim=1, descending=True).values
+                thr = srt.gather(1, (k - 1).clamp_(0, n - 1)[:, None])
+                keep = probs >= thr
+            nz = keep.nonzero()
+            ri.append(nz[:, 0] + lo); ci.append(nz[:, 1])
+        ri, ci = torch.cat(ri).cpu().numpy(), torch.cat(ci).cpu().numpy()
+        adj = sp.csr_matrix((np.ones(ri.shape[0]), (ri, ci)), shape=(n, n))
+        if n_neighbors is not None:
+            adj = adj.maximum(adj.T)
+        return adj
 
     def get_gp_summary(self, *a, **k):
         self._out_of_scope("get_gp_summary")

@@ -36,9 +36,14 @@ def compute_omics_recon_nb_loss_from_logits(logits: torch.Tensor, x_full: torch.
 
 
 def compute_omics_recon_nb_loss(x: torch.Tensor, mu: torch.Tensor, theta: torch.Tensor, eps: float = 1e-8):
-    raise NotImplementedError(
-        "the stand-alone NB loss on precomputed means has no CUDA kernel; VGPGAE uses "
-        "compute_omics_recon_nb_loss_from_logits (same arithmetic fused with the decoder softmax)")
+    """Mean over rows of the summed negative-binomial negative log-likelihood for given means ``mu`` [R, F] and
+    inverse dispersions ``theta`` [F] (modules/losses.py:169-212), differentiable w.r.t. ``mu`` and ``theta``.
+    ``VGPGAE`` itself uses ``compute_omics_recon_nb_loss_from_logits`` (the same arithmetic fused with the decoder
+    softmax and the column selection)."""
+    from ..functional import NBLossMeansFn
+    if theta.dim() != 1 or theta.numel() != mu.size(-1):
+        theta = theta.expand(mu.size(-1)) if theta.numel() == 1 else theta.reshape(-1)
+    return NBLossMeansFn.apply(x, mu, theta, eps)
 
 
 def _rna_decoder_weights(model: nn.Module, layer_name: str):

@@ -658,10 +658,13 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
         ``active_gp_thresh_ratio_`` times the maximum, by sum OR by mean over non-zero weights,
         thresholded separately for prior and add-on programs unless ``active_gp_type_ == 'mixed'``
         (modules/vgpgae.py:1205-1334)."""
-        if normalize_gp_weights_with_features_scale_factors:
-            raise NotImplementedError("normalisation with feature scale factors is not implemented")
-        if abs_gp_weights_agg_mode not in ("sum", "nzmeans", "sum+nzmeans"):
-            raise NotImplementedError(f"aggregation mode {abs_gp_weights_agg_mode} is not implemented")
+        if abs_gp_weights_agg_mode not in ("sum", "nzmeans", "sum+nzmeans", "nzmedians", "sum+nzmedians"):
+            raise ValueError(f"unknown aggregation mode {abs_gp_weights_agg_mode}")
+        if normalize_gp_weights_with_features_scale_factors or "nzmedians" in abs_gp_weights_agg_mode:
+            # analysis-time variants (medians / per-feature scale factors): evaluated on the materialised weight
+            # matrix, statement by statement as modules/vgpgae.py:1254-1330 -- not on the training path
+            return self._active_gp_mask_general(abs_gp_weights_agg_mode, return_gp_weights,
+                                                normalize_gp_weights_with_features_scale_factors)
         dev = self.device
         Pp, Pa = self.n_prior_gp_, self.n_addon_gp_
         abs_p, nnz_p = self._gp_block_stats("masked_l")
@@ -686,6 +689,73 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
         if return_gp_weights:
             return active, self.get_gp_weights(gp_type="all")[0][:, active]
         return active
+
+    @torch.no_grad()
+    def _active_gp_mask_general(self, mode: str, return_gp_weights: bool, normalize: bool):
+        dev = self.device
+        Pp, Pa = self.n_prior_gp_, self.n_addon_gp_
+        active = torch.zeros(Pp + Pa, dtype=torch.bool, device=dev)
+        if self.active_gp_type_ == "mixed":
+            types = [("all", slice(None, None))]
+        elif Pa > 0:
+            types = [("masked", slice(None, Pp)), ("addon", slice(Pp, None))]
+        else:
+            types = [("masked", slice(None, Pp))]
+        ratio = self.active_gp_thresh_ratio_
+        for gp_type, sl in types:
+            w = self.get_gp_weights(only_masked_features=False, gp_type=gp_type)[0]
+            if normalize:
+                w = w / self.features_scale_factors_[:, None].to(dev)
+            w = self.running_mean_abs_mu[sl] * w
+            sums = w.abs().sum(0)
+            if mode in ("sum", "sum+nzmeans", "sum+nzmedians"):
+                active[sl] |= sums >= ratio * sums.max()
+            if mode in ("nzmeans", "sum+nzmeans"):
+                nzmeans = torch.nan_to_num(sums / torch.count_nonzero(w, dim=0))
+                active[sl] |= nzmeans >= ratio * nzmeans.max()
+            if mode in ("nzmedians", "sum+nzmedians"):
+                with_nan = torch.where(w == 0, torch.full_like(w, float("nan")), w.abs())
+                med = torch.nan_to_num(torch.nanmedian(with_nan, dim=0).values)
+                active[sl] |= med >= 0.01 * med.max()               # the reference hard-codes 0.01 here (:1317)
+        if return_gp_weights:
+            return active, self.get_gp_weights(gp_type="all")[0][:, active]
+        return active
+
+    # ------------------------------------------------------------------ decoder outputs (post-hoc retrieval)
+    @torch.no_grad()
+    def get_omics_decoder_outputs(self, node_batch, only_active_gps: bool = True) -> dict:
+        """Negative-binomial means of every decoder for the seeds of ``node_batch`` over ALL output features
+        (modules/vgpgae.py:1439-1620): encoder -> z (= mu in eval mode) with inactive gene programs zeroed ->
+        library size = sum of the node labels over all features -> exp(log lib) * softmax(decoder logits).
+        No column selection here, unlike ``forward``.  Same kernels as the training path:
+        ``nc_nb_loss_fused`` with every column selected returns the means."""
+        graph, x_enc, target_rows, neighbor_rows, embed = self._prepare(node_batch, "omics")
+        P = self.n_prior_gp_ + self.n_addon_gp_
+        nb = int(node_batch.batch_size)
+        ml = self.encoder.encode(x_enc, graph)[:nb]
+        mu, logstd = ml[:, :P].contiguous(), ml[:, P:].contiguous()
+        eps = self._draw_eps(mu)
+        active_u8 = self.get_active_gp_mask().to(torch.uint8) if only_active_gps else None
+        z = mu if (eps is None and active_u8 is None) else ReparamFn.apply(mu, logstd, eps, active_u8)
+        x_t, x_n = target_rows(nb), neighbor_rows(nb)
+        Fg = self.n_output_genes_
+        cols = {"rna": slice(0, Fg), "atac": slice(Fg, Fg + self.n_output_peaks_)}
+        inj = {"rna": "gene_expr_decoder", "atac": "chrom_access_decoder"}
+        emb_b = embed[:nb] if embed is not None else None
+        out = {"node_labels": {}}
+        for mod in self.modalities_:
+            for ent, xsrc in (("target", x_t), ("source", x_n)):
+                key = f"{ent}_{mod}"
+                dec = getattr(self, f"{key}_decoder")
+                dyn = getattr(self, f"{key}_dynamic_decoder_mask").to(self.device) if mod == "atac" else None
+                e = emb_b if (emb_b is not None and inj[mod] in self.cat_covariates_embeds_injection_) else None
+                logits = dec.logits(z, e, dyn)
+                labels = xsrc[:, cols[mod]].contiguous()
+                every = torch.ones(labels.size(1), dtype=torch.uint8, device=labels.device)
+                _, means = compute_omics_recon_nb_loss_from_logits(logits, labels, getattr(self, f"{key}_theta"), every)
+                out["node_labels"][key] = labels
+                out[f"{key}_nb_means"] = means
+        return out
 
     def log_module_hyperparams_to_mlflow(self, excluded_attr: list = ["features_idx_dict_", "gene_peaks_mask_"]):
         """mlflow is not part of this build; logging is a no-op (modules/vgpgae.py:1336-1366)."""

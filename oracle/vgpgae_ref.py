@@ -342,6 +342,34 @@ class VGPGAERef:
                 out[f"{key}_nb_means"] = means[:, ridx]
         return out
 
+    def get_omics_decoder_outputs(self, batch, only_active_gps=True, eps=None):
+        """modules/vgpgae.py:1439-1620: NB means over ALL output features (no column selection), library size =
+        row sum of the node labels over all features; z = mu in eval mode."""
+        c = self.cfg
+        x, edge_index = batch.x, batch.edge_index
+        nb = batch.batch_size
+        x_enc = torch.log(1 + x) if c.get("log_variational", True) else x
+        embed = self._embed(getattr(batch, "cat_covariates_cats", None))
+        inj = c.get("cat_covariates_embeds_injection", [])
+        mu_all, logstd_all = self.encoder(x_enc, edge_index, embed if "encoder" in inj else None)
+        mu, logstd = mu_all[:nb], logstd_all[:nb]
+        z = mu + eps * torch.exp(logstd) if self.training else mu.clone()
+        if only_active_gps:
+            z[:, ~self.get_active_gp_mask()] = 0
+        Fg = c["n_output_genes"]
+        out = {"node_labels": {}}
+        for mod, xm, inj_key in (("rna", x[:, :Fg], "gene_expr_decoder"), ("atac", x[:, Fg:], "chrom_access_decoder")):
+            if mod not in self.modalities:
+                continue
+            x_nbr, _ = self.aggregate(xm, edge_index, mod)
+            for ent, lab in (("target", xm[:nb]), ("source", x_nbr[:nb])):
+                key = f"{ent}_{mod}"
+                out["node_labels"][key] = lab
+                e = embed[:nb] if (embed is not None and inj_key in inj) else None
+                out[f"{key}_nb_means"] = self.decoder(key, z, torch.log(lab.sum(1, keepdim=True)), e,
+                                                      self.dynamic_mask[key] if mod == "atac" else None)
+        return out
+
     def _update_atac_dynamic_mask(self):
         """modules/vgpgae.py:813-857."""
         c = self.cfg
