@@ -4,7 +4,7 @@ bench.py -- training throughput of the VGPGAE hot loop (BASELINE.json metric: tr
 per epoch).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
-                    [--workload c2|c1|c3] [--edge-batch-size B] [--cells N_CELLS]
+                    [--workload c2|c1|c3|c4] [--edge-batch-size B] [--cells N_CELLS]
 
 A "step" is one iteration of the reference hot loop (train/trainer.py:364-421): one node batch
 through the omics decoders, one edge batch (B positive + B negative edges) through the graph
@@ -65,9 +65,26 @@ WORKLOADS = {
     "c3": dict(name="multi-sample atlas, 8 samples x 500k cells x 5k genes, kNN k=8, sample covariate embedding",
                n_cells=4_000_000, n_genes=5000, k=8, n_prior_gp=1500, n_addon_gp=100, n_samples=8,
                lib_mean=300., dtype="bf16"),
+    # BASELINE.json configs[3]: multimodal RNA + ATAC (MaskedGeneExprDecoder + MaskedChromAccessDecoder)
+    "c4": dict(name="multimodal RNA+ATAC, 2M cells x 5k genes + 50k peaks, kNN k=8, 1.5k prior + 100 add-on gene "
+                    "programs, masked RNA and chromatin-accessibility decoders, bf16",
+               n_cells=2_000_000, n_genes=5000, n_peaks=50_000, k=8, n_prior_gp=1500, n_addon_gp=100, n_samples=1,
+               lib_mean=300., atac_lib_mean=600., dtype="bf16"),
 }
 LAMBDAS = dict(lambda_edge_recon=500000., lambda_gene_expr_recon=300., lambda_l1_addon=30.,
                lambda_group_lasso=0., lambda_l1_masked=0.)       # NicheCompass.train defaults
+
+
+def config_dict(wl, edge_bs, node_bs, steps_per_epoch, world):
+    """Workload description shared by both arms (the driver compares the two dicts key by key)."""
+    d = {"workload": wl["name"], "n_cells": wl["n_cells"], "n_genes": wl["n_genes"], "k": wl["k"],
+         "edge_batch_size": int(edge_bs), "node_batch_size": int(node_bs), "steps_per_epoch": int(steps_per_epoch),
+         "global_steps_per_epoch": int(math.ceil(steps_per_epoch / world)), "parallelism": f"dp{world}",
+         "l2_policy": "inputs larger than L2: every step samples a new sub-graph and reads all parameters "
+                      "(260 MB fp32 at C2) plus fresh activations (> 126 MB L2); no flush needed"}
+    if wl.get("n_peaks"):
+        d["n_peaks"] = wl["n_peaks"]
+    return d
 
 
 def log(*a):
@@ -105,6 +122,10 @@ def build_adata(wl: dict, seed: int):
     adata = make_synthetic_adata_large(wl["n_cells"], wl["n_genes"], wl["k"], wl["n_prior_gp"], seed=seed,
                                        n_samples=wl["n_samples"], lib_mean=wl["lib_mean"])
     log(f"[bench] synthetic data: {adata} in {time.time() - t0:.1f} s")
+    if wl.get("n_peaks"):
+        from nichecompass_b200.data import add_synthetic_atac
+        adata.uns["_atac"] = add_synthetic_atac(adata, wl["n_peaks"], seed=seed, lib_mean=wl["atac_lib_mean"])
+        log(f"[bench] synthetic ATAC: {adata.uns['_atac']} in {time.time() - t0:.1f} s")
     return adata
 
 
@@ -284,10 +305,12 @@ def make_trainer(adata, wl, args, store_location="device"):
     from nichecompass_b200.models import NicheCompass
     from nichecompass_b200.train import Trainer
     cov = ["batch"] if wl["n_samples"] > 1 else None
+    atac = adata.uns.get("_atac")
     with quiet():
-        model = NicheCompass(adata, n_addon_gp=wl["n_addon_gp"], cat_covariates_keys=cov, seed=args.seed)
+        model = NicheCompass(adata, adata_atac=atac, n_addon_gp=wl["n_addon_gp"], cat_covariates_keys=cov,
+                             seed=args.seed)
         dtype = torch.bfloat16 if wl["dtype"] == "bf16" else torch.float32
-        tr = Trainer(adata, model.model, cat_covariates_keys=cov, edge_batch_size=args.edge_batch_size,
+        tr = Trainer(adata, model.model, adata_atac=atac, cat_covariates_keys=cov, edge_batch_size=args.edge_batch_size,
                      seed=args.seed, monitor=False, compute_dtype=dtype, store_location=store_location)
         tr.setup_training(lr=1e-3, **LAMBDAS)
     return model, tr
@@ -506,12 +529,9 @@ def run_ours(args):
             "metric": "training cells/sec per epoch", "value": value, "unit": "cells/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
-            "config": {"workload": wl["name"], "n_cells": wl["n_cells"], "n_genes": wl["n_genes"], "k": wl["k"],
-                       "edge_batch_size": tr.edge_batch_size_, "node_batch_size": tr.node_batch_size_,
-                       "steps_per_epoch": steps_per_epoch, "global_steps_per_epoch": global_steps_per_epoch,
-                       "parallelism": f"dp{world} over the batch stream, flat-gradient NCCL all-reduce" if world > 1 else "single GPU",
-                       "l2_policy": "inputs larger than L2: every step samples a new sub-graph and reads ~65 M "
-                                    "parameters (260 MB fp32 + bf16 shadows) plus fresh activations (> 126 MB L2)"},
+            "config": config_dict(wl, tr.edge_batch_size_, tr.node_batch_size_, steps_per_epoch, world),
+            "parallelism_note": (f"dp{world} over the batch stream, flat-gradient exchange over NVLink" if world > 1
+                                 else "single GPU"),
             "clocks": clock_info, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "kernels": kernels,
         }
@@ -566,6 +586,7 @@ def cpu_reference(adata, wl, args, steps=None, warmup=1, budget_s=20.0, wall_s=N
     sample = (f"{steps} hot-loop steps (after {warmup} warm-up) of the same workload: edge batch "
               f"{args.edge_batch_size}, node batch {ld.node_batch_size}, {steps_per_epoch} steps/epoch; sampling + "
               f"dense row slicing + forward/backward/Adam, fp32, extrapolated to the epoch")
+    cpu_reference.last_shape = {"node_batch_size": int(ld.node_batch_size), "steps_per_epoch": int(steps_per_epoch)}
     return value, sec_step, (steps, warmup), cores, sample
 
 
@@ -585,8 +606,9 @@ def run_reference(args):
         "warmup_requested": args.warmup,
         "ms_per_step": sec_step * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["name"], "n_cells": wl["n_cells"], "n_genes": wl["n_genes"], "k": wl["k"],
-                   "edge_batch_size": args.edge_batch_size},
+        "config": config_dict(wl, args.edge_batch_size, cpu_reference.last_shape["node_batch_size"],
+                              cpu_reference.last_shape["steps_per_epoch"], args.gpus),
+        "parallelism_note": "rank 0 only: one process, all host threads (the reference has no data parallelism)",
         "cpu_baseline": {"value": value, "unit": "cells/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -616,7 +638,7 @@ def main():
     res, (adata, wl, tr, rank, world) = run_ours(args)
     if rank == 0 and world == 1:
         res["spmm"] = spmm_metric(tr)
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and not wl.get("n_peaks"):
         try:
             import psutil
             free_gb = psutil.virtual_memory().available / 2 ** 30

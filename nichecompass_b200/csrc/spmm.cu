@@ -296,10 +296,14 @@ k_spmm_csr_store(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict
                  const float* __restrict__ x_val, int32_t n_cols, const int32_t* __restrict__ n_id,
                  const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
                  const float* __restrict__ w, const float* __restrict__ wself, int skip_self,
-                 float* __restrict__ out, int64_t ldo) {
+                 float* __restrict__ out, int64_t ldo, int chunk) {
+    // blockIdx.y = column chunk [c0, c1) of the output row (rows wider than the shared-memory budget, e.g. the
+    // 5 k genes + 50 k peaks of the RNA + ATAC layout): column ids are sorted inside a store row, so every
+    // neighbour row is entered at lower_bound(c0) and left at the first id >= c1
     extern __shared__ float s_row[];
     const int i = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int c = tid; c < n_cols; c += STORE_T) s_row[c] = 0.f;
+    const int c0 = blockIdx.y * chunk, c1 = min(n_cols, c0 + chunk);
+    for (int c = tid; c < c1 - c0; c += STORE_T) s_row[c] = 0.f;
     __syncthreads();
     const int e0 = rowptr[i], e1 = rowptr[i + 1];
     const int total = (e1 - e0) + (wself ? 1 : 0);
@@ -316,13 +320,25 @@ k_spmm_csr_store(const int64_t* __restrict__ x_rowptr, const int32_t* __restrict
         }
         if (wt == 0.f) continue;
         const int64_t g = n_id ? (int64_t)n_id[j] : (int64_t)j;
-        const int64_t p0 = x_rowptr[g], p1 = x_rowptr[g + 1];
-        for (int64_t p = p0 + lane; p < p1; p += 32)
-            atomicAdd(&s_row[__ldg(x_col + p)], wt * __ldg(x_val + p));
+        int64_t p0 = x_rowptr[g];
+        const int64_t p1 = x_rowptr[g + 1];
+        if (c0 > 0) {                                   // first entry with column id >= c0
+            int64_t lo = p0, hi = p1;
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (__ldg(x_col + mid) < c0) lo = mid + 1; else hi = mid;
+            }
+            p0 = lo;
+        }
+        for (int64_t p = p0 + lane; p < p1; p += 32) {
+            const int c = __ldg(x_col + p);
+            if (c >= c1) break;
+            atomicAdd(&s_row[c - c0], wt * __ldg(x_val + p));
+        }
     }
     __syncthreads();
-    float* orow = out + (int64_t)i * ldo;
-    for (int c = tid; c < n_cols; c += STORE_T) orow[c] = s_row[c];
+    float* orow = out + (int64_t)i * ldo + c0;
+    for (int c = tid; c < c1 - c0; c += STORE_T) orow[c] = s_row[c];
 }
 
 extern "C" int nc_spmm_csr_store(const int64_t* x_rowptr, const int32_t* x_col, const float* x_val,
@@ -332,14 +348,15 @@ extern "C" int nc_spmm_csr_store(const int64_t* x_rowptr, const int32_t* x_col, 
                                  void* stream) {
     NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldo >= n_cols, NC_ESHAPE,
                "nc_spmm_csr_store: bad shape n_rows=%d n_cols=%d ldo=%lld", n_rows, n_cols, (long long)ldo);
-    const size_t smem = (size_t)n_cols * sizeof(float);
-    NC_REQUIRE(smem <= 200 * 1024, NC_EUNSUPPORTED,
-               "nc_spmm_csr_store: n_cols=%d needs %zu B of shared memory (> 200 KiB)", n_cols, smem);
+    constexpr int MAX_CHUNK = 200 * 1024 / (int)sizeof(float);
+    const int n_chunks = (int)nc_cdiv(n_cols, MAX_CHUNK);
+    const int chunk = (int)nc_cdiv(nc_cdiv(n_cols, n_chunks), 4) * 4;          // equal chunks, 16-byte aligned starts
+    const size_t smem = (size_t)chunk * sizeof(float);
     if (n_rows == 0) return NC_OK;
     static bool attr_set[64] = {false};
     if (int rc = nc_set_max_smem((const void*)k_spmm_csr_store, 200 * 1024, attr_set, "nc_spmm_csr_store")) return rc;
-    k_spmm_csr_store<<<n_rows, STORE_T, smem, (cudaStream_t)stream>>>(
-        x_rowptr, x_col, x_val, n_cols, n_id, rowptr, col, w, wself, skip_self, out, ldo);
+    k_spmm_csr_store<<<dim3((unsigned)n_rows, (unsigned)n_chunks), STORE_T, smem, (cudaStream_t)stream>>>(
+        x_rowptr, x_col, x_val, n_cols, n_id, rowptr, col, w, wself, skip_self, out, ldo, chunk);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_spmm_csr_store");
     return NC_OK;
@@ -379,9 +396,10 @@ extern "C" int nc_csr_gather_rows(const int64_t* x_rowptr, const int32_t* x_col,
     NC_REQUIRE(n_cols > 0 && n_rows >= 0 && ldo >= n_cols, NC_ESHAPE,
                "nc_csr_gather_rows: bad shape n_rows=%d n_cols=%d ldo=%lld", n_rows, n_cols, (long long)ldo);
     const size_t smem = (size_t)ldo * sizeof(float);
-    NC_REQUIRE(smem <= 200 * 1024, NC_EUNSUPPORTED,
-               "nc_csr_gather_rows: ldo=%lld needs %zu B of shared memory (> 200 KiB)", (long long)ldo, smem);
     if (n_rows == 0) return NC_OK;
+    if (smem > 200 * 1024)          // RNA + ATAC rows (55 k features): no staging, zero the row then scatter its non-zeros
+        return nc_csr_gather_rows_bg(x_rowptr, x_col, x_val, n_cols, n_id, n_rows, apply_log1p, out, out_dtype, ldo,
+                                     8 * nc_num_sms(), stream);
     static bool attr_f32[64] = {false}, attr_bf16[64] = {false};
     if (int rc = nc_set_max_smem((const void*)k_csr_gather_rows<float>, 200 * 1024, attr_f32, "nc_csr_gather_rows")) return rc;
     if (int rc = nc_set_max_smem((const void*)k_csr_gather_rows<__nv_bfloat16>, 200 * 1024, attr_bf16, "nc_csr_gather_rows")) return rc;

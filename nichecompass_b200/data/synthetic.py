@@ -198,3 +198,43 @@ def make_synthetic_adata_large(n_cells: int, n_genes: int, k: int, n_prior_gp: i
     tm, sm = random_gp_masks(rng, n_genes, n_prior_gp)
     add_gp_masks(adata, tm, sm)
     return adata
+
+
+def add_synthetic_atac(adata: AnnDataLite, n_peaks: int, seed: int = 0, lib_mean: float = 600., lib_sigma: float = 0.5,
+                       n_clusters: int = 8, extra_links: float = 0.2, device=None) -> AnnDataLite:
+    """Chromatin-accessibility modality for a synthetic ``adata`` (BASELINE.json config 4: RNA + ATAC): returns
+    ``adata_atac`` [n_obs, n_peaks] and writes the gene-peak mapping into ``adata.varm['nichecompass_gene_peaks']``.
+    Every peak is linked to one random gene (+ ``extra_links`` more on average); the peak masks of the gene programs
+    follow from the gene masks through that mapping, as the reference derives them
+    (utils/multimodal_mapping.py -> ``adata_atac.varm['nichecompass_ca_targets' / '_sources']``, consumed at
+    models/nichecompass.py:404-447)."""
+    rng = np.random.default_rng(seed + 7)
+    n_cells, n_genes = adata.shape
+    n_links = n_peaks + int(extra_links * n_peaks)
+    rows = np.concatenate((rng.integers(0, n_genes, n_peaks), rng.integers(0, n_genes, n_links - n_peaks)))
+    cols = np.concatenate((np.arange(n_peaks), rng.integers(0, n_peaks, n_links - n_peaks)))
+    gene_peaks = sp.csr_matrix((np.ones(n_links, dtype=np.float32), (rows, cols)), shape=(n_genes, n_peaks))
+    gene_peaks.data[:] = 1.
+    adata.varm["nichecompass_gene_peaks"] = gene_peaks.astype(bool)
+    coords = adata.obsm["spatial"]
+    local = coords - np.floor(coords / 2.0) * 2.0
+    cluster = ((np.minimum((local[:, 0] * 4).astype(int), 3)
+                + 4 * np.minimum((local[:, 1] * 2).astype(int), 1)) % n_clusters).astype(np.int64)
+    logits = rng.normal(0., 1.5, size=(n_clusters, n_peaks))
+    prof = np.exp(logits - logits.max(1, keepdims=True))
+    prof /= prof.sum(1, keepdims=True)
+    lib = np.maximum(rng.lognormal(np.log(lib_mean), lib_sigma, n_cells), 1.0)
+    x = _poisson_counts_chunked(rng, n_cells, n_peaks, cluster, prof, lib, device, chunk=4096)
+    atac = AnnDataLite(x, obs=adata.obs.copy(),
+                       var=pd.DataFrame(index=[f"peak{i}" for i in range(n_peaks)]))
+    atac.layers["counts"] = x
+    gpt = gene_peaks.T.tocsr().astype(np.float32)                                  # [n_peaks, n_genes]
+    for name, key in (("targets", "nichecompass_gp_targets"), ("sources", "nichecompass_gp_sources")):
+        gene_mask = sp.csr_matrix(np.asarray(adata.varm[key], dtype=np.float32))   # [n_genes, P]
+        atac.varm[f"nichecompass_ca_{name}"] = (gpt @ gene_mask).astype(bool).tocsr()   # [n_peaks, P]
+    t_idx = np.nonzero(np.asarray(atac.varm["nichecompass_ca_targets"].sum(1)).reshape(-1))[0]
+    s_idx = np.nonzero(np.asarray(atac.varm["nichecompass_ca_sources"].sum(1)).reshape(-1))[0]
+    atac.uns["nichecompass_target_peaks_idx"] = t_idx
+    atac.uns["nichecompass_source_peaks_idx"] = s_idx
+    atac.uns["nichecompass_peaks_idx"] = np.concatenate((t_idx, s_idx + n_peaks))
+    return atac

@@ -404,6 +404,10 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
             if self.training:
                 mu_d = self.mu.detach()
                 call("nc_abs_mean_ema", mu_d, mu_d.stride(0), mu_d.size(0), P, 0.1, self.running_mean_abs_mu)
+                if getattr(self, "_dp_sync_ema", False):
+                    # data-parallel training (train/trainer.py of this build): every rank saw a different node batch
+                    import torch.distributed as dist
+                    dist.all_reduce(self.running_mean_abs_mu, op=dist.ReduceOp.AVG)
             if use_only_active_gps:
                 # all on the device, no host sync (the reference's boolean-mask assignments sync)
                 self.running_mean_abs_mu.mul_(active)

@@ -30,7 +30,7 @@ import torch.nn as nn
 
 from ..data import initialize_dataloaders, prepare_data
 from .basetrainermixin import BaseTrainerMixin
-from .metrics import eval_metrics
+from .metrics import eval_metrics, eval_metrics_device
 from .optim import FlatAdam
 from .utils import EarlyStopping, _cycle_iterable, print_progress
 
@@ -206,6 +206,9 @@ class Trainer(BaseTrainerMixin):
             if ld is not None:
                 ld.set_pipeline(self.pipeline_sampler_)
         self._side_streams = ([torch.cuda.Stream(), torch.cuda.Stream()] if self.prefetch_ else [None, None])
+        # data parallelism: the module averages the |mu| EMA over the ranks right after updating it, so that the edge
+        # forward of the same iteration already derives its active-GP mask from the value every rank shares
+        self.model._dp_sync_ema = self.world_size_ > 1
 
     # ------------------------------------------------------------------ one iteration
     def _loss_kwargs(self):
@@ -240,8 +243,7 @@ class Trainer(BaseTrainerMixin):
         self.optimizer.zero_grad()
         loss_dict["optim_loss"].backward()
         if self.world_size_ > 1:
-            self.optimizer.all_reduce_grads()
-            self._sync_running_stats()
+            self.optimizer.all_reduce_grads()            # (the |mu| EMA was averaged inside the node forward)
         hook = getattr(self, "after_backward", None)
         if hook is not None:                 # parity tests: the gradients live in the arena until the Adam kernel clears them
             hook(self, node_out, edge_out)
@@ -438,16 +440,17 @@ class Trainer(BaseTrainerMixin):
         return {"probs": [], "labels": [], "same": [[] for _ in range(self.n_cat_covariates)], "incl": []}
 
     @staticmethod
-    def _cat_np(ts):
-        return torch.cat(ts).cpu().numpy() if len(ts) > 0 else None
+    def _cat(ts):
+        return torch.cat(ts) if len(ts) > 0 else None
 
     def _edge_metrics(self, store: dict, omics_pred_dict: Optional[dict] = None) -> dict:
-        incl = self._cat_np(store["incl"])
-        same = [self._cat_np(s) for s in store["same"]] if incl is not None else None
-        return eval_metrics(edge_recon_probs=self._cat_np(store["probs"]),
-                            edge_labels=self._cat_np(store["labels"]),
-                            edge_same_cat_covariates_cat=same, edge_incl=incl,
-                            omics_pred_dict=omics_pred_dict)
+        """AUROC / AUPRC / threshold sweeps on the device (``train/metrics.py: eval_metrics_device``): the edge
+        probabilities never leave HBM, one read-back of the finished scalars."""
+        incl = self._cat(store["incl"])
+        same = [self._cat(s) for s in store["same"]] if incl is not None else None
+        return eval_metrics_device(edge_recon_probs=self._cat(store["probs"]), edge_labels=self._cat(store["labels"]),
+                                   edge_same_cat_covariates_cat=same, edge_incl=incl,
+                                   omics_pred_dict=omics_pred_dict)
 
     @torch.no_grad()
     def eval_epoch(self, acc: Optional[dict] = None):
@@ -455,11 +458,15 @@ class Trainer(BaseTrainerMixin):
         acc = {} if acc is None else acc
         self.model.eval()
         store = self._edge_store()
+        joint = getattr(self.model, "joint_supported", None)
         for edge_batch, node_batch in self.joint_batches(self.edge_val_loader, self.node_val_loader):
-            node_out = self.model(data_batch=node_batch.to(self.device), decoder="omics",
-                                  use_only_active_gps=self.use_only_active_gps)
-            edge_out = self.model(data_batch=edge_batch.to(self.device), decoder="graph",
-                                  use_only_active_gps=self.use_only_active_gps)
+            if self.joint_encoder_ and joint is not None and joint(node_batch, edge_batch):
+                node_out, edge_out = self.model.forward_joint(node_batch, edge_batch, self.use_only_active_gps)
+            else:
+                node_out = self.model(data_batch=node_batch.to(self.device), decoder="omics",
+                                      use_only_active_gps=self.use_only_active_gps)
+                edge_out = self.model(data_batch=edge_batch.to(self.device), decoder="graph",
+                                      use_only_active_gps=self.use_only_active_gps)
             loss_dict = self.model.loss(edge_model_output=edge_out, node_model_output=node_out,
                                         **self._loss_kwargs(), edge_recon_active=True)
             self._accumulate(acc, "val", loss_dict)
@@ -491,7 +498,7 @@ class Trainer(BaseTrainerMixin):
                     for ent in ("target", "source"):
                         preds[f"{ent}_{mod}_preds"].append(node_out[f"{ent}_{mod}_nb_means"].reshape(-1))
                         preds[f"{ent}_{mod}"].append(node_out["node_labels"][f"{ent}_{mod}"].reshape(-1))
-        omics = {k: torch.cat(v).cpu().numpy() for k, v in preds.items()} if preds else None
+        omics = {k: torch.cat(v) for k, v in preds.items()} if preds else None
         self.model.materialize_outputs = prev
         val_eval_dict = self._edge_metrics(store, omics)
         self.val_eval_dict_ = val_eval_dict
@@ -516,6 +523,14 @@ class Trainer(BaseTrainerMixin):
         answer whether to stop."""
         metric = self.early_stopping.early_stopping_metric
         current = self.epoch_logs[metric][-1]
+        if self.world_size_ > 1:
+            # validation is replicated per rank and may differ in the last ulp (float atomics): every rank acts on
+            # rank 0's value, so stop / reduce-lr / best-state decisions cannot diverge (a rank that stops alone
+            # would leave the others in the gradient exchange forever)
+            import torch.distributed as dist
+            t = torch.tensor([float(current)], dtype=torch.float64, device=self.device)
+            dist.broadcast(t, src=0)
+            current = float(t.item())
         if self.early_stopping.update_state(current):
             self.best_model_state_dict = copy.deepcopy(self.model.state_dict())
             self.best_epoch = self.epoch

@@ -107,6 +107,28 @@ class TrainerRef:
         adam_step(self.p, self.keys, self.state, self.lr, self.weight_decay, clip_value=self.clip)
         return {k: float(v.detach()) for k, v in L.items()}
 
+    @torch.no_grad()
+    def eval_epoch(self, edge_val_loader, node_val_loader):
+        """train/trainer.py:492-589: evaluation mode (z = mu), every (edge, cycled node) validation pair through
+        both forwards and the loss with ``edge_recon_active=True``.  Returns (mean of every loss term over the
+        validation iterations, edge probabilities, edge labels) -- the inputs of train/metrics.py:eval_metrics."""
+        only_active = not (self.epoch < self.n_epochs_all_gps)
+        was = self.model.training
+        self.model.training = False
+        sums, n = {}, 0
+        probs, labels = [], []
+        for edge_batch, node_batch in zip(edge_val_loader, R.cycle_iterable(node_val_loader)):
+            node_out = self.model.forward(node_batch, "omics", use_only_active_gps=only_active)
+            edge_out = self.model.forward(edge_batch, "graph", use_only_active_gps=only_active)
+            L = self.model.loss(edge_out, node_out, edge_recon_active=True, **self.loss_kwargs)
+            for k, v in L.items():
+                sums[k] = sums.get(k, 0.0) + float(v)
+            n += 1
+            probs.append(torch.sigmoid(edge_out["edge_recon_logits"]))
+            labels.append(edge_out["edge_recon_labels"])
+        self.model.training = was
+        return {k: v / max(n, 1) for k, v in sums.items()}, torch.cat(probs), torch.cat(labels)
+
     def run(self, max_iters: Optional[int] = None) -> List[dict]:
         """One epoch (or ``max_iters`` iterations) of zip(edge loader, cycled node loader)."""
         logs = []
@@ -134,7 +156,16 @@ def build_loaders(x, adj_csr, edge_batch_size: int, node_batch_size: Optional[in
                                   cat_covariates_cats=cat_covariates_cats)
     edge_loader = R.LinkLoaderRef(x, splits["train"].edge_index, n, splits["train"].edge_label_index,
                                   edge_batch_size, num_neighbors, cat_covariates_cats=cat_covariates_cats)
-    return SimpleNamespace(edge_loader=edge_loader, node_loader=node_loader, node_batch_size=node_batch_size,
+    # validation loaders (data/dataloaders.py:71-101): the validation nodes over the full graph, the validation
+    # edges over the TRAINING message-passing graph
+    node_val_loader = R.NodeLoaderRef(x, ei, n, val_mask, node_batch_size, num_neighbors,
+                                      cat_covariates_cats=cat_covariates_cats) if int(val_mask.sum()) > 0 else None
+    edge_val_loader = None
+    if "val" in splits and splits["val"].edge_label_index.size(1) > 0:
+        edge_val_loader = R.LinkLoaderRef(x, splits["val"].edge_index, n, splits["val"].edge_label_index,
+                                          edge_batch_size, num_neighbors, cat_covariates_cats=cat_covariates_cats)
+    return SimpleNamespace(edge_val_loader=edge_val_loader, node_val_loader=node_val_loader,
+                           edge_loader=edge_loader, node_loader=node_loader, node_batch_size=node_batch_size,
                            n_edges_train=n_edges_train, n_nodes_train=int(train_mask.sum()),
                            splits=splits, train_mask=train_mask, val_mask=val_mask, edge_index=ei)
 

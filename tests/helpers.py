@@ -117,3 +117,26 @@ def multimodal_covariate_problem(n_cells=140, n_genes=36, n_peaks=52, n_prior_gp
         both = sorted(set(fd["target_masked_atac_idx"]) | {i + n_peaks for i in fd["source_masked_atac_idx"]})
         fd["masked_atac_idx"] = both
     return adata, cfg, x, cats
+
+
+def oracle_cfg_multimodal(adata, atac, n_addon_gp=3, **extra):
+    """Oracle configuration of an RNA + ATAC problem built by ``add_synthetic_atac`` (the masks the reference
+    reads at models/nichecompass.py:404-447, densified)."""
+    import scipy.sparse as sp
+    n_genes, n_peaks = adata.n_vars, atac.n_vars
+    gpm = torch.from_numpy(np.asarray(sp.csr_matrix(adata.varm["nichecompass_gene_peaks"]).astype(bool).todense()))
+    tam = torch.from_numpy(np.asarray(sp.csr_matrix(atac.varm["nichecompass_ca_targets"]).astype(bool).todense()).T.copy())
+    sam = torch.from_numpy(np.asarray(sp.csr_matrix(atac.varm["nichecompass_ca_sources"]).astype(bool).todense()).T.copy())
+    cfg = oracle_cfg_from_adata(adata, n_addon_gp=n_addon_gp, n_input=n_genes + n_peaks, n_output_peaks=n_peaks,
+                                gene_peaks_mask=gpm, target_atac_mask=tam, source_atac_mask=sam, **extra)
+    cfg["n_hidden"] = min(n_genes, cfg["n_prior_gp"] + n_addon_gp)
+    fd = cfg["features_idx_dict"]
+    keep = np.ones(n_peaks, dtype=bool)
+    for ent in ("target", "source"):
+        masked = [int(i) for i in atac.uns[f"nichecompass_{ent}_peaks_idx"]]
+        k = keep.copy()
+        k[masked] = False
+        fd[f"{ent}_masked_atac_idx"] = masked
+        fd[f"{ent}_unmasked_atac_idx"] = np.nonzero(k)[0].tolist()
+    fd["masked_atac_idx"] = [int(i) for i in atac.uns["nichecompass_peaks_idx"]]
+    return cfg

@@ -261,3 +261,37 @@ def test_cat_covariates_contrastive_loss_matches_oracle():
     out.backward()
     assert H.rel_err(out, ref) < 1e-5
     assert H.rel_err(lc.grad, lo.grad) < 1e-5
+
+
+def test_store_kernels_on_rows_wider_than_shared_memory():
+    """RNA + ATAC layout of config 4 (5 k genes + 50 k peaks = 55 k columns > the 51 200 floats a CTA can stage):
+    the gather takes the zero-then-scatter kernel, the label aggregation runs in column chunks."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(3)
+    n, F = 400, 55_003
+    x = sp.random(n, F, density=0.004, format="csr", random_state=7, dtype=np.float32)
+    x.data = np.ceil(x.data * 5).astype(np.float32)
+    store = CSRFeatureStore.from_scipy(x, DEV)
+    n_id = torch.from_numpy(rng.permutation(n)[:96].astype(np.int32)).to(DEV)
+    dense = torch.from_numpy(np.asarray(x.todense())).to(DEV)
+    ld = ops.pad8(F)
+    got = ops.csr_gather_rows(store, n_id, 96, False, torch.float32, ld)
+    assert torch.equal(got[:, :F], dense[n_id.long()]) and float(got[:, F:].abs().max()) == 0.0
+    gotb = ops.csr_gather_rows(store, n_id, 96, True, torch.bfloat16, ld)
+    assert H.rel_err(gotb[:, :F].float(), torch.log1p(dense[n_id.long()])) < 4e-3
+    # aggregation over a random local graph of the 96 gathered cells
+    g = torch.Generator().manual_seed(0)
+    deg = torch.randint(1, 7, (32,), generator=g)
+    rowptr = torch.zeros(33, dtype=torch.int32)
+    rowptr[1:] = torch.cumsum(deg, 0)
+    col = torch.randint(0, 96, (int(rowptr[-1]),), generator=g).to(torch.int32)
+    w = torch.rand(col.numel(), generator=g)
+    wself = torch.rand(32, generator=g)
+    out = ops.spmm_csr_store(store, n_id, rowptr.to(DEV), col.to(DEV), w.to(DEV), wself.to(DEV), False, 32)
+    xs = dense[n_id.long()].double().cpu()
+    ref = torch.zeros(32, F, dtype=torch.float64)
+    for i in range(32):
+        for e in range(int(rowptr[i]), int(rowptr[i + 1])):
+            ref[i] += float(w[e]) * xs[int(col[e])]
+        ref[i] += float(wself[i]) * xs[i]
+    assert H.rel_err(out, ref) < 1e-6

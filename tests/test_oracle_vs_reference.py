@@ -438,3 +438,32 @@ def test_encoder_state_dict_keys_and_shapes_match_reference(conv_layer, n_fc, n_
     assert list(ours.keys()) == list(theirs.keys())
     for k, v in theirs.items():
         assert ours[k].shape == v.shape and ours[k].dtype == v.dtype, k
+
+
+def test_load_and_expand_state_dict_matches_reference():
+    """modules/basemodulemixin.py:50-95 (the unmodified reference mixin) against nichecompass_b200's on a module
+    that grew a covariate category (embedding rows) and add-on gene programs (weight columns, mask columns)."""
+    import torch.nn as nn
+    from nichecompass_b200.modules.basemodulemixin import BaseModuleMixin as Ours
+    ref = load_reference()
+    Theirs = ref.modules.basemodulemixin.BaseModuleMixin
+
+    def make(mixin, n_cat, n_addon, seed):
+        class M(nn.Module, mixin):
+            def __init__(self):
+                super().__init__()
+                torch.manual_seed(seed)
+                self.embedder = nn.Embedding(n_cat, 3)
+                self.addon_l = nn.Linear(n_addon, 5, bias=False)          # weight [5, n_addon]: grows along dim 1
+                self.conv = nn.Linear(4, 2 * (6 + n_addon))               # weight + bias grow along dim 0
+                self.register_buffer("mask", torch.ones(5, n_addon))
+                self.extra = nn.Parameter(torch.randn(2))
+        return M()
+    small = make(Ours, 2, 3, seed=0).state_dict()
+    a, b = make(Ours, 3, 5, seed=1), make(Theirs, 3, 5, seed=1)
+    a.load_and_expand_state_dict({k: v.clone() for k, v in small.items()})
+    b.load_and_expand_state_dict({k: v.clone() for k, v in small.items()})
+    for (ka, va), (kb, vb) in zip(a.state_dict().items(), b.state_dict().items()):
+        assert ka == kb and torch.equal(va, vb), ka
+    assert torch.equal(a.state_dict()["embedder.weight"][:2], small["embedder.weight"])
+    assert torch.equal(a.state_dict()["addon_l.weight"][:, :3], small["addon_l.weight"])

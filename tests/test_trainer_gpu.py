@@ -253,3 +253,88 @@ def test_pipelined_sampler_yields_the_same_batches():
             assert torch.equal(x[0], y[0]) and torch.equal(x[1], y[1]) and torch.equal(x[2], y[2])
             assert x[3] == y[3] and x[4] == y[4]
             assert (x[5] is None and y[5] is None) or torch.equal(x[5], y[5])
+
+
+def test_rna_atac_training_iterations_on_rows_wider_than_shared_memory():
+    """Config-4 layout through the product path: RNA ++ ATAC count store with 52 060 columns (wider than one CTA
+    can stage: the gather takes the scatter kernel, the label aggregation runs in column chunks), both pairs of
+    masked decoders, two full training iterations against the CPU loop (losses incl. chrom_access_recon_loss)."""
+    from nichecompass_b200.data import add_synthetic_atac, make_synthetic_adata_large
+    from nichecompass_b200.models import NicheCompass
+    from nichecompass_b200.train import Trainer
+    adata = make_synthetic_adata_large(360, 60, 5, 12, seed=0, lib_mean=120.)
+    atac = add_synthetic_atac(adata, 52_000, seed=0, lib_mean=400.)
+    cfg = H.oracle_cfg_multimodal(adata, atac, n_addon_gp=3)
+    p32 = init_params(cfg, seed=5)
+    lam = dict(LAM, lambda_chrom_access_recon=100.)
+    # CPU loop on the dense [N, F + Fp] matrix
+    torch.manual_seed(0)
+    x = torch.cat((H.dense_x(adata, torch.float64), torch.tensor(np.asarray(atac.X.todense()), dtype=torch.float64)), 1)
+    p64 = {k: v.double().clone() for k, v in p32.items()}
+    ld = TR.build_loaders(x, adata.obsp["spatial_connectivities"], 24)
+    ref = TR.TrainerRef(cfg, p64, ld.edge_loader, ld.node_loader, lr=1e-3, loss_kwargs=lam)
+    ref_logs = ref.run(max_iters=2)
+    assert "chrom_access_recon_loss" in ref_logs[0]
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = NicheCompass(adata, adata_atac=atac, n_addon_gp=3, active_gp_thresh_ratio=0.01)
+        missing = model.model.load_state_dict({k: v.float() for k, v in p32.items()}, strict=True)
+        tr = Trainer(adata, model.model, adata_atac=atac, edge_batch_size=24, seed=0, monitor=False,
+                     compute_dtype=torch.float32, pipeline_sampler=False)
+        tr.setup_training(lr=1e-3, **lam)
+    assert tr.node_masked_data.store.n_cols == 52_060
+    tr.model._eps_queue = [e.clone() for e in ref.noise_log]
+    logs = []
+    for i, (eb, nb) in enumerate(tr.joint_batches(tr.edge_train_loader, tr.node_train_loader)):
+        logs.append({k: float(v.detach()) for k, v in tr.train_iteration(eb, nb).items()})
+        if i + 1 == 2:
+            break
+    for it, (a, b) in enumerate(zip(logs, ref_logs)):
+        assert set(a) == set(b)
+        for k in b:
+            assert abs(a[k] - b[k]) <= 2e-5 * abs(b[k]) * (1 + it) + 1e-12, (it, k, a[k], b[k])
+
+
+def test_query_fine_tuning_with_a_new_covariate_category(tmp_path):
+    """BASELINE.json config 5, second half (reference mapping): a model trained on samples 0 / 1 is loaded on a
+    query dataset that brings a third sample; ``load`` grows the covariate embedder through
+    ``load_and_expand_state_dict`` (models/basemodelmixin.py:144-303, modules/basemodulemixin.py:50-95), freezes
+    everything and unfreezes the embedder; fine-tuning then moves the embedder only."""
+    from nichecompass_b200.models import NicheCompass
+    ref_adata = H.tiny_problem(n_cells=300, n_genes=48, n_prior_gp=12, lib_mean=80., n_samples=2)
+    kw = dict(cat_covariates_keys=["batch"], cat_covariates_embeds_injection=["encoder", "gene_expr_decoder"],
+              cat_covariates_embeds_nums=[3], cat_covariates_no_edges=[True])
+    with contextlib.redirect_stdout(io.StringIO()):
+        model = NicheCompass(ref_adata, n_addon_gp=4, active_gp_thresh_ratio=0.01, **kw)
+        model.train(n_epochs=2, n_epochs_all_gps=1, edge_batch_size=64, verbose=False)
+    d = os.path.join(tmp_path, "reference_model")
+    model.save(d, overwrite=True)
+    old = {k: v.detach().cpu().clone() for k, v in model.model.state_dict().items()}
+    assert old["cat_covariate0_embedder.weight"].shape == (2, 3)
+
+    query = H.tiny_problem(n_cells=240, n_genes=48, n_prior_gp=12, lib_mean=80., n_samples=3, seed=1)
+    for store in ("varm", "uns"):                       # same genes, same gene programs as the reference model
+        for k, v in getattr(ref_adata, store).items():
+            if k.startswith("nichecompass_") and "latent" not in k and "active" not in k:
+                getattr(query, store)[k] = v
+    assert sorted(query.obs["batch"].unique().tolist()) == ["sample0", "sample1", "sample2"]
+    with contextlib.redirect_stdout(io.StringIO()):
+        loaded = NicheCompass.load(d, adata=query, use_cuda=True, unfreeze_cat_covariates_embedder_weights=True)
+    new = {k: v.detach().cpu().clone() for k, v in loaded.model.state_dict().items()}
+    assert loaded.cat_covariates_cats_ == [["sample0", "sample1", "sample2"]]
+    assert new["cat_covariate0_embedder.weight"].shape == (3, 3)
+    assert torch.equal(new["cat_covariate0_embedder.weight"][:2], old["cat_covariate0_embedder.weight"])
+    for k, v in old.items():
+        if k != "cat_covariate0_embedder.weight":
+            assert torch.equal(new[k], v), k
+    flags = {n: p.requires_grad for n, p in loaded.model.named_parameters()}
+    assert [n for n, f in flags.items() if f] == ["cat_covariate0_embedder.weight"]
+    with contextlib.redirect_stdout(io.StringIO()):
+        loaded.train(n_epochs=2, n_epochs_all_gps=0, edge_batch_size=64, verbose=False)
+    tuned = {k: v.detach().cpu() for k, v in loaded.model.state_dict().items()}
+    for k, v in new.items():
+        if k == "cat_covariate0_embedder.weight":
+            assert not torch.equal(tuned[k][2], v[2])               # the new sample's embedding learned something
+        elif "running_mean_abs_mu" not in k:
+            assert torch.equal(tuned[k], v), k                      # frozen
+    lat = loaded.get_latent_representation(adata=query, cat_covariates_keys=["batch"], only_active_gps=False)
+    assert lat.shape == (240, 16) and np.isfinite(lat).all()
