@@ -129,6 +129,31 @@ def build_adata(wl: dict, seed: int):
     return adata
 
 
+def build_adata_shared(wl: dict, seed: int, rank: int, world: int):
+    """N > 1 ranks on one box: rank 0 draws the synthetic dataset once and hands it to the other ranks through
+    /dev/shm (8 ranks drawing 4 M cells each would need ~3x the dataset per rank in host memory at the same time)."""
+    if world == 1:
+        return build_adata(wl, seed)
+    import pickle
+    import torch.distributed as dist
+    path = f"/dev/shm/nc_bench_{os.getuid()}_{wl['n_cells']}_{wl['n_genes']}_{wl.get('n_peaks', 0)}_{seed}.pkl"
+    adata = None
+    if rank == 0:
+        adata = build_adata(wl, seed)
+        with open(path + ".tmp", "wb") as fh:
+            pickle.dump(adata, fh, protocol=5)
+        os.replace(path + ".tmp", path)
+    dist.barrier()
+    if rank != 0:
+        with open(path, "rb") as fh:
+            adata = pickle.load(fh)
+    dist.barrier()
+    if rank == 0:
+        with contextlib.suppress(OSError):
+            os.remove(path)
+    return adata
+
+
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
@@ -451,7 +476,7 @@ def run_ours(args):
     wl = dict(WORKLOADS[args.workload])
     if args.cells:
         wl["n_cells"] = args.cells
-    adata = build_adata(wl, args.seed)
+    adata = build_adata_shared(wl, args.seed, rank, world)
     model, tr = make_trainer(adata, wl, args)
     steps_per_epoch = tr.edge_train_loader.n_batches_total
     global_steps_per_epoch = math.ceil(steps_per_epoch / world)

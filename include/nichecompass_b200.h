@@ -40,6 +40,8 @@ const char* nc_last_error(void);
 int nc_version(void);
 /* number of kernels launched by this library in this process so far (bench.py gpu_launches) */
 int64_t nc_launch_count(void);
+/* adds the launches of a replayed CUDA graph (the caller counted them at capture time); returns the new total */
+int64_t nc_launch_count_add(int64_t n);
 
 /* Page-locked, device-mapped host memory for a count store that stays in host memory
  * (data/store.py, location="host"; the reference keeps the dense count tensor in pageable host memory and
@@ -297,6 +299,12 @@ int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t P, float l
 int nc_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
                  float beta2, float eps, float weight_decay, int32_t step, float clip_value,
                  void* p_bf16, int zero_grad, void* stream);
+/* The same update with {lr, step} read from device memory (dyn[0], dyn[1]; step >= 1 = the number of this
+ * update) and the step advanced on the device afterwards: no launch argument depends on host state, so the
+ * launch can be replayed from a captured CUDA graph.                                                      */
+int nc_adam_step_dyn(float* p, float* g, float* m, float* v, int64_t n, float* dyn, float beta1,
+                     float beta2, float eps, float weight_decay, float clip_value, void* p_bf16,
+                     int zero_grad, void* stream);
 /* fp32 [R, C] (lds) -> bf16 dst [R, fill_cols] (row pitch ldd; columns [C, fill_cols) zeroed;
  * fill_cols <= 0 means ldd), optionally multiplied by `mask` (nn/layercomponents.py:77-80:
  * weight * mask before the contraction).                                                    */
@@ -329,6 +337,15 @@ int nc_merge_subgraphs(const int32_t* a_rowptr, const int32_t* a_col, const int3
                        int32_t a_seed, int32_t a_sub, const int32_t* b_rowptr, const int32_t* b_col,
                        const int32_t* b_nid, int32_t b_seed, int32_t b_sub, int32_t* m_rowptr,
                        int32_t* m_col, int32_t* m_nid, void* stream);
+/* The same merge into PADDED buffers (size buckets of the CUDA-graph training step): b_seed_pad >= b_seed merged
+ * edge seeds, n_sub_pad nodes, e_pad entries; merged node order = [a seeds | b seeds | pad seeds | a others |
+ * b others | pad others]; pad seeds have empty rows, pad nodes repeat a real node id and are referenced by no
+ * edge.  m_rowptr[a_seed + b_seed_pad + 1], m_col[e_pad], m_nid[n_sub_pad].                                */
+int nc_merge_subgraphs_padded(const int32_t* a_rowptr, const int32_t* a_col, const int32_t* a_nid,
+                              int32_t a_seed, int32_t a_sub, const int32_t* b_rowptr, const int32_t* b_col,
+                              const int32_t* b_nid, int32_t b_seed, int32_t b_sub, int32_t b_seed_pad,
+                              int32_t n_sub_pad, int32_t e_pad, int32_t* m_rowptr, int32_t* m_col,
+                              int32_t* m_nid, void* stream);
 /* torch.unique(ids, return_inverse=True) for the link-batch seeds (sorted ascending), n <= 16384. */
 int nc_unique_sorted_i32(const int32_t* ids, int32_t n, int32_t* uniq, int32_t* inverse,
                          int32_t* n_unique, void* stream);
@@ -344,6 +361,32 @@ int nc_relu_bwd(const float* dh, int64_t lddh, const void* h, int dtype, int64_t
  * layers of the 2-layer encoder (nn/encoders.py:191-194, ``hidden = activation(conv_l1(hidden))``).   */
 int nc_relu_cast(const float* x, int64_t ldx, int32_t R, int32_t C, void* out, int dtype, int64_t ldo,
                  void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Data-parallel training over NVLink peer memory (one process per GPU on one NVSwitch box).
+ * The reference has no data parallelism (docs/installation.md:3-5); its optimiser step is
+ * torch.optim.Adam.step() after loss.backward() (train/trainer.py:414-421).  nc_dp_adam_step replaces
+ * ncclAllReduce(gradients) + nc_adam_step by ONE kernel: reduce-scatter of the gradient arenas through
+ * peer loads, Adam on the owned shard, all-gather of the new parameters (+ bf16 shadow) and clearing of
+ * the gradients through peer stores, cross-GPU barriers on flags in peer memory.
+ * nc_peer_*: device memory that other processes on the box can map (cudaIpc); synchronous, no stream.
+ * ---------------------------------------------------------------------------------------- */
+int nc_peer_alloc(int64_t bytes, void** out_dev);
+int nc_peer_free(void* dev);
+int nc_peer_get_handle(void* dev, void* handle_host);          /* handle_host: 64 bytes */
+int nc_peer_open(const void* handle_host, void** out_dev);
+int nc_peer_close(void* dev);
+/* *_ptrs_host: `world` device pointers each (entry `rank`: own buffer; others: nc_peer_open mappings);
+ * shadow_ptrs_host NULL in fp32 mode; flag buffers: 2 * world uint32 each, zero-initialised; m, v: the
+ * moments of this rank's shard only (ceil(numel / world / 4) * 4 floats); done_counter: one zeroed uint32.
+ * Every rank calls with the same `step` sequence (1, 2, ...): it is the bias-correction step AND the
+ * barrier epoch.  dyn != NULL: {lr, step} are read from device memory instead (and the step advanced by the
+ * kernel), so that the launch can be replayed from a CUDA graph.  n_ctas <= 0: 64.                                                                     */
+int nc_dp_adam_step(void* const* p_ptrs_host, void* const* g_ptrs_host, void* const* shadow_ptrs_host,
+                    void* const* flag_ptrs_host, float* m, float* v, int64_t numel, int32_t rank,
+                    int32_t world, float lr, float beta1, float beta2, float eps, float weight_decay,
+                    int32_t step, float clip_value, uint32_t* done_counter, int32_t n_ctas, float* dyn,
+                    void* stream);
 
 #ifdef __cplusplus
 }

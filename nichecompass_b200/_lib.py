@@ -49,9 +49,10 @@ def _parse_header(path: str) -> dict:
 
 
 # entry points that return a value instead of a status code (bound separately in ``_load``)
-VALUE_FUNCS = ("nc_last_error", "nc_version", "nc_launch_count", "nc_gatv2_bwd_ws_bytes")
+VALUE_FUNCS = ("nc_last_error", "nc_version", "nc_launch_count", "nc_launch_count_add", "nc_gatv2_bwd_ws_bytes")
 # synchronous host-side entry points (no stream argument; called through ``lib()`` directly, not ``call``)
-HOST_FUNCS = ("nc_host_alloc", "nc_host_free")
+HOST_FUNCS = ("nc_host_alloc", "nc_host_free", "nc_peer_alloc", "nc_peer_free", "nc_peer_get_handle", "nc_peer_open",
+              "nc_peer_close")
 SIGNATURES = {k: v for k, v in _parse_header(HEADER_PATH).items() if k not in VALUE_FUNCS}
 
 _lib = None
@@ -78,6 +79,8 @@ def _load():
     lib.nc_last_error.restype = ctypes.c_char_p
     lib.nc_version.restype = ctypes.c_int
     lib.nc_launch_count.restype = ctypes.c_int64
+    lib.nc_launch_count_add.restype = ctypes.c_int64
+    lib.nc_launch_count_add.argtypes = [ctypes.c_int64]
     lib.nc_gatv2_bwd_ws_bytes.restype = ctypes.c_int64
     lib.nc_gatv2_bwd_ws_bytes.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int32, ctypes.c_int32]
     for name, sig in SIGNATURES.items():

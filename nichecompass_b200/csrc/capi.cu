@@ -20,6 +20,8 @@ void nc_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed)
 extern "C" const char* nc_last_error(void) { return g_err; }
 extern "C" int nc_version(void) { return 100; }
 extern "C" int64_t nc_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+// launches replayed from a captured CUDA graph (counted by the caller at capture time)
+extern "C" int64_t nc_launch_count_add(int64_t n) { return g_launches.fetch_add(n, std::memory_order_relaxed) + n; }
 
 // ---------------------------------------------------------------------------- pinned host blocks
 // Host-resident count store (data/store.py, location="host"): page-locked, device-mapped memory owned by the

@@ -1,0 +1,225 @@
+// Data-parallel gradient exchange fused with the optimiser step, over NVLink peer memory.
+//
+// The reference has no data parallelism (docs/installation.md:3-5); its optimiser step is
+// torch.optim.Adam.step() after loss.backward() (train/trainer.py:414-421).  Here, with W ranks on one NVSwitch
+// box, every rank keeps the parameter arena, the gradient arena and the bf16 shadow (train/optim.py FlatAdam) in
+// memory that its peers have mapped (cudaIpc), and ONE kernel per step does what ncclAllReduce + k_adam did:
+//
+//   start barrier   every rank tells every peer "my gradients of step e are final" (a flag in the peer's memory)
+//   reduce-scatter  rank r reads shard r of the gradient arena of all W ranks through NVLink (128-bit loads,
+//                   coalesced, W independent streams in flight per thread) and averages them
+//   Adam            on its shard of p / m / v (the moments exist only where they are used)
+//   all-gather      the new fp32 parameters and their bf16 shadow are STORED into all W ranks' arenas, and shard
+//                   r of every rank's gradient arena is cleared for the next backward pass
+//   end barrier     a rank's kernel ends only when every peer has finished writing into its arenas
+//
+// No shared memory and a few dozen CTAs: the kernel can run beside persistent GEMM CTAs that own every SM's
+// shared memory (the reason NCCL's copy kernels could not be overlapped), and the transfers
+// are bound by the NVLink ports, not by SM count.  Per rank and step: 4 N bytes read and 10 N bytes written over
+// the links (N = parameters) against 8 N + 8 N for a ring all-reduce followed by a separate 34 N-byte Adam pass.
+#include <math.h>
+
+#include "common.cuh"
+
+extern void nc_count_launch(int n);
+
+namespace {
+constexpr int DP_MAX_WORLD = 16;
+
+struct DpPeers {
+    float* p[DP_MAX_WORLD];
+    float* g[DP_MAX_WORLD];
+    __nv_bfloat16* sh[DP_MAX_WORLD];     // may be all NULL (fp32 mode)
+    uint32_t* flags[DP_MAX_WORLD];       // [2 * world] per rank: [0, W) start flags, [W, 2W) end flags
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_peer4(const float* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float adam1(float pi, float gi, float& mi, float& vi, float lr_bc1, float b1, float b2,
+                                       float eps, float wd, float bc2_sqrt, float clip) {
+    if (clip > 0.f) gi = fminf(fmaxf(gi, -clip), clip);
+    if (wd != 0.f) gi += wd * pi;
+    mi = b1 * mi + (1.f - b1) * gi;
+    vi = b2 * vi + (1.f - b2) * gi * gi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    return pi - lr_bc1 * (mi / denom);
+}
+
+// Waits until flags[lo + k] >= epoch for every k < W (epochs only grow; wrap-around after 4e9 steps).
+__device__ __forceinline__ void wait_all(const uint32_t* flags, int lo, int W, uint32_t epoch) {
+    for (int k = 0; k < W; ++k)
+        while ((int32_t)(ld_acquire_sys(flags + lo + k) - epoch) < 0) __nanosleep(64);
+}
+
+template <int W>
+__global__ void __launch_bounds__(512)
+k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t lo, int64_t hi, int rank, uint32_t epoch,
+          float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt, float clip,
+          unsigned int* __restrict__ done_counter, float* __restrict__ dyn) {
+    if (dyn) {                      // {lr, step} on the device (CUDA-graph replay): step is also the barrier epoch
+        lr = dyn[0];
+        const double step = (double)dyn[1];
+        epoch = (uint32_t)dyn[1];
+        bc1 = (float)(1.0 - pow((double)b1, step));
+        bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, step));
+    }
+    // ---- start barrier
+    if (threadIdx.x == 0) {
+        if (blockIdx.x == 0) {
+            __threadfence_system();
+#pragma unroll
+            for (int k = 0; k < W; ++k) st_release_sys(P.flags[k] + rank, epoch);
+        }
+        wait_all(P.flags[rank], 0, W, epoch);
+    }
+    __syncthreads();
+    const float lr_bc1 = lr / bc1, invW = 1.0f / (float)W;
+    const bool shadow = P.sh[0] != nullptr;
+    const int64_t n4 = (hi - lo) >> 2;                        // lo and the shard length are multiples of 4 (host)
+    const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t q = t0; q < n4; q += nt) {
+        const int64_t i = lo + (q << 2);
+        float4 gs[W];
+#pragma unroll
+        for (int k = 0; k < W; ++k) gs[k] = ld_peer4(P.g[(rank + k) % W] + i);          // W loads in flight
+        float4 pp = *reinterpret_cast<const float4*>(P.p[rank] + i);
+        float4 mm = *reinterpret_cast<const float4*>(m + (i - lo));
+        float4 vv = *reinterpret_cast<const float4*>(v + (i - lo));
+        float4 g = gs[0];
+#pragma unroll
+        for (int k = 1; k < W; ++k) { g.x += gs[k].x; g.y += gs[k].y; g.z += gs[k].z; g.w += gs[k].w; }
+        pp.x = adam1(pp.x, g.x * invW, mm.x, vv.x, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        pp.y = adam1(pp.y, g.y * invW, mm.y, vv.y, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        pp.z = adam1(pp.z, g.z * invW, mm.z, vv.z, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        pp.w = adam1(pp.w, g.w * invW, mm.w, vv.w, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+        *reinterpret_cast<float4*>(m + (i - lo)) = mm;
+        *reinterpret_cast<float4*>(v + (i - lo)) = vv;
+        __nv_bfloat162 b_lo = __floats2bfloat162_rn(pp.x, pp.y), b_hi = __floats2bfloat162_rn(pp.z, pp.w);
+        uint2 sq;
+        sq.x = *reinterpret_cast<uint32_t*>(&b_lo);
+        sq.y = *reinterpret_cast<uint32_t*>(&b_hi);
+        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < W; ++k) {
+            const int peer = (rank + k) % W;
+            *reinterpret_cast<float4*>(P.p[peer] + i) = pp;
+            if (shadow) *reinterpret_cast<uint2*>(P.sh[peer] + i) = sq;
+            *reinterpret_cast<float4*>(P.g[peer] + i) = zero;
+        }
+    }
+    // ---- end barrier: the last CTA of this rank to finish publishes "my writes are done" and waits for the peers
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int ticket = atomicAdd(done_counter, 1u);
+        if (ticket == gridDim.x - 1) {
+            *done_counter = 0u;
+            __threadfence_system();
+#pragma unroll
+            for (int k = 0; k < W; ++k) st_release_sys(P.flags[k] + W + rank, epoch);
+            wait_all(P.flags[rank], W, W, epoch);
+            if (dyn) dyn[1] += 1.0f;                     // every CTA has read the step: this is the last one running
+        }
+    }
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------- peer memory (cudaIpc)
+extern "C" int nc_peer_alloc(int64_t bytes, void** out_dev) {
+    NC_REQUIRE(bytes > 0 && out_dev != nullptr, NC_EINVAL, "nc_peer_alloc: bad arguments");
+    cudaError_t e = cudaMalloc(out_dev, (size_t)bytes);
+    if (e == cudaSuccess) e = cudaMemset(*out_dev, 0, (size_t)bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        nc_set_error("nc_peer_alloc: %lld B: %s", (long long)bytes, cudaGetErrorString(e));
+        return NC_ECUDA;
+    }
+    return NC_OK;
+}
+
+extern "C" int nc_peer_free(void* dev) {
+    if (dev == nullptr) return NC_OK;
+    cudaError_t e = cudaFree(dev);
+    if (e != cudaSuccess) { cudaGetLastError(); nc_set_error("nc_peer_free: %s", cudaGetErrorString(e)); return NC_ECUDA; }
+    return NC_OK;
+}
+
+// handle_host: 64 bytes (cudaIpcMemHandle_t) for a pointer returned by nc_peer_alloc
+extern "C" int nc_peer_get_handle(void* dev, void* handle_host) {
+    NC_REQUIRE(dev != nullptr && handle_host != nullptr, NC_EINVAL, "nc_peer_get_handle: NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaError_t e = cudaIpcGetMemHandle((cudaIpcMemHandle_t*)handle_host, dev);
+    if (e != cudaSuccess) { cudaGetLastError(); nc_set_error("nc_peer_get_handle: %s", cudaGetErrorString(e)); return NC_ECUDA; }
+    return NC_OK;
+}
+
+extern "C" int nc_peer_open(const void* handle_host, void** out_dev) {
+    NC_REQUIRE(handle_host != nullptr && out_dev != nullptr, NC_EINVAL, "nc_peer_open: NULL argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle_host, sizeof(h));
+    cudaError_t e = cudaIpcOpenMemHandle(out_dev, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { cudaGetLastError(); nc_set_error("nc_peer_open: %s", cudaGetErrorString(e)); return NC_ECUDA; }
+    return NC_OK;
+}
+
+extern "C" int nc_peer_close(void* dev) {
+    if (dev == nullptr) return NC_OK;
+    cudaError_t e = cudaIpcCloseMemHandle(dev);
+    if (e != cudaSuccess) { cudaGetLastError(); nc_set_error("nc_peer_close: %s", cudaGetErrorString(e)); return NC_ECUDA; }
+    return NC_OK;
+}
+
+// p_ptrs_host / g_ptrs_host / shadow_ptrs_host / flag_ptrs_host: `world` device pointers each (entry `rank` = this
+// rank's own buffer, the others = peer mappings); shadow_ptrs_host may be NULL.  m, v: this rank's moments for its
+// shard only, [shard] floats with shard = ceil(numel / world / 4) * 4.  done_counter: one zero-initialised uint32
+// in this rank's memory.  `step` >= 1 is also the barrier epoch: every rank must call with the same sequence.
+extern "C" int nc_dp_adam_step(void* const* p_ptrs_host, void* const* g_ptrs_host, void* const* shadow_ptrs_host,
+                               void* const* flag_ptrs_host, float* m, float* v, int64_t numel, int32_t rank,
+                               int32_t world, float lr, float beta1, float beta2, float eps, float weight_decay,
+                               int32_t step, float clip_value, uint32_t* done_counter, int32_t n_ctas, float* dyn,
+                               void* stream) {
+    NC_REQUIRE(world >= 1 && world <= DP_MAX_WORLD && rank >= 0 && rank < world && numel > 0 && (step >= 1 || dyn), NC_EINVAL,
+               "nc_dp_adam_step: bad arguments (world=%d rank=%d numel=%lld step=%d)", world, rank, (long long)numel, step);
+    NC_REQUIRE(numel % 4 == 0, NC_ESHAPE, "nc_dp_adam_step: the arena length must be a multiple of 4");
+    DpPeers P;
+    for (int k = 0; k < DP_MAX_WORLD; ++k) { P.p[k] = nullptr; P.g[k] = nullptr; P.sh[k] = nullptr; P.flags[k] = nullptr; }
+    for (int k = 0; k < world; ++k) {
+        P.p[k] = (float*)p_ptrs_host[k];
+        P.g[k] = (float*)g_ptrs_host[k];
+        P.sh[k] = shadow_ptrs_host ? (__nv_bfloat16*)shadow_ptrs_host[k] : nullptr;
+        P.flags[k] = (uint32_t*)flag_ptrs_host[k];
+        NC_REQUIRE(P.p[k] && P.g[k] && P.flags[k], NC_EINVAL, "nc_dp_adam_step: NULL peer pointer %d", k);
+    }
+    const int64_t shard = nc_cdiv(nc_cdiv(numel, world), 4) * 4;
+    const int64_t lo = std::min<int64_t>((int64_t)rank * shard, numel), hi = std::min<int64_t>(lo + shard, numel);
+    const float bc1 = dyn ? 1.f : (float)(1.0 - pow((double)beta1, (double)step));
+    const float bc2_sqrt = dyn ? 1.f : (float)sqrt(1.0 - pow((double)beta2, (double)step));
+    if (n_ctas <= 0) n_ctas = 64;
+    cudaStream_t s = (cudaStream_t)stream;
+#define DP_LAUNCH(WW)                                                                                              \
+    k_dp_adam<WW><<<n_ctas, 512, 0, s>>>(P, m, v, lo, hi, rank, (uint32_t)step, lr, beta1, beta2, eps, weight_decay, bc1, \
+                                         bc2_sqrt, clip_value, done_counter, dyn)
+    switch (world) {
+        case 1: DP_LAUNCH(1); break;
+        case 2: DP_LAUNCH(2); break;
+        case 4: DP_LAUNCH(4); break;
+        case 8: DP_LAUNCH(8); break;
+        default: NC_REQUIRE(false, NC_EUNSUPPORTED, "nc_dp_adam_step: world size %d (1, 2, 4 or 8)", world);
+    }
+#undef DP_LAUNCH
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_dp_adam_step");
+    return NC_OK;
+}

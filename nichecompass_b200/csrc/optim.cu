@@ -139,7 +139,13 @@ __device__ __forceinline__ float adam_elem(float pi, float gi, float& mi, float&
 __global__ void __launch_bounds__(256)
 k_adam(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
        int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
-       float clip, __nv_bfloat16* __restrict__ p_bf16, int zero_g) {
+       float clip, __nv_bfloat16* __restrict__ p_bf16, int zero_g, const float* __restrict__ dyn) {
+    if (dyn) {                      // {lr, step} live on the device: the launch can be replayed from a CUDA graph
+        lr = dyn[0];
+        const double step = (double)dyn[1];
+        bc1 = (float)(1.0 - pow((double)b1, step));
+        bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, step));
+    }
     const float lr_bc1 = lr / bc1;
     const int64_t n4 = n >> 2;
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
@@ -299,9 +305,30 @@ extern "C" int nc_adam_step(float* p, float* g, float* m, float* v, int64_t n, f
                NC_EINVAL, "nc_adam_step: buffers must be 16-byte aligned");
     k_adam<<<grid_for((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, lr, beta1, beta2, eps, weight_decay,
                                                                    bc1, bc2_sqrt, clip_value, (__nv_bfloat16*)p_bf16,
-                                                                   zero_grad);
+                                                                   zero_grad, nullptr);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_adam_step");
+    return NC_OK;
+}
+
+__global__ void k_bump_step(float* dyn) { dyn[1] += 1.0f; }
+
+// Same update with the learning rate and the step number read from device memory (dyn = {lr, step}, step >= 1 is the
+// number of THIS update) and the step advanced by a second one-thread launch: nothing in the launch sequence
+// depends on host state, so a captured training step can be replayed (train/trainer.py CUDA-graph buckets).
+extern "C" int nc_adam_step_dyn(float* p, float* g, float* m, float* v, int64_t n, float* dyn, float beta1,
+                                float beta2, float eps, float weight_decay, float clip_value, void* p_bf16,
+                                int zero_grad, void* stream) {
+    NC_REQUIRE(n >= 0 && dyn != nullptr, NC_EINVAL, "nc_adam_step_dyn: need n >= 0 and the device state");
+    if (n == 0) return NC_OK;
+    NC_REQUIRE(((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) % 16 == 0 && (uintptr_t)p_bf16 % 8 == 0,
+               NC_EINVAL, "nc_adam_step_dyn: buffers must be 16-byte aligned");
+    k_adam<<<grid_for((n + 3) / 4), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, 0.f, beta1, beta2, eps, weight_decay,
+                                                                   1.f, 1.f, clip_value, (__nv_bfloat16*)p_bf16,
+                                                                   zero_grad, dyn);
+    k_bump_step<<<1, 1, 0, (cudaStream_t)stream>>>(dyn);
+    nc_count_launch(2);
+    NC_CHECK_LAUNCH("nc_adam_step_dyn");
     return NC_OK;
 }
 

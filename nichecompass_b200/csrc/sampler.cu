@@ -359,36 +359,48 @@ namespace {
 __device__ __forceinline__ int merge_map(int j, int n_seed_self, int add_seed, int add_other) {
     return j < n_seed_self ? j + add_seed : j + add_other;
 }
+// b_seed_pad >= b_seed, n_sub_pad, e_pad: padded sizes of the merged problem (CUDA-graph size buckets of the
+// training step): merged node order = [a seeds | b seeds | pad seeds | a others | b others | pad others]; pad seeds
+// have empty rows, pad nodes carry the id of a real node (so every gather stays in bounds) and are referenced by no
+// edge -- their rows cost work but change no result.
 __global__ void k_merge_subgraphs(const int32_t* __restrict__ a_rowptr, const int32_t* __restrict__ a_col,
                                   const int32_t* __restrict__ a_nid, int a_seed, int a_sub,
                                   const int32_t* __restrict__ b_rowptr, const int32_t* __restrict__ b_col,
                                   const int32_t* __restrict__ b_nid, int b_seed, int b_sub,
                                   int32_t* __restrict__ m_rowptr, int32_t* __restrict__ m_col,
-                                  int32_t* __restrict__ m_nid) {
-    const int n_dst = a_seed + b_seed, n_sub = a_sub + b_sub;
+                                  int32_t* __restrict__ m_nid, int b_seed_pad, int n_sub_pad, int e_pad) {
+    const int n_dst = a_seed + b_seed, n_dst_pad = a_seed + b_seed_pad;
+    const int pad = b_seed_pad - b_seed;
+    const int n_sub = a_sub + b_sub + pad;                    // real nodes + pad seeds
     const int Ea = a_rowptr[a_seed];
+    const int Etot = Ea + b_rowptr[b_seed];
     const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    const int filler = a_sub > 0 ? a_nid[0] : (b_sub > 0 ? b_nid[0] : 0);
     // node ids in merged order
-    for (int i = gtid; i < n_sub; i += gsz) {
+    for (int i = gtid; i < n_sub_pad; i += gsz) {
         int v;
         if (i < a_seed) v = a_nid[i];
         else if (i < n_dst) v = b_nid[i - a_seed];
-        else if (i < n_dst + (a_sub - a_seed)) v = a_nid[i - b_seed];
-        else v = b_nid[i - a_sub];
+        else if (i < n_dst_pad) v = filler;
+        else if (i < n_dst_pad + (a_sub - a_seed)) v = a_nid[i - b_seed_pad];
+        else if (i < n_sub) v = b_nid[i - a_sub - pad];
+        else v = filler;
         m_nid[i] = v;
     }
-    // rows of the targets, column ids remapped: a: seeds stay, others + b_seed; b: seeds + a_seed, others + a_sub
-    for (int r = gtid; r <= n_dst; r += gsz)
-        m_rowptr[r] = r <= a_seed ? a_rowptr[r] : Ea + b_rowptr[r - a_seed];
+    // rows of the targets, column ids remapped: a: seeds stay, others + b_seed_pad; b: seeds + a_seed,
+    // others + a_sub + pad
+    for (int r = gtid; r <= n_dst_pad; r += gsz)
+        m_rowptr[r] = r <= a_seed ? a_rowptr[r] : (r <= n_dst ? Ea + b_rowptr[r - a_seed] : Etot);
+    for (int e = Etot + gtid; e < e_pad; e += gsz) m_col[e] = 0;
     const int warp = gtid >> 5, lane = gtid & 31, nwarp = gsz >> 5;
     for (int r = warp; r < n_dst; r += nwarp) {
         if (r < a_seed) {
             const int e0 = a_rowptr[r], e1 = a_rowptr[r + 1];
-            for (int e = e0 + lane; e < e1; e += 32) m_col[e] = merge_map(a_col[e], a_seed, 0, b_seed);
+            for (int e = e0 + lane; e < e1; e += 32) m_col[e] = merge_map(a_col[e], a_seed, 0, b_seed_pad);
         } else {
             const int q = r - a_seed;
             const int e0 = b_rowptr[q], e1 = b_rowptr[q + 1];
-            for (int e = e0 + lane; e < e1; e += 32) m_col[Ea + e] = merge_map(b_col[e], b_seed, a_seed, a_sub);
+            for (int e = e0 + lane; e < e1; e += 32) m_col[Ea + e] = merge_map(b_col[e], b_seed, a_seed, a_sub + pad);
         }
     }
 }
@@ -404,8 +416,27 @@ extern "C" int nc_merge_subgraphs(const int32_t* a_rowptr, const int32_t* a_col,
     const int n = a_sub + b_sub;
     const int grid = (int)std::min<int64_t>(nc_cdiv(n, 256), 2 * nc_num_sms());
     k_merge_subgraphs<<<grid, 256, 0, (cudaStream_t)stream>>>(a_rowptr, a_col, a_nid, a_seed, a_sub, b_rowptr, b_col,
-                                                             b_nid, b_seed, b_sub, m_rowptr, m_col, m_nid);
+                                                             b_nid, b_seed, b_sub, m_rowptr, m_col, m_nid, b_seed,
+                                                             a_sub + b_sub, 0);
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_merge_subgraphs");
+    return NC_OK;
+}
+
+extern "C" int nc_merge_subgraphs_padded(const int32_t* a_rowptr, const int32_t* a_col, const int32_t* a_nid,
+                                         int32_t a_seed, int32_t a_sub, const int32_t* b_rowptr, const int32_t* b_col,
+                                         const int32_t* b_nid, int32_t b_seed, int32_t b_sub, int32_t b_seed_pad,
+                                         int32_t n_sub_pad, int32_t e_pad, int32_t* m_rowptr, int32_t* m_col,
+                                         int32_t* m_nid, void* stream) {
+    NC_REQUIRE(a_seed >= 0 && b_seed >= 0 && a_sub >= a_seed && b_sub >= b_seed && b_seed_pad >= b_seed &&
+               n_sub_pad >= a_sub + b_sub + (b_seed_pad - b_seed) && e_pad >= 0, NC_ESHAPE,
+               "nc_merge_subgraphs_padded: bad sizes");
+    if (n_sub_pad == 0) return NC_OK;
+    const int grid = (int)std::min<int64_t>(nc_cdiv(n_sub_pad, 256), 2 * nc_num_sms());
+    k_merge_subgraphs<<<grid, 256, 0, (cudaStream_t)stream>>>(a_rowptr, a_col, a_nid, a_seed, a_sub, b_rowptr, b_col,
+                                                             b_nid, b_seed, b_sub, m_rowptr, m_col, m_nid, b_seed_pad,
+                                                             n_sub_pad, e_pad);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_merge_subgraphs_padded");
     return NC_OK;
 }

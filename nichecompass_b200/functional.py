@@ -214,6 +214,20 @@ def _col_sum(x: torch.Tensor, n_cols: int, out: Optional[torch.Tensor] = None) -
 HIDDEN_INPUT = "hidden"
 
 
+_CONV_SEG = {}
+
+
+def _conv_segments(offs, Cs, out_offsets, dev):
+    """(host, device) int32 [NC, 4] segment table of the stacked convs, built once per layout: no host-to-device
+    copy inside a training step (a copy from pageable memory cannot be captured into a CUDA graph)."""
+    key = (offs, Cs, out_offsets, str(dev))
+    hit = _CONV_SEG.get(key)
+    if hit is None:
+        host = torch.tensor([[offs[c], Cs[c], out_offsets[c], 0] for c in range(len(Cs))], dtype=torch.int32)
+        hit = _CONV_SEG[key] = (host, host.to(dev))
+    return hit
+
+
 class EncoderGATv2Fn(torch.autograd.Function):
     """fc_l1 + ReLU + the four GATv2Conv heads of nn/encoders.py:144-208 (n_fc_layers=1,
     n_layers=1) for the first ``graph.n_dst`` nodes: returns [n_dst, 2P] = (mu | logstd) with
@@ -241,8 +255,7 @@ class EncoderGATv2Fn(torch.autograd.Function):
         offs = [sum(widths[:c]) for c in range(NC)]
         NL = sum(widths)
         ldl = pad8(NL)
-        seg_host = torch.tensor([[offs[c], Cs[c], out_offsets[c], 0] for c in range(NC)], dtype=torch.int32)
-        seg = seg_host.to(dev, non_blocking=True)
+        seg_host, seg = _conv_segments(tuple(offs), tuple(Cs), tuple(out_offsets), dev)
         W1p = None if pre else pack_rows((cache_key, "W1"), [W1], act, W1.size(1))
         Wl = pack_rows((cache_key, "Wl"), [cv[0] for cv in conv], act, Hd)
         Wr = pack_rows((cache_key, "Wr"), [cv[2] for cv in conv], act, Hd)
@@ -593,11 +606,12 @@ def mask_info(mask: Optional[torch.Tensor]):
     if mask is None:
         return ("none",)
     key = (mask.data_ptr(), mask._version, tuple(mask.shape))
-    hit = _MASK_INFO.get(key)
+    hit = _MASK_INFO.pop(key, None)
     if hit is not None:
+        _MASK_INFO[key] = hit                  # most recently used last
         return hit[0]
-    if len(_MASK_INFO) > 64:
-        _MASK_INFO.clear()
+    while len(_MASK_INFO) >= 256:              # least recently used first; never the masks of the running step
+        _MASK_INFO.pop(next(iter(_MASK_INFO)))
     with torch.no_grad():
         nz = mask != 0
         nnz = int(nz.sum())

@@ -411,7 +411,9 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
             if use_only_active_gps:
                 # all on the device, no host sync (the reference's boolean-mask assignments sync)
                 self.running_mean_abs_mu.mul_(active)
-                self._rna_gp_alive = self._rna_gp_alive.to(active.device) & active
+                if self._rna_gp_alive.device != active.device:
+                    self._rna_gp_alive = self._rna_gp_alive.to(active.device)
+                self._rna_gp_alive.logical_and_(active)      # in place: one persistent buffer (CUDA-graph replays)
                 if "atac" in self.modalities_:
                     for ent in ("target", "source"):
                         dm = getattr(self, f"{ent}_atac_dynamic_decoder_mask").to(active.device)
@@ -508,7 +510,8 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
         staged = getattr(edge_batch, "_joint_input", None)
         if staged is not None and staged[0] is node_batch:
             _, gm, x_enc, ev, labels = staged
-            torch.cuda.current_stream().wait_event(ev)          # staged on a side stream (``stage_joint_input``)
+            if ev is not None:
+                torch.cuda.current_stream().wait_event(ev)      # staged on a side stream (``stage_joint_input``)
             edge_batch._joint_input = None
         else:
             gm, x_enc = self._joint_input(node_batch, edge_batch)

@@ -42,9 +42,9 @@ class OneHopGCNNormNodeLabelAggregator(nn.Module):
         out = ops.spmm_csr(x.detach(), graph.rowptr, graph.col, w, wself, True, n_rows)
         return out, (_entry_weights_in_edge_order(graph, w, wself) if return_agg_weights else None)
 
-    def forward_store(self, store, n_id, graph: SubgraphCSR, n_rows: int) -> torch.Tensor:
+    def forward_store(self, store, n_id, graph: SubgraphCSR, n_rows: int, out=None) -> torch.Tensor:
         w, wself = graph.gcn_weights(use_out_degree=True, n_rows=n_rows)
-        return ops.spmm_csr_store(store, n_id, graph.rowptr, graph.col, w, wself, True, n_rows)
+        return ops.spmm_csr_store(store, n_id, graph.rowptr, graph.col, w, wself, True, n_rows, out=out)
 
 
 class OneHopSumNodeLabelAggregator(nn.Module):
@@ -60,8 +60,8 @@ class OneHopSumNodeLabelAggregator(nn.Module):
         n_rows = graph.n_nodes if n_rows is None else n_rows
         return ops.spmm_csr(x.detach(), graph.rowptr, graph.col, None, None, False, n_rows), None
 
-    def forward_store(self, store, n_id, graph: SubgraphCSR, n_rows: int) -> torch.Tensor:
-        return ops.spmm_csr_store(store, n_id, graph.rowptr, graph.col, None, None, False, n_rows)
+    def forward_store(self, store, n_id, graph: SubgraphCSR, n_rows: int, out=None) -> torch.Tensor:
+        return ops.spmm_csr_store(store, n_id, graph.rowptr, graph.col, None, None, False, n_rows, out=out)
 
 
 class OneHopAttentionNodeLabelAggregator(nn.Module):

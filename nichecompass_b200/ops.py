@@ -85,9 +85,11 @@ def spmm_csr(x: torch.Tensor, rowptr, col, w, wself, skip_self: bool, n_rows: in
     return out
 
 
-def spmm_csr_store(store, n_id, rowptr, col, w, wself, skip_self: bool, n_rows: int) -> torch.Tensor:
+def spmm_csr_store(store, n_id, rowptr, col, w, wself, skip_self: bool, n_rows: int,
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
     n_id, rowptr, col = _i32(n_id), _i32(rowptr), _i32(col)
-    out = torch.empty(n_rows, store.n_cols, dtype=torch.float32, device=rowptr.device)
+    if out is None:
+        out = torch.empty(n_rows, store.n_cols, dtype=torch.float32, device=rowptr.device)
     call("nc_spmm_csr_store", store.rowptr, store.col, store.val, store.n_cols, n_id, rowptr, col,
          w, wself, int(skip_self), n_rows, out, out.stride(0))
     return out
@@ -97,11 +99,12 @@ BG_MAX_CTAS = 0         # grid bound of the side-stream gather (0: the library's
 
 
 def csr_gather_rows(store, n_id, n_rows: int, log1p: bool, dtype: torch.dtype, ld: Optional[int] = None,
-                    background: bool = False):
+                    background: bool = False, out: Optional[torch.Tensor] = None):
     """``background``: the low-footprint kernel for a side stream (``nc_csr_gather_rows_bg``)."""
     ld = store.n_cols if ld is None else ld
     n_id = _i32(n_id)
-    out = torch.empty(n_rows, ld, dtype=dtype, device=store.device)
+    if out is None:
+        out = torch.empty(n_rows, ld, dtype=dtype, device=store.device)
     if background:
         call("nc_csr_gather_rows_bg", store.rowptr, store.col, store.val, store.n_cols, n_id, n_rows,
              int(log1p), out, dtype_code(dtype), ld, BG_MAX_CTAS)

@@ -27,11 +27,73 @@ from .._lib import call
 ALIGN = 8          # elements: group starts are 32-byte (fp32) / 16-byte (bf16 shadow) aligned
 
 
+class _RawCuda:
+    """``__cuda_array_interface__`` over a raw device pointer (memory owned by ``PeerBuffer``)."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.owner = owner
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerBuffer:
+    """Device memory the other ranks of the box can map: ``nc_peer_alloc`` (cudaMalloc, zero-filled) + a cudaIpc
+    handle exchanged through ``torch.distributed``; ``ptrs[r]`` is rank r's buffer as seen from this process
+    (own pointer for the own rank).  Backs the arenas of ``FlatAdam(peer_group=...)``."""
+
+    def __init__(self, nbytes: int, group=None):
+        import ctypes
+        import torch.distributed as dist
+        from .._lib import NicheCompassCudaError, lib
+        self._lib, self._ct = lib(), ctypes
+        self.nbytes = int(nbytes)
+        p = ctypes.c_void_p()
+        if self._lib.nc_peer_alloc(ctypes.c_int64(self.nbytes), ctypes.byref(p)) != 0:
+            raise NicheCompassCudaError(self._lib.nc_last_error().decode())
+        self.ptr = p.value
+        h = (ctypes.c_ubyte * 64)()
+        if self._lib.nc_peer_get_handle(ctypes.c_void_p(self.ptr), h) != 0:
+            raise NicheCompassCudaError(self._lib.nc_last_error().decode())
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        handles = [None] * world
+        dist.all_gather_object(handles, bytes(h), group=group)
+        self.ptrs, self._opened = [], []
+        for r, hb in enumerate(handles):
+            if r == rank:
+                self.ptrs.append(self.ptr)
+                continue
+            q = ctypes.c_void_p()
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(hb)
+            if self._lib.nc_peer_open(buf, ctypes.byref(q)) != 0:
+                raise NicheCompassCudaError(f"rank {rank}: cannot map rank {r}'s buffer: " +
+                                            self._lib.nc_last_error().decode())
+            self.ptrs.append(q.value)
+            self._opened.append(q.value)
+        self.ptr_array = (ctypes.c_void_p * world)(*self.ptrs)
+        dist.barrier(group=group)
+
+    def tensor(self, dtype: torch.dtype) -> torch.Tensor:
+        t = torch.as_tensor(_RawCuda(self.ptr, self.nbytes, self), device=torch.device("cuda", torch.cuda.current_device()))
+        return t.view(dtype)
+
+    def close(self):
+        """Unmap the peers' buffers and free the own one (all ranks must have stopped using them)."""
+        torch.cuda.synchronize()
+        for q in self._opened:
+            self._lib.nc_peer_close(self._ct.c_void_p(q))
+        self._opened = []
+        if self.ptr:
+            self._lib.nc_peer_free(self._ct.c_void_p(self.ptr))
+            self.ptr = None
+
+
 class FlatAdam:
     def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999),
                  eps: float = 1e-8, weight_decay: float = 0.,
                  groups: Optional[Sequence[Sequence[torch.nn.Parameter]]] = None,
-                 bf16_shadow: bool = False):
+                 bf16_shadow: bool = False, peer_group=None, peer_ctas: int = 0):
+        """``peer_group``: a ``torch.distributed`` process group of ranks on ONE NVLink box (``True``: the world).
+        The arenas then live in peer-mapped memory and ``step()`` is the fused exchange + Adam kernel
+        (``nc_dp_adam_step``, csrc/dp_exchange.cu): no NCCL all-reduce, the moments exist for the owned shard only."""
         wanted = [p for p in params if p.requires_grad]
         if not wanted:
             raise ValueError("optimizer got an empty parameter list")
@@ -61,11 +123,32 @@ class FlatAdam:
                 self.offsets.append(n)
                 n += p.numel()
         self.numel = n = (n + ALIGN - 1) // ALIGN * ALIGN
-        self.flat_p = torch.zeros(n, dtype=torch.float32, device=dev)
-        self.flat_g = torch.zeros(n, dtype=torch.float32, device=dev)
-        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
-        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
-        self.flat_bf16 = torch.zeros(n, dtype=torch.bfloat16, device=dev) if bf16_shadow else None
+        self.peer = None
+        if peer_group is not None and peer_group is not False:
+            import torch.distributed as dist
+            grp = None if peer_group is True else peer_group
+            world, rank = dist.get_world_size(grp), dist.get_rank(grp)
+            if world > 1:
+                bufs = {"p": PeerBuffer(4 * n, grp), "g": PeerBuffer(4 * n, grp),
+                        "flags": PeerBuffer(max(8 * world, 256), grp)}
+                if bf16_shadow:
+                    bufs["sh"] = PeerBuffer(2 * n, grp)
+                shard = ((n + world - 1) // world + 3) // 4 * 4
+                self.peer = {"bufs": bufs, "world": world, "rank": rank, "group": grp, "shard": shard,
+                             "ctas": int(peer_ctas),
+                             "done": torch.zeros(1, dtype=torch.int32, device=dev)}
+        if self.peer is None:
+            self.flat_p = torch.zeros(n, dtype=torch.float32, device=dev)
+            self.flat_g = torch.zeros(n, dtype=torch.float32, device=dev)
+            self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+            self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+            self.flat_bf16 = torch.zeros(n, dtype=torch.bfloat16, device=dev) if bf16_shadow else None
+        else:
+            b = self.peer["bufs"]
+            self.flat_p, self.flat_g = b["p"].tensor(torch.float32), b["g"].tensor(torch.float32)
+            self.flat_bf16 = b["sh"].tensor(torch.bfloat16) if bf16_shadow else None
+            self.exp_avg = torch.zeros(self.peer["shard"], dtype=torch.float32, device=dev)
+            self.exp_avg_sq = torch.zeros(self.peer["shard"], dtype=torch.float32, device=dev)
         with torch.no_grad():
             for p, o in zip(self.params, self.offsets):
                 view = self.flat_p[o:o + p.numel()].view_as(p)
@@ -80,6 +163,23 @@ class FlatAdam:
         self.param_groups = [{"lr": lr, "betas": betas, "eps": eps, "weight_decay": weight_decay,
                               "params": self.params}]
         self.step_count = 0
+        # {learning rate, number of the NEXT update} on the device: the update kernels read them there, so a captured
+        # training step can be replayed without any host-side argument going stale (train/trainer.py graph buckets)
+        self.dyn = torch.tensor([float(lr), 1.0], dtype=torch.float32, device=dev)
+        self._lr_on_device = float(lr)
+
+    def sync_lr(self):
+        """Push ``param_groups[0]["lr"]`` (the reference's ``param_group["lr"] *= factor`` idiom) to the device."""
+        lr = float(self.param_groups[0]["lr"])
+        if lr != self._lr_on_device:
+            self.dyn[0:1].fill_(lr)
+            self._lr_on_device = lr
+
+    def note_replayed_step(self):
+        """Book-keeping for one update that ran from a replayed CUDA graph (no Python ``step()`` call)."""
+        self.step_count += 1
+        self._grads_clean = True
+        Fn.bump_param_epoch()
 
     # ------------------------------------------------------------------ bf16 shadow
     def _versions(self):
@@ -107,7 +207,10 @@ class FlatAdam:
                 p.grad = self.flat_g[o:o + p.numel()].view_as(p)
 
     def all_reduce_grads(self, group=None):
-        """Data-parallel exchange: mean of the flat gradient buffer over the ranks."""
+        """Data-parallel exchange: mean of the flat gradient buffer over the ranks (a no-op with peer arenas: the
+        exchange is part of ``step``)."""
+        if self.peer is not None:
+            return
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
             dist.all_reduce(self.flat_g, op=dist.ReduceOp.AVG if self.flat_g.is_cuda else dist.ReduceOp.SUM,
@@ -119,11 +222,21 @@ class FlatAdam:
     def step(self, clip_value: float = 0.):
         g = self.param_groups[0]
         self.step_count += 1
+        self.sync_lr()
         if self.flat_bf16 is not None and not self.shadow_is_current():
             self._shadow_versions = self._versions()       # the kernel below rewrites the whole shadow
-        call("nc_adam_step", self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.numel,
-             float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
-             float(g["weight_decay"]), self.step_count, float(clip_value), self.flat_bf16, 1)
+        if self.peer is not None:
+            pr, b = self.peer, self.peer["bufs"]
+            call("nc_dp_adam_step", b["p"].ptr_array, b["g"].ptr_array, b["sh"].ptr_array if "sh" in b else None,
+                 b["flags"].ptr_array, self.exp_avg, self.exp_avg_sq, self.numel, pr["rank"], pr["world"],
+                 float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
+                 float(g["weight_decay"]), self.step_count, float(clip_value), pr["done"], pr["ctas"], self.dyn)
+            self._grads_clean = True
+            Fn.bump_param_epoch()
+            return
+        call("nc_adam_step_dyn", self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.numel, self.dyn,
+             float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), float(g["weight_decay"]),
+             float(clip_value), self.flat_bf16, 1)
         self._grads_clean = True
         Fn.bump_param_epoch()
 
@@ -133,6 +246,7 @@ class FlatAdam:
 
     def load_state_dict(self, sd):
         self.step_count = int(sd["step"])
+        self.dyn[1:2].fill_(float(self.step_count + 1))
         self.exp_avg.copy_(sd["exp_avg"])
         self.exp_avg_sq.copy_(sd["exp_avg_sq"])
         self.param_groups[0]["lr"] = sd["lr"]

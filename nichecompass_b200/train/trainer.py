@@ -19,9 +19,11 @@ What runs differently (and why it is result-preserving):
 """
 import copy
 import math
+import os
 import time
 import warnings
 from collections import defaultdict
+from types import SimpleNamespace
 from typing import List, Optional
 
 import numpy as np
@@ -134,6 +136,12 @@ class Trainer(BaseTrainerMixin):
         self.pipeline_sampler_ = kwargs.pop("pipeline_sampler", True)
         # None: stage the next iteration's encoder input on a side stream when the count store lives in host memory
         self.stage_inputs_ = kwargs.pop("stage_inputs", None)
+        # CUDA graphs: the whole iteration (encoder input gather ... Adam) is captured once per size bucket and replayed
+        self.cuda_graphs_ = bool(int(kwargs.pop("cuda_graphs", os.environ.get("NC_CUDA_GRAPHS", "1"))))
+        self._graph_buckets, self._graph_pool = {}, None
+        self.graph_stats_ = {"replayed": 0, "captured": 0, "eager": 0}
+        self.dp_exchange_ = kwargs.pop("dp_exchange", os.environ.get("NC_DP_EXCHANGE", "peer"))
+        self.dp_exchange_ctas_ = int(kwargs.pop("dp_exchange_ctas", os.environ.get("NC_DP_EXCHANGE_CTAS", "0")))
         kwargs.pop("latent_dtype", None)          # forwarded by NicheCompass.train, unused here (as in the reference)
         self.epoch = -1
         self.training_time = 0
@@ -227,6 +235,9 @@ class Trainer(BaseTrainerMixin):
     def train_iteration(self, edge_batch, node_batch) -> dict:
         """train/trainer.py:368-421: two forwards, loss, zero_grad, backward, clip, Adam step.
         Returns the loss dictionary (device scalars; nothing is read back here)."""
+        if self._graph_eligible(node_batch, edge_batch):
+            return self._graph_iteration(node_batch, edge_batch)
+        self.graph_stats_["eager"] += 1
         joint = getattr(self.model, "joint_supported", None)
         if self.joint_encoder_ and joint is not None and joint(node_batch, edge_batch):
             # one encoder pass over the block-diagonal union of the two sampled sub-graphs
@@ -248,7 +259,139 @@ class Trainer(BaseTrainerMixin):
         if hook is not None:                 # parity tests: the gradients live in the arena until the Adam kernel clears them
             hook(self, node_out, edge_out)
         self.optimizer.step(clip_value=self.grad_clip_value_)
-        return loss_dict
+        # detached: a caller that keeps the dictionary must not keep the iteration's autograd graph alive with it
+        return {k: v.detach() for k, v in loss_dict.items()}
+
+    # ------------------------------------------------------------------ CUDA-graph size buckets
+    # The reference loop (train/trainer.py:364-421) is ~70 kernel launches behind ~100 small torch ops and 16
+    # autograd functions per iteration: 3.2-3.8 ms of Python for 3.2 ms of device work.  Every size of an iteration is
+    # known on the host before it is launched (the sampler runs one batch ahead), so the iteration is captured ONCE
+    # per size bucket -- sub-graph rows rounded up to 256, live edges to 1024, edge seeds to 4 x edge batch -- and
+    # replayed: the host then only merges the two sampled sub-graphs into the bucket's padded buffers, gathers the
+    # parameter-free label rows, draws the reparameterisation noise and launches the graph.  Padding rows repeat a
+    # real node and are referenced by no edge: they cost (<= 3 %) work and change no result
+    # (tests/test_trainer_gpu.py::test_cuda_graph_iterations_equal_eager_iterations).
+    def _graph_eligible(self, node_batch, edge_batch) -> bool:
+        if not self.cuda_graphs_:
+            return False
+        from .. import _lib
+        m = self.model
+        joint = getattr(m, "joint_supported", None)
+        return (m.training and self.joint_encoder_ and joint is not None and joint(node_batch, edge_batch)
+                and m._eps_queue is None and getattr(self, "after_backward", None) is None and _lib._HOOK is None
+                and m.n_cat_covariates_ == 0 and m.node_label_method_ != "one-hop-attention"
+                and "atac" not in m.modalities_
+                and int(node_batch.batch_size) == int(self.node_batch_size_)
+                and edge_batch.edge_label_index.size(1) == 2 * int(self.edge_batch_size_)
+                and getattr(edge_batch, "_joint_input", None) is None)
+
+    def _graph_iteration(self, node_batch, edge_batch):
+        from .. import _lib, ops
+        from .._lib import call
+        from ..functional import SubgraphCSR
+        m, opt = self.model, self.optimizer
+        gn, ge = node_batch.graph, edge_batch.graph
+        a_seed, a_sub, b_seed, b_sub = gn.n_dst, gn.n_nodes, ge.n_dst, ge.n_nodes
+        nb, B4 = int(self.node_batch_size_), 4 * int(self.edge_batch_size_)
+        pad = B4 - b_seed
+        n_sub_pad = (a_sub + b_sub + pad + 255) // 256 * 256
+        e_pad = (max(gn.e_dst + ge.e_dst, 1) + 1023) // 1024 * 1024
+        key = (n_sub_pad, e_pad, bool(self.use_only_active_gps), bool(self.edge_recon_active),
+               bool(self.cat_covariates_contrastive_active), float(self.grad_clip_value_))
+        S = self._graph_buckets.get(key)
+        store = node_batch.store
+        if S is None:
+            dev = self.device
+            P = m.n_prior_gp_ + m.n_addon_gp_
+            eli = edge_batch.edge_label_index
+            S = self._graph_buckets[key] = SimpleNamespace(
+                n_sub_pad=n_sub_pad, e_pad=e_pad, n_dst_pad=a_seed + B4, graph=None, losses=None, n_launches=0, uses=0,
+                m_rowptr=torch.zeros(a_seed + B4 + 1, dtype=torch.int32, device=dev),
+                m_col=torch.zeros(e_pad, dtype=torch.int32, device=dev),
+                m_nid=torch.zeros(n_sub_pad, dtype=torch.int32, device=dev),
+                x_t=torch.zeros(nb, store.n_cols, dtype=torch.float32, device=dev),
+                x_n=torch.zeros(nb, store.n_cols, dtype=torch.float32, device=dev),
+                eli=torch.zeros_like(eli), elab=torch.zeros_like(edge_batch.edge_label),
+                eps_n=torch.zeros(nb, P, dtype=torch.float32, device=dev),
+                eps_e=torch.zeros(eli.size(1) * 2, P, dtype=torch.float32, device=dev))
+        # ---- per-iteration inputs (eager, a handful of launches)
+        call("nc_merge_subgraphs_padded", gn.rowptr, gn.col, node_batch.n_id, a_seed, a_sub, ge.rowptr, ge.col,
+             edge_batch.n_id, b_seed, b_sub, B4, n_sub_pad, e_pad, S.m_rowptr, S.m_col, S.m_nid)
+        ops.csr_gather_rows(store, node_batch.n_id, nb, False, torch.float32, out=S.x_t)
+        m.rna_node_label_aggregator.forward_store(store, node_batch.n_id, gn, nb, out=S.x_n)
+        S.eli.copy_(edge_batch.edge_label_index)
+        S.elab.copy_(edge_batch.edge_label)
+        S.eps_n.normal_()                                  # same draws, same order as the eager path's randn_like
+        S.eps_e.normal_()
+        opt.sync_lr()
+        S.uses += 1
+        if S.graph is None and S.uses == 1:
+            # first visit of a bucket: a genuine eager iteration on the bucket's buffers (also the warm-up that
+            # every lazily initialised piece -- mask structure, function attributes -- needs before a capture)
+            self.graph_stats_["eager"] += 1
+            return self._graph_body(S, store)
+        if S.graph is None:
+            if self._graph_pool is None:
+                self._graph_pool = torch.cuda.graph_pool_handle()
+            # no autograd graph of an earlier (eager, default-stream) iteration may be alive: its AccumulateGrad nodes
+            # would be reused and tie the capture to the stream they were created on
+            # (cudaErrorStreamCaptureIsolation); the module keeps mu / logstd, the decoder its packed z
+            import gc
+            from .. import functional as Fn
+            m.mu = m.logstd = None
+            Fn._ZA_CACHE.clear()
+            gc.collect()
+            g = torch.cuda.CUDAGraph()
+            n0, steps0 = _lib.launch_count(), opt.step_count
+            with torch.cuda.graph(g, pool=self._graph_pool):
+                S.losses = self._graph_body(S, store)
+            S.n_launches = _lib.launch_count() - n0
+            _lib.lib().nc_launch_count_add(-S.n_launches)       # recorded, not run
+            opt.step_count = steps0
+            S.graph = g
+            self.graph_stats_["captured"] += 1
+        S.graph.replay()
+        _lib.lib().nc_launch_count_add(S.n_launches)
+        opt.note_replayed_step()
+        self.graph_stats_["replayed"] += 1
+        return S.losses
+
+    def _graph_body(self, S, store):
+        """One iteration on a bucket's static buffers: everything from the encoder-input gather to the Adam update."""
+        from .. import ops
+        from ..functional import SubgraphCSR
+        from ..ops import pad8
+        m = self.model
+        nb = int(self.node_batch_size_)
+        gm = SubgraphCSR(S.m_rowptr, S.m_col, S.n_sub_pad, S.n_dst_pad, self._graph_max_deg(), e_dst=S.e_pad)
+        x_enc = ops.csr_gather_rows(store, S.m_nid, S.n_sub_pad, m.log_variational_, m.compute_dtype,
+                                    pad8(m.encoder.n_input))
+        node_b = SimpleNamespace(store=store, batch_size=nb, n_id=None, graph=SimpleNamespace(n_dst=nb, n_nodes=nb))
+        edge_b = SimpleNamespace(store=store, edge_label_index=S.eli, edge_label=S.elab, n_id=None,
+                                 graph=SimpleNamespace(n_dst=S.n_dst_pad - nb, n_nodes=S.n_sub_pad - nb))
+        edge_b._joint_input = (node_b, gm, x_enc, None, (S.x_t, S.x_n))
+        m._eps_queue = [S.eps_n, S.eps_e]
+        try:
+            node_out, edge_out = m.forward_joint(node_b, edge_b, self.use_only_active_gps)
+        finally:
+            m._eps_queue = None
+        loss_dict = m.loss(edge_model_output=edge_out, node_model_output=node_out, **self._loss_kwargs(),
+                           edge_recon_active=self.edge_recon_active,
+                           cat_covariates_contrastive_active=self.cat_covariates_contrastive_active)
+        self.optimizer.zero_grad()
+        loss_dict["optim_loss"].backward()
+        if self.world_size_ > 1:
+            self.optimizer.all_reduce_grads()
+        self.optimizer.step(clip_value=self.grad_clip_value_)
+        return {k: v.detach() for k, v in loss_dict.items()}
+
+    def _graph_max_deg(self) -> int:
+        """Upper bound of a sampled row's length: the largest in-degree of the two message-passing graphs."""
+        d = getattr(self, "_graph_max_deg_", None)
+        if d is None:
+            d = max(self.node_masked_data.device_graph().max_deg, self.edge_train_data.device_graph().max_deg)
+            self._graph_max_deg_ = d
+        return d
 
     def _sync_running_stats(self):
         """Ranks see different node batches: average the |mu| EMA so that every rank prunes the
@@ -400,9 +543,29 @@ class Trainer(BaseTrainerMixin):
         enc = getattr(self.model, "encoder", None)
         groups = enc.arena_groups() if hasattr(enc, "arena_groups") else None
         shadow = getattr(self.model, "compute_dtype", torch.float32) == torch.bfloat16
-        self.optimizer = FlatAdam(params, lr=lr, weight_decay=weight_decay, groups=groups, bf16_shadow=shadow)
+        self.optimizer = self._make_optimizer(params, lr, weight_decay, groups, shadow)
         self.epoch = 0
         self._set_epoch_flags()
+
+    def _make_optimizer(self, params, lr, weight_decay, groups, shadow):
+        """N > 1 ranks: arenas in peer-mapped memory, gradient exchange fused with Adam over NVLink
+        (``dp_exchange="peer"``, default; csrc/dp_exchange.cu); ``"nccl"`` keeps the all-reduce + Adam pair.  If peer
+        memory cannot be set up (no cudaIpc between the ranks' devices) every rank falls back to NCCL together."""
+        if self.world_size_ > 1 and self.dp_exchange_ == "peer":
+            import torch.distributed as dist
+            opt, ok = None, 1
+            try:
+                opt = FlatAdam(params, lr=lr, weight_decay=weight_decay, groups=groups, bf16_shadow=shadow,
+                               peer_group=True, peer_ctas=self.dp_exchange_ctas_)
+            except Exception as e:                                      # noqa: BLE001
+                warnings.warn(f"rank {self.rank_}: peer-memory gradient exchange unavailable ({e}); using NCCL")
+                ok = 0
+            flag = torch.tensor([ok], device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 1:
+                return opt
+            self.dp_exchange_ = "nccl"
+        return FlatAdam(params, lr=lr, weight_decay=weight_decay, groups=groups, bf16_shadow=shadow)
 
     def _epoch_logs_from(self, acc: dict):
         """Mean of the per-iteration losses (train/trainer.py:437-445); one read-back per epoch."""

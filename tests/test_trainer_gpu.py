@@ -338,3 +338,43 @@ def test_query_fine_tuning_with_a_new_covariate_category(tmp_path):
             assert torch.equal(tuned[k], v), k                      # frozen
     lat = loaded.get_latent_representation(adata=query, cat_covariates_keys=["batch"], only_active_gps=False)
     assert lat.shape == (240, 16) and np.isfinite(lat).all()
+
+
+@pytest.mark.parametrize("dtype,use_active", [(torch.float32, False), (torch.bfloat16, False), (torch.float32, True)])
+def test_cuda_graph_iterations_equal_eager_iterations(dtype, use_active):
+    """The captured-and-replayed iteration (size buckets with padding rows, device-side Adam step counter, noise drawn
+    into static buffers) against the eager iteration on the same batches and the same generator state: same losses
+    every iteration and the same parameters after eight updates, up to the order of float atomics."""
+    from nichecompass_b200.train import Trainer
+    adata = H.tiny_problem(n_cells=600, n_genes=44, n_prior_gp=12)
+    cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=4)
+    p32 = init_params(cfg, seed=3)
+
+    def run(graphs):
+        with contextlib.redirect_stdout(io.StringIO()):
+            tr = Trainer(adata, _module(cfg, p32), edge_batch_size=32, seed=0, monitor=False, compute_dtype=dtype,
+                         cuda_graphs=graphs)
+            tr.setup_training(lr=1e-3, n_epochs_all_gps=0 if use_active else 25, **LAM)
+        torch.manual_seed(11)
+        torch.cuda.manual_seed(11)
+        logs = []
+        for i, (eb, nb) in enumerate(tr.joint_batches(tr.edge_train_loader, tr.node_train_loader)):
+            logs.append({k: float(v) for k, v in tr.train_iteration(eb, nb).items()})
+            if i + 1 == 8:
+                break
+        return tr, logs
+    tr_e, eager = run(False)
+    tr_g, graph = run(True)
+    assert tr_e.graph_stats_["replayed"] == 0
+    assert tr_g.graph_stats_["replayed"] >= 5 and tr_g.graph_stats_["captured"] >= 1, tr_g.graph_stats_
+    tol = 2e-6 if dtype == torch.float32 else 2e-3
+    for it, (a, b) in enumerate(zip(graph, eager)):
+        for k in b:
+            assert abs(a[k] - b[k]) <= tol * abs(b[k]) * (1 + it) + 1e-10, (it, k, a[k], b[k])
+    if dtype == torch.float32:
+        sd_e, sd_g = tr_e.model.state_dict(), tr_g.model.state_dict()
+        for k in sd_e:
+            if sd_e[k].is_floating_point():
+                assert float((sd_e[k] - sd_g[k]).abs().max()) <= 2e-3 * 8 * 1e-3 + 1e-6 * float(sd_e[k].abs().max()) + 1e-3 * 2 * 8, k
+        assert tr_g.optimizer.step_count == tr_e.optimizer.step_count == 8
+        assert abs(float(tr_g.optimizer.dyn[1]) - 9.0) < 1e-6
