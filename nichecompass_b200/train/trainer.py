@@ -285,40 +285,96 @@ class Trainer(BaseTrainerMixin):
                 and edge_batch.edge_label_index.size(1) == 2 * int(self.edge_batch_size_)
                 and getattr(edge_batch, "_joint_input", None) is None)
 
+    def _bucket_sizes(self, node_batch, edge_batch):
+        gn, ge = node_batch.graph, edge_batch.graph
+        B4 = 4 * int(self.edge_batch_size_)
+        n_sub_pad = (gn.n_nodes + ge.n_nodes + (B4 - ge.n_dst) + 255) // 256 * 256
+        e_pad = (max(gn.e_dst + ge.e_dst, 1) + 1023) // 1024 * 1024
+        return B4, n_sub_pad, e_pad
+
+    def _graph_inputs(self, node_batch, edge_batch, out, background: bool):
+        """Parameter-free inputs of one iteration into ``out`` (a bucket's static buffers, or look-ahead staging
+        buffers): padded merge of the two sub-graphs, label rows, aggregated neighbour labels and -- for a count
+        store in host memory -- the encoder input rows."""
+        from .. import ops
+        from .._lib import call
+        from ..ops import pad8
+        m = self.model
+        gn, ge = node_batch.graph, edge_batch.graph
+        nb = int(self.node_batch_size_)
+        store = node_batch.store
+        call("nc_merge_subgraphs_padded", gn.rowptr, gn.col, node_batch.n_id, gn.n_dst, gn.n_nodes, ge.rowptr, ge.col,
+             edge_batch.n_id, ge.n_dst, ge.n_nodes, out.B4, out.n_sub_pad, out.e_pad, out.m_rowptr, out.m_col, out.m_nid)
+        ops.csr_gather_rows(store, node_batch.n_id, nb, False, torch.float32, out=out.x_t, background=background)
+        m.rna_node_label_aggregator.forward_store(store, node_batch.n_id, gn, nb, out=out.x_n)
+        if out.x_enc is not None:
+            ops.csr_gather_rows(store, out.m_nid, out.n_sub_pad, m.log_variational_, m.compute_dtype,
+                                pad8(m.encoder.n_input), background=background, out=out.x_enc)
+
+    def _input_buffers(self, node_batch, edge_batch, B4, n_sub_pad, e_pad):
+        from ..ops import pad8
+        m, dev, store = self.model, self.device, node_batch.store
+        nb = int(self.node_batch_size_)
+        host = store.location == "host"
+        return SimpleNamespace(
+            B4=B4, n_sub_pad=n_sub_pad, e_pad=e_pad, n_dst_pad=nb + B4,
+            m_rowptr=torch.zeros(nb + B4 + 1, dtype=torch.int32, device=dev),
+            m_col=torch.zeros(e_pad, dtype=torch.int32, device=dev),
+            m_nid=torch.zeros(n_sub_pad, dtype=torch.int32, device=dev),
+            x_t=torch.zeros(nb, store.n_cols, dtype=torch.float32, device=dev),
+            x_n=torch.zeros(nb, store.n_cols, dtype=torch.float32, device=dev),
+            # host-resident count store: the encoder input is an INPUT of the captured iteration (its rows cross
+            # the host link one iteration ahead, on a side stream), not a gather inside it
+            x_enc=(torch.zeros(n_sub_pad, pad8(m.encoder.n_input), dtype=m.compute_dtype, device=dev)
+                   if host else None))
+
+    def stage_graph_inputs(self, node_batch, edge_batch, side: "torch.cuda.Stream"):
+        """Look-ahead for the captured iteration: the inputs of iteration k + 1 are built on ``side`` while iteration
+        k replays (``_staged_pairs``); ``_graph_iteration`` then copies them device-to-device into the bucket."""
+        B4, n_sub_pad, e_pad = self._bucket_sizes(node_batch, edge_batch)
+        main = torch.cuda.current_stream()
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            t = self._input_buffers(node_batch, edge_batch, B4, n_sub_pad, e_pad)
+            self._graph_inputs(node_batch, edge_batch, t, background=True)
+            ev = torch.cuda.Event()
+            ev.record(side)
+        cached = [x for v in node_batch.graph._norm.values() for x in v if x is not None]
+        for x in [t.m_rowptr, t.m_col, t.m_nid, t.x_t, t.x_n] + ([t.x_enc] if t.x_enc is not None else []) + cached:
+            x.record_stream(main)
+        edge_batch._graph_staged = (t, ev)
+
     def _graph_iteration(self, node_batch, edge_batch):
         from .. import _lib, ops
         from .._lib import call
         from ..functional import SubgraphCSR
         m, opt = self.model, self.optimizer
-        gn, ge = node_batch.graph, edge_batch.graph
-        a_seed, a_sub, b_seed, b_sub = gn.n_dst, gn.n_nodes, ge.n_dst, ge.n_nodes
-        nb, B4 = int(self.node_batch_size_), 4 * int(self.edge_batch_size_)
-        pad = B4 - b_seed
-        n_sub_pad = (a_sub + b_sub + pad + 255) // 256 * 256
-        e_pad = (max(gn.e_dst + ge.e_dst, 1) + 1023) // 1024 * 1024
-        key = (n_sub_pad, e_pad, bool(self.use_only_active_gps), bool(self.edge_recon_active),
+        B4, n_sub_pad, e_pad = self._bucket_sizes(node_batch, edge_batch)
+        store = node_batch.store
+        key = (n_sub_pad, e_pad, store.location, bool(self.use_only_active_gps), bool(self.edge_recon_active),
                bool(self.cat_covariates_contrastive_active), float(self.grad_clip_value_))
         S = self._graph_buckets.get(key)
-        store = node_batch.store
         if S is None:
             dev = self.device
             P = m.n_prior_gp_ + m.n_addon_gp_
             eli = edge_batch.edge_label_index
-            S = self._graph_buckets[key] = SimpleNamespace(
-                n_sub_pad=n_sub_pad, e_pad=e_pad, n_dst_pad=a_seed + B4, graph=None, losses=None, n_launches=0, uses=0,
-                m_rowptr=torch.zeros(a_seed + B4 + 1, dtype=torch.int32, device=dev),
-                m_col=torch.zeros(e_pad, dtype=torch.int32, device=dev),
-                m_nid=torch.zeros(n_sub_pad, dtype=torch.int32, device=dev),
-                x_t=torch.zeros(nb, store.n_cols, dtype=torch.float32, device=dev),
-                x_n=torch.zeros(nb, store.n_cols, dtype=torch.float32, device=dev),
-                eli=torch.zeros_like(eli), elab=torch.zeros_like(edge_batch.edge_label),
-                eps_n=torch.zeros(nb, P, dtype=torch.float32, device=dev),
-                eps_e=torch.zeros(eli.size(1) * 2, P, dtype=torch.float32, device=dev))
+            nb = int(self.node_batch_size_)
+            S = self._graph_buckets[key] = self._input_buffers(node_batch, edge_batch, B4, n_sub_pad, e_pad)
+            S.graph, S.losses, S.n_launches, S.uses = None, None, 0, 0
+            S.eli, S.elab = torch.zeros_like(eli), torch.zeros_like(edge_batch.edge_label)
+            S.eps_n = torch.zeros(nb, P, dtype=torch.float32, device=dev)
+            S.eps_e = torch.zeros(eli.size(1) * 2, P, dtype=torch.float32, device=dev)
         # ---- per-iteration inputs (eager, a handful of launches)
-        call("nc_merge_subgraphs_padded", gn.rowptr, gn.col, node_batch.n_id, a_seed, a_sub, ge.rowptr, ge.col,
-             edge_batch.n_id, b_seed, b_sub, B4, n_sub_pad, e_pad, S.m_rowptr, S.m_col, S.m_nid)
-        ops.csr_gather_rows(store, node_batch.n_id, nb, False, torch.float32, out=S.x_t)
-        m.rna_node_label_aggregator.forward_store(store, node_batch.n_id, gn, nb, out=S.x_n)
+        staged = getattr(edge_batch, "_graph_staged", None)
+        if staged is not None and staged[0].n_sub_pad == n_sub_pad and staged[0].e_pad == e_pad:
+            t, ev = staged
+            edge_batch._graph_staged = None
+            torch.cuda.current_stream().wait_event(ev)
+            for name in ("m_rowptr", "m_col", "m_nid", "x_t", "x_n", "x_enc"):
+                if getattr(S, name) is not None:
+                    getattr(S, name).copy_(getattr(t, name))
+        else:
+            self._graph_inputs(node_batch, edge_batch, S, background=False)
         S.eli.copy_(edge_batch.edge_label_index)
         S.elab.copy_(edge_batch.edge_label)
         S.eps_n.normal_()                                  # same draws, same order as the eager path's randn_like
@@ -364,8 +420,8 @@ class Trainer(BaseTrainerMixin):
         m = self.model
         nb = int(self.node_batch_size_)
         gm = SubgraphCSR(S.m_rowptr, S.m_col, S.n_sub_pad, S.n_dst_pad, self._graph_max_deg(), e_dst=S.e_pad)
-        x_enc = ops.csr_gather_rows(store, S.m_nid, S.n_sub_pad, m.log_variational_, m.compute_dtype,
-                                    pad8(m.encoder.n_input))
+        x_enc = S.x_enc if S.x_enc is not None else ops.csr_gather_rows(
+            store, S.m_nid, S.n_sub_pad, m.log_variational_, m.compute_dtype, pad8(m.encoder.n_input))
         node_b = SimpleNamespace(store=store, batch_size=nb, n_id=None, graph=SimpleNamespace(n_dst=nb, n_nodes=nb))
         edge_b = SimpleNamespace(store=store, edge_label_index=S.eli, edge_label=S.elab, n_id=None,
                                  graph=SimpleNamespace(n_dst=S.n_dst_pad - nb, n_nodes=S.n_sub_pad - nb))
@@ -434,7 +490,9 @@ class Trainer(BaseTrainerMixin):
         side = self._side_streams[2]
         prev = None
         for eb, nb in pairs:
-            if self.model.training and self.model.joint_supported(nb, eb):
+            if self._graph_eligible(nb, eb):
+                self.stage_graph_inputs(nb, eb, side)
+            elif self.model.training and self.model.joint_supported(nb, eb):
                 self.model.stage_joint_input(nb, eb, side)
             if prev is not None:
                 yield prev

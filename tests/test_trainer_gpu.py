@@ -340,8 +340,9 @@ def test_query_fine_tuning_with_a_new_covariate_category(tmp_path):
     assert lat.shape == (240, 16) and np.isfinite(lat).all()
 
 
-@pytest.mark.parametrize("dtype,use_active", [(torch.float32, False), (torch.bfloat16, False), (torch.float32, True)])
-def test_cuda_graph_iterations_equal_eager_iterations(dtype, use_active):
+@pytest.mark.parametrize("dtype,use_active,store", [(torch.float32, False, "device"), (torch.bfloat16, False, "device"),
+                                                    (torch.float32, True, "device"), (torch.float32, False, "host")])
+def test_cuda_graph_iterations_equal_eager_iterations(dtype, use_active, store):
     """The captured-and-replayed iteration (size buckets with padding rows, device-side Adam step counter, noise drawn
     into static buffers) against the eager iteration on the same batches and the same generator state: same losses
     every iteration and the same parameters after eight updates, up to the order of float atomics."""
@@ -353,7 +354,7 @@ def test_cuda_graph_iterations_equal_eager_iterations(dtype, use_active):
     def run(graphs):
         with contextlib.redirect_stdout(io.StringIO()):
             tr = Trainer(adata, _module(cfg, p32), edge_batch_size=32, seed=0, monitor=False, compute_dtype=dtype,
-                         cuda_graphs=graphs)
+                         cuda_graphs=graphs, store_location=store)
             tr.setup_training(lr=1e-3, n_epochs_all_gps=0 if use_active else 25, **LAM)
         torch.manual_seed(11)
         torch.cuda.manual_seed(11)
