@@ -422,7 +422,9 @@ def timed(tr, it, steps, world, read_loss=False):
     barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    t0 = time.perf_counter()
     losses = run_steps(tr, it, steps, read_loss)
+    timed.last_host_ms = (time.perf_counter() - t0) * 1e3 / max(steps, 1)      # enqueue time: no device wait inside
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
@@ -492,6 +494,7 @@ def run_ours(args):
         clocks.start()
     n0 = _lib.launch_count()
     ms_total, _ = timed(tr, it, args.steps, world)
+    host_ms = timed.last_host_ms
     launches = _lib.launch_count() - n0
     clock_info = clocks.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
@@ -558,6 +561,7 @@ def run_ours(args):
             "parallelism_note": (f"dp{world} over the batch stream, flat-gradient exchange over NVLink" if world > 1
                                  else "single GPU"),
             "clocks": clock_info, "e2e": e2e, "gpu_launches": int(launches),
+            "host_enqueue_ms_per_step": host_ms, "cuda_graphs": dict(tr.graph_stats_),
             "roofline": roofline, "kernels": kernels,
         }
     return result, (adata, wl, tr, rank, world)

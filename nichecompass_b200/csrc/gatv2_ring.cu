@@ -26,17 +26,20 @@
 extern void nc_count_launch(int n);
 
 namespace {
-constexpr int RW_MAX = 8;            // warps per CTA
+constexpr int RW_MAX = 8;            // consumer warps per CTA (two warpgroups)
+// 8 consumer warps + one producer warpgroup (1 working warp, 3 that only hand their registers over):
+// setmaxnreg moves the register file from the producer group (40 per thread) to the consumers (232 per thread)
+constexpr int RING_THREADS = (RW_MAX + 4) * 32;
 constexpr int RS_MAX = 16;           // ring stages per warp
 constexpr int K_NBR = 0, K_XR = 1, K_LAST = 256;
 constexpr int SMEM_MAX = 227 * 1024;
 
 // element offset in the row, C / 4, output column, c * H + h; copy window of the segment inside a row
 // (16-byte aligned superset, in bytes) and the byte offset of the segment's first element inside the stage
-struct RingSeg { int off, C4, out_off, ch, win_start, win_bytes, st_off; };
+struct RingSeg { int off, C4, out_off, ch, st_off; };   // st_off: byte offset of the segment inside a row
 struct RingPlan {
     RingSeg a[RW_MAX], b[RW_MAX];                  // b[w].C4 == 0: warp w has one segment only
-    int n_warps, NL, n_stages, stage_bytes, warp_bytes, NCH, out_width, max_deg1, meta_off, bar_off, sc_off;
+    int n_warps, NL, n_stages, stage_bytes, row_bytes, sc_stride, NCH, out_width, max_deg1, meta_off, bar_off, sc_off;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -81,19 +84,26 @@ __device__ __forceinline__ uint2 pack_bf4(float4 v) {
 }
 __device__ __forceinline__ float lrelu(float v, float slope) { return fmaxf(v, v * slope); }   // 0 < slope < 1
 
-// ---------------------------------------------------------------------------------- per-warp pipeline
-// Producer cursor of one warp: enumerates, for the targets ir = blockIdx.x, + gridDim.x, ..., the rows
-// [x_r[ir] | x_l[j] for every CSR entry j != i | x_l[i]] and starts the copy of the warp's slice of the next
-// one.  The CSR range / first 32 column ids of the NEXT target are fetched one target ahead.
+// ---------------------------------------------------------------------------------- CTA pipeline
+// One producer warp per CTA enumerates, for the targets ir = blockIdx.x, + gridDim.x, ..., the rows
+// [x_r[ir] | x_l[j] for every CSR entry j != i | x_l[i]] and copies each WHOLE row (all segments, one bulk copy)
+// into the next free stage of a shared-memory ring; the consumer warps wait on the stage's full barrier, pull
+// their segments into registers and arrive on its empty barrier.  (First version: every consumer warp ran its own
+// cursor and its own ring -- ~300 instructions of bookkeeping per row and warp, 40 % of all instructions issued.)
+// The CSR range / first 32 column ids of the NEXT target are fetched one target ahead.
 struct Cursor {
     int ir, e0, e1, t, cbase, jv;
     int ne0, ne1, njv;
 };
-struct WarpRing {
+struct Ring {
     uint8_t* base;       // n_stages * stage_bytes
     int4* meta;          // [n_stages]: {kind | flags, ir, slot, t}
     uint64_t* full;      // [n_stages]
+    uint64_t* empty;     // [n_stages]
 };
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 
 __device__ __forceinline__ void cur_fetch(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, int ir,
                                           int n_dst, int dst_off, int lane, int& e0, int& e1, int& jv) {
@@ -113,13 +123,12 @@ __device__ __forceinline__ void cur_init(Cursor& c, const int32_t* rowptr, const
     cur_fetch(rowptr, col, c.ir + (int)gridDim.x, n_dst, dst_off, lane, c.ne0, c.ne1, c.njv);
 }
 
-// Starts the copy of the next row of the sequence into stage `ps` (all lanes call; lane 0 issues).
+// Producer warp: starts the copy of the next row of the sequence into stage `ps` (all lanes call; lane 0 issues).
 // Returns false when the sequence is exhausted.
-__device__ __forceinline__ bool issue_next(Cursor& c, const WarpRing& R, const RingPlan& P, const RingSeg& sa,
-                                           const RingSeg& sb, uint32_t ps, const __nv_bfloat16* __restrict__ xl,
-                                           const __nv_bfloat16* __restrict__ xr, int64_t ld,
-                                           const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
-                                           int n_dst, int dst_off, int lane) {
+__device__ __forceinline__ bool issue_next(Cursor& c, const Ring& R, const RingPlan& P, uint32_t ps,
+                                           const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __restrict__ xr,
+                                           int64_t ld, const int32_t* __restrict__ rowptr,
+                                           const int32_t* __restrict__ col, int n_dst, int dst_off, int lane) {
     const __nv_bfloat16* src;
     int4 meta;
     while (true) {
@@ -153,36 +162,61 @@ __device__ __forceinline__ bool issue_next(Cursor& c, const WarpRing& R, const R
         break;
     }
     if (lane == 0) {
-        uint8_t* st = R.base + (size_t)ps * P.stage_bytes;
         R.meta[ps] = meta;
-        // the warp's generic-proxy reads of this slot (ordered before this point by __syncwarp) must not be
-        // overtaken by the async-proxy write
+        // the consumers' generic-proxy reads of this stage (ordered before this point by their arrivals on the
+        // empty barrier) must not be overtaken by the async-proxy write
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(&R.full[ps], (uint32_t)(sa.win_bytes + sb.win_bytes));
-        const uint8_t* s8 = reinterpret_cast<const uint8_t*>(src);
-        bulk_load(st, s8 + sa.win_start, (uint32_t)sa.win_bytes, &R.full[ps]);
-        if (sb.win_bytes) bulk_load(st + sa.win_bytes, s8 + sb.win_start, (uint32_t)sb.win_bytes, &R.full[ps]);
+        mbar_expect_tx(&R.full[ps], (uint32_t)P.row_bytes);
+        bulk_load(R.base + (size_t)ps * P.stage_bytes, src, (uint32_t)P.row_bytes, &R.full[ps]);
     }
     return true;
 }
 
-__device__ __forceinline__ WarpRing ring_setup(const RingPlan& P, uint8_t* smem, int warp, int lane) {
-    WarpRing R;
-    uint8_t* wb = smem + (size_t)warp * P.warp_bytes;
-    R.base = wb;
-    R.meta = reinterpret_cast<int4*>(wb + P.meta_off);
-    R.full = reinterpret_cast<uint64_t*>(wb + P.bar_off);
-    if (lane == 0) {
-        for (int s = 0; s < P.n_stages; ++s) mbar_init(&R.full[s], 1);
+// All threads of the CTA call; barriers initialised by thread 0.
+__device__ __forceinline__ Ring ring_setup(const RingPlan& P, uint8_t* smem) {
+    Ring R;
+    R.base = smem;
+    R.meta = reinterpret_cast<int4*>(smem + P.meta_off);
+    R.full = reinterpret_cast<uint64_t*>(smem + P.bar_off);
+    R.empty = R.full + P.n_stages;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < P.n_stages; ++s) {
+            mbar_init(&R.full[s], 1);
+            mbar_init(&R.empty[s], (uint32_t)P.n_warps);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    __syncwarp();
+    __syncthreads();
     return R;
 }
 
+// The producer warp's whole life: fill stages round-robin, waiting for a stage to be drained before reuse.
+__device__ __forceinline__ void producer_loop(const Ring& R, const RingPlan& P, const __nv_bfloat16* __restrict__ xl,
+                                              const __nv_bfloat16* __restrict__ xr, int64_t ld,
+                                              const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
+                                              int n_dst, int dst_off, int lane) {
+    Cursor cur;
+    cur_init(cur, rowptr, col, n_dst, dst_off, lane);
+    uint32_t stage = 0, round = 0;
+    while (true) {
+        mbar_wait(&R.empty[stage], (round & 1) ^ 1);                 // passes at once in the first round
+        if (!issue_next(cur, R, P, stage, xl, xr, ld, rowptr, col, n_dst, dst_off, lane)) break;
+        if (++stage == (uint32_t)P.n_stages) { stage = 0; ++round; }
+    }
+}
+
 // ---------------------------------------------------------------------------------- forward
+// Instruction diet of the inner loop (the first version of this kernel issued 15 instructions per row element and
+// was bound by issue slots -- 2 warps per scheduler, IPC 0.5 -- not by memory; ncu: profiles/r2_gatv2_*):
+//   * leaky_relu(v) = c1 v + c2 |v| with c1 = (1 + slope) / 2, c2 = (1 - slope) / 2, so the score is
+//     c1 <att, x_l[j]> + c2 <att, |x_l[j] + x_r[i]|> (+ c1 <att, x_r[i]>, which is the same for every neighbour of i
+//     and cancels in the softmax): one add and two fused multiply-adds per element (|.| is an operand modifier),
+//     instead of add, multiply, max, multiply-add;
+//   * x_r[i] and att live in registers as fp32 for the whole target (no re-unpacking per row);
+//   * lanes past the end of a segment read the first element of the slot (valid data) with att = 0 instead of
+//     branching around every 128-bit chunk.
 template <int NVA, int NVB>
-__global__ void __launch_bounds__(RW_MAX * 32, 1)
+__global__ void __launch_bounds__(RING_THREADS, 1)
 k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restrict__ xl,
                const __nv_bfloat16* __restrict__ xr, int64_t ld, const float* __restrict__ att,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, int n_dst, int dst_off, float slope,
@@ -190,34 +224,42 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
     constexpr int NV = NVA + NVB;
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp >= P.n_warps) return;
     int n_left = (n_dst > (int)blockIdx.x) ? (n_dst - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     if (n_left == 0) return;
-    const WarpRing R = ring_setup(P, smem, warp, lane);
+    const Ring R = ring_setup(P, smem);
+    if (warp >= RW_MAX) {                                     // producer warpgroup: warp 8 works, 9..11 only donate
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == RW_MAX) producer_loop(R, P, xl, xr, ld, rowptr, col, n_dst, dst_off, lane);
+        return;
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const RingSeg sa = P.a[warp], sb = P.b[warp];
-    const uint32_t offA = (uint32_t)(sa.st_off + 8 * lane), offB = (uint32_t)(sb.st_off + 8 * lane);
+    const float c1 = 0.5f * (1.0f + slope), c2 = 0.5f * (1.0f - slope);
     uint32_t vmask = 0;
+    // offS: a valid, 8-byte aligned element of the slot for the lanes past the end of a segment
+    const uint32_t offA = (uint32_t)(sa.st_off + 8 * lane), offB = (uint32_t)(sb.st_off + 8 * lane), offS = (uint32_t)sa.st_off;
     float4 attv[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
         const bool isA = k < NVA;
-        const int u = lane + 32 * (isA ? k : k - NVA);
+        const int kk = isA ? k : k - NVA;
+        const int u = lane + 32 * kk;
         attv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (u < (isA ? sa.C4 : sb.C4)) {
             vmask |= 1u << k;
             attv[k] = __ldg(reinterpret_cast<const float4*>(att + (isA ? sa.off : sb.off) + 4 * u));
         }
     }
-    float* scA = reinterpret_cast<float*>(smem + (size_t)warp * P.warp_bytes + P.sc_off);
+#define BOFF(k) ((((vmask) >> (k)) & 1u) ? ((k) < NVA ? offA + 256u * (uint32_t)(k) : offB + 256u * (uint32_t)((k) - NVA)) : offS)
+    float* scA = reinterpret_cast<float*>(smem + P.sc_off + (size_t)warp * P.sc_stride);
     float* scB = scA + P.max_deg1;
-    Cursor cur;
-    cur_init(cur, rowptr, col, n_dst, dst_off, lane);
-    for (int s = 0; s < P.n_stages; ++s)
-        if (!issue_next(cur, R, P, sa, sb, (uint32_t)s, xl, xr, ld, rowptr, col, n_dst, dst_off, lane)) break;
-    uint2 xrv[NV];
-    float4 acc[NV];
+    if (alpha) {
+        for (int t = lane; t < P.max_deg1; t += 32) { scA[t] = -INFINITY; scB[t] = -INFINITY; }
+        __syncwarp();
+    }
+    float4 xrv[NV], acc[NV];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) { xrv[k] = make_uint2(0u, 0u); acc[k] = make_float4(0.f, 0.f, 0.f, 0.f); }
+    for (int k = 0; k < NV; ++k) { xrv[k] = make_float4(0.f, 0.f, 0.f, 0.f); acc[k] = make_float4(0.f, 0.f, 0.f, 0.f); }
     float mA = -INFINITY, lA = 0.f, mB = -INFINITY, lB = 0.f;
     int slot0 = 0, nE = 0;
     uint32_t stage = 0, round = 0;
@@ -225,46 +267,41 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
         mbar_wait(&R.full[stage], round & 1);
         const uint8_t* row = R.base + (size_t)stage * P.stage_bytes;
         const int4 meta = R.meta[stage];
+        uint2 raw[NV];
+#pragma unroll
+        for (int k = 0; k < NV; ++k) raw[k] = *reinterpret_cast<const uint2*>(row + BOFF(k));
+        __syncwarp();                                        // the row now lives in registers: release the stage
+        if (lane == 0) mbar_arrive(&R.empty[stage]);
         if ((meta.x & 255) == K_XR) {
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                const uint32_t bo = (k < NVA ? offA : offB) + 256u * (uint32_t)(k < NVA ? k : k - NVA);
-                if ((vmask >> k) & 1u) xrv[k] = *reinterpret_cast<const uint2*>(row + bo);
+                xrv[k] = bf4(raw[k]);
                 acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            __syncwarp();
-            issue_next(cur, R, P, sa, sb, stage, xl, xr, ld, rowptr, col, n_dst, dst_off, lane);
             mA = mB = -INFINITY;
             lA = lB = 0.f;
             slot0 = meta.z;
             nE = min(meta.w, P.max_deg1);
-            if (alpha) {
-                for (int t = lane; t < nE; t += 32) { scA[t] = -INFINITY; scB[t] = -INFINITY; }
-                __syncwarp();
-            }
         } else {
-            uint2 raw[NV];
-            float pA = 0.f, pB = 0.f;
+            // (the row stays packed in `raw` and is unpacked again for the accumulation: 26 registers instead of 52)
+            float s1A = 0.f, s2A = 0.f, s1B = 0.f, s2B = 0.f;
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                const uint32_t bo = (k < NVA ? offA : offB) + 256u * (uint32_t)(k < NVA ? k : k - NVA);
-                raw[k] = make_uint2(0u, 0u);
-                if ((vmask >> k) & 1u) {
-                    raw[k] = *reinterpret_cast<const uint2*>(row + bo);
-                    const float4 f = bf4(raw[k]), x = bf4(xrv[k]);
-                    const float s = attv[k].x * lrelu(f.x + x.x, slope) + attv[k].y * lrelu(f.y + x.y, slope) +
-                                    attv[k].z * lrelu(f.z + x.z, slope) + attv[k].w * lrelu(f.w + x.w, slope);
-                    if (k < NVA) pA += s; else pB += s;
-                }
+                const float4 f = bf4(raw[k]);
+                const float4 a = attv[k], x = xrv[k];
+                float t1 = a.x * f.x, t2 = a.x * fabsf(f.x + x.x);
+                t1 = fmaf(a.y, f.y, t1); t2 = fmaf(a.y, fabsf(f.y + x.y), t2);
+                t1 = fmaf(a.z, f.z, t1); t2 = fmaf(a.z, fabsf(f.z + x.z), t2);
+                t1 = fmaf(a.w, f.w, t1); t2 = fmaf(a.w, fabsf(f.w + x.w), t2);
+                if (k < NVA) { s1A += t1; s2A += t2; } else { s1B += t1; s2B += t2; }
             }
-            __syncwarp();                                    // the row now lives in registers: refill its slot
-            issue_next(cur, R, P, sa, sb, stage, xl, xr, ld, rowptr, col, n_dst, dst_off, lane);
-            pA = warp_sum(pA);
-            if (NVB > 0) pB = warp_sum(pB);
+            float pA = warp_sum(fmaf(c1, s1A, c2 * s2A));
+            float pB = 0.f;
+            if (NVB > 0) pB = warp_sum(fmaf(c1, s1B, c2 * s2B));
             const int t = meta.w;
             if (alpha && lane == 0 && t < P.max_deg1) { scA[t] = pA; scB[t] = pB; }
             {
-                const float mn = fmaxf(mA, pA), corr = expf(mA - mn), w = expf(pA - mn);
+                const float mn = fmaxf(mA, pA), corr = __expf(mA - mn), w = __expf(pA - mn);
                 lA = lA * corr + w;
                 mA = mn;
                 if (corr != 1.f) {
@@ -274,18 +311,19 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
 #pragma unroll
                 for (int k = 0; k < NVA; ++k) {
                     const float4 f = bf4(raw[k]);
-                    acc[k].x += w * f.x; acc[k].y += w * f.y; acc[k].z += w * f.z; acc[k].w += w * f.w;
+                    acc[k].x = fmaf(w, f.x, acc[k].x); acc[k].y = fmaf(w, f.y, acc[k].y);
+                    acc[k].z = fmaf(w, f.z, acc[k].z); acc[k].w = fmaf(w, f.w, acc[k].w);
                 }
             }
             if (NVB > 0) {
-                const float mn = fmaxf(mB, pB), corr = expf(mB - mn), w = expf(pB - mn);
+                const float mn = fmaxf(mB, pB), corr = __expf(mB - mn), w = __expf(pB - mn);
                 lB = lB * corr + w;
                 mB = mn;
 #pragma unroll
                 for (int k = NVA; k < NV; ++k) {
                     const float4 f = bf4(raw[k]);
-                    acc[k].x = acc[k].x * corr + w * f.x; acc[k].y = acc[k].y * corr + w * f.y;
-                    acc[k].z = acc[k].z * corr + w * f.z; acc[k].w = acc[k].w * corr + w * f.w;
+                    acc[k].x = fmaf(w, f.x, acc[k].x * corr); acc[k].y = fmaf(w, f.y, acc[k].y * corr);
+                    acc[k].z = fmaf(w, f.z, acc[k].z * corr); acc[k].w = fmaf(w, f.w, acc[k].w * corr);
                 }
             }
             if (meta.x & K_LAST) {
@@ -306,9 +344,13 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
                     __syncwarp();
                     for (int tt = lane; tt < nE; tt += 32) {
                         float* al = alpha + (int64_t)(slot0 + tt) * P.NCH;
-                        al[sa.ch] = expf(scA[tt] - mA) * iA;
-                        if (sb.C4 > 0) al[sb.ch] = expf(scB[tt] - mB) * iB;
+                        // a removed self entry (PyG drops it, cursor skipped it) never got a score: alpha = 0
+                        const float sA = scA[tt], sB = scB[tt];
+                        al[sa.ch] = sA == -INFINITY ? 0.f : __expf(sA - mA) * iA;
+                        if (sb.C4 > 0) al[sb.ch] = sB == -INFINITY ? 0.f : __expf(sB - mB) * iB;
                     }
+                    __syncwarp();
+                    for (int tt = lane; tt < nE; tt += 32) { scA[tt] = -INFINITY; scB[tt] = -INFINITY; }
                     __syncwarp();
                 }
                 if (--n_left == 0) break;
@@ -317,6 +359,8 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
         if (++stage == (uint32_t)P.n_stages) { stage = 0; ++round; }
     }
 }
+
+#undef BOFF
 
 // out[ir, out_off_c + k] = mean_h O[ir, off_c + h * C_c + k] + bias   (one CTA per target)
 __global__ void __launch_bounds__(256)
@@ -365,7 +409,7 @@ k_gat_D(const float* __restrict__ head_out, int64_t ld, const float* __restrict_
 
 // ---------------------------------------------------------------------------------- backward, per target
 template <int NVA, int NVB>
-__global__ void __launch_bounds__(RW_MAX * 32, 1)
+__global__ void __launch_bounds__(RING_THREADS, 1)
 k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restrict__ xl,
                const __nv_bfloat16* __restrict__ xr, int64_t ld, const float* __restrict__ att,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, int n_dst, float slope,
@@ -375,22 +419,27 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
     constexpr int NV = NVA + NVB;
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp >= P.n_warps) return;
     int n_left = (n_dst > (int)blockIdx.x) ? (n_dst - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     if (n_left == 0) return;
-    const WarpRing R = ring_setup(P, smem, warp, lane);
+    const Ring R = ring_setup(P, smem);
+    if (warp >= RW_MAX) {                                     // producer warpgroup: warp 8 works, 9..11 only donate
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == RW_MAX) producer_loop(R, P, xl, xr, ld, rowptr, col, n_dst, 0, lane);
+        return;
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const RingSeg sa = P.a[warp], sb = P.b[warp];
-    const uint32_t offA = (uint32_t)(sa.st_off + 8 * lane), offB = (uint32_t)(sb.st_off + 8 * lane);
+    // lanes past the end of a segment read the first element of the slot (valid data) and carry g = 0: no branch
+    // around the 128-bit chunks (same diet as the forward kernel)
     uint32_t vmask = 0;
+    const uint32_t offA = (uint32_t)(sa.st_off + 8 * lane), offB = (uint32_t)(sb.st_off + 8 * lane), offS = (uint32_t)sa.st_off;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-        const int u = lane + 32 * (k < NVA ? k : k - NVA);
-        if (u < (k < NVA ? sa.C4 : sb.C4)) vmask |= 1u << k;
+        const bool isA = k < NVA;
+        const int u = lane + 32 * (isA ? k : k - NVA);
+        if (u < (isA ? sa.C4 : sb.C4)) vmask |= 1u << k;
     }
-    Cursor cur;
-    cur_init(cur, rowptr, col, n_dst, 0, lane);
-    for (int s = 0; s < P.n_stages; ++s)
-        if (!issue_next(cur, R, P, sa, sb, (uint32_t)s, xl, xr, ld, rowptr, col, n_dst, 0, lane)) break;
+#define BOFF(k) ((((vmask) >> (k)) & 1u) ? ((k) < NVA ? offA + 256u * (uint32_t)(k) : offB + 256u * (uint32_t)((k) - NVA)) : offS)
     float4 gv[NV], dxa[NV], dat[NV];
     uint2 xrv[NV];
 #pragma unroll
@@ -413,11 +462,10 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
             for (int k = 0; k < NV; ++k) {
                 const bool isA = k < NVA;
                 const int kk = isA ? k : k - NVA;
-                const uint32_t bo = (isA ? offA : offB) + 256u * (uint32_t)kk;
-                if ((vmask >> k) & 1u) {
-                    xrv[k] = *reinterpret_cast<const uint2*>(row + bo);
+                xrv[k] = *reinterpret_cast<const uint2*>(row + BOFF(k));
+                gv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if ((vmask >> k) & 1u)
                     gv[k] = __ldg(reinterpret_cast<const float4*>(g + (isA ? sa.out_off : sb.out_off) + 4 * (lane + 32 * kk)));
-                }
                 dxa[k] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
             DA = __ldg(Dbuf + (int64_t)ir * P.NCH + sa.ch);
@@ -428,18 +476,15 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
                 if (sb.C4 > 0) alB = __ldg(alpha + (int64_t)(slot0 + lane) * P.NCH + sb.ch);
             }
             __syncwarp();
-            issue_next(cur, R, P, sa, sb, stage, xl, xr, ld, rowptr, col, n_dst, 0, lane);
+            if (lane == 0) mbar_arrive(&R.empty[stage]);
         } else {
             // sweep 1: d alpha = <g, x_l[j, head]> / H
             float pA = 0.f, pB = 0.f;
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                const uint32_t bo = (k < NVA ? offA : offB) + 256u * (uint32_t)(k < NVA ? k : k - NVA);
-                if ((vmask >> k) & 1u) {
-                    const float4 f = bf4(*reinterpret_cast<const uint2*>(row + bo));
-                    const float s = f.x * gv[k].x + f.y * gv[k].y + f.z * gv[k].z + f.w * gv[k].w;
-                    if (k < NVA) pA += s; else pB += s;
-                }
+                const float4 f = bf4(*reinterpret_cast<const uint2*>(row + BOFF(k)));
+                const float s = fmaf(f.x, gv[k].x, fmaf(f.y, gv[k].y, fmaf(f.z, gv[k].z, f.w * gv[k].w)));
+                if (k < NVA) pA += s; else pB += s;
             }
             pA = warp_sum(pA);
             if (NVB > 0) pB = warp_sum(pB);
@@ -463,9 +508,8 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
             uint32_t w0 = 0u, w1 = 0u;
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                const uint32_t bo = (k < NVA ? offA : offB) + 256u * (uint32_t)(k < NVA ? k : k - NVA);
-                if ((vmask >> k) & 1u) {
-                    const float4 f = bf4(*reinterpret_cast<const uint2*>(row + bo)), x = bf4(xrv[k]);
+                {
+                    const float4 f = bf4(*reinterpret_cast<const uint2*>(row + BOFF(k))), x = bf4(xrv[k]);
                     const float d1 = k < NVA ? dsA : dsB, d0 = k < NVA ? dsAs : dsBs;
                     uint32_t bits = 0u;
                     float v, tt;
@@ -477,7 +521,7 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
                 }
             }
             __syncwarp();
-            issue_next(cur, R, P, sa, sb, stage, xl, xr, ld, rowptr, col, n_dst, 0, lane);
+            if (lane == 0) mbar_arrive(&R.empty[stage]);
             uint32_t* mrow = mask + ((int64_t)slot * RW_MAX + warp) * 64;
             mrow[lane] = w0;
             if (NV > 8) mrow[32 + lane] = w1;
@@ -509,94 +553,104 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
     }
 }
 
+#undef BOFF
+
 // ---------------------------------------------------------------------------------- backward, per source
 // d x_l[j] = sum over the out edges (j -> i, slot) of  alpha / H * g_i  +  d score * att * (bit ? 1 : slope).
 // Same warp <-> segment plan as the per-target kernel (the sign bits are stored per warp and lane).
 template <int NVA, int NVB>
-__global__ void __launch_bounds__(RW_MAX * 32)
+__global__ void __launch_bounds__(RW_MAX * 32, 1)
 k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__ att,
                    const int32_t* __restrict__ rptr, const int32_t* __restrict__ rdst,
                    const int32_t* __restrict__ rslot, float slope, float invH, const float* __restrict__ dout,
                    int64_t ldo, const float* __restrict__ alpha, const float* __restrict__ ds,
-                   const uint32_t* __restrict__ mask, __nv_bfloat16* __restrict__ dxl, int64_t ld) {
+                   const uint32_t* __restrict__ mask, __nv_bfloat16* __restrict__ dxl, int64_t ld, int n_src) {
+    // persistent CTAs striding over the sources: att stays in registers (it was re-read from L2 for every edge),
+    // the reverse-CSR range of the NEXT source is fetched while the current one is reduced
     constexpr int NV = NVA + NVB;
-    const int j = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (warp >= P.n_warps) return;
     const RingSeg sa = P.a[warp], sb = P.b[warp];
     uint32_t vmask = 0;
+    float4 attv[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-        const int u = lane + 32 * (k < NVA ? k : k - NVA);
-        if (u < (k < NVA ? sa.C4 : sb.C4)) vmask |= 1u << k;
+        const bool isA = k < NVA;
+        const int u = lane + 32 * (isA ? k : k - NVA);
+        attv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (u < (isA ? sa.C4 : sb.C4)) {
+            vmask |= 1u << k;
+            attv[k] = __ldg(reinterpret_cast<const float4*>(att + (isA ? sa.off : sb.off) + 4 * u));
+        }
     }
-    float4 acc[NV];
+    int j = blockIdx.x;
+    int p0 = 0, p1 = 0;
+    if (j < n_src) { p0 = __ldg(rptr + j); p1 = __ldg(rptr + j + 1); }
+    for (; j < n_src; j += (int)gridDim.x) {
+        const int jn = j + (int)gridDim.x;
+        int np0 = 0, np1 = 0;
+        if (jn < n_src) { np0 = __ldg(rptr + jn); np1 = __ldg(rptr + jn + 1); }
+        float4 acc[NV];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-    const int p0 = __ldg(rptr + j), p1 = __ldg(rptr + j + 1);
-    for (int p = p0; p < p1; ++p) {
-        const int i = __ldg(rdst + p), slot = __ldg(rslot + p);
-        const float* al = alpha + (int64_t)slot * P.NCH;
-        const float* dsl = ds + (int64_t)slot * P.NCH;
-        const float aA = __ldg(al + sa.ch) * invH, dA = __ldg(dsl + sa.ch);
-        const float aB = (sb.C4 > 0) ? __ldg(al + sb.ch) * invH : 0.f, dB = (sb.C4 > 0) ? __ldg(dsl + sb.ch) : 0.f;
-        const uint32_t* mrow = mask + ((int64_t)slot * RW_MAX + warp) * 64;
-        const uint32_t w0 = __ldg(mrow + lane);
-        const uint32_t w1 = (NV > 8) ? __ldg(mrow + 32 + lane) : 0u;
-        const float* g = dout + (int64_t)i * ldo;
-        const float dAs = dA * slope, dBs = dB * slope;
+        for (int k = 0; k < NV; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int p = p0; p < p1; ++p) {
+            const int i = __ldg(rdst + p), slot = __ldg(rslot + p);
+            const float* al = alpha + (int64_t)slot * P.NCH;
+            const float* dsl = ds + (int64_t)slot * P.NCH;
+            const float aA = __ldg(al + sa.ch) * invH, dA = __ldg(dsl + sa.ch);
+            const float aB = (sb.C4 > 0) ? __ldg(al + sb.ch) * invH : 0.f, dB = (sb.C4 > 0) ? __ldg(dsl + sb.ch) : 0.f;
+            const uint32_t* mrow = mask + ((int64_t)slot * RW_MAX + warp) * 64;
+            const uint32_t w0 = __ldg(mrow + lane);
+            const uint32_t w1 = (NV > 8) ? __ldg(mrow + 32 + lane) : 0u;
+            const float* g = dout + (int64_t)i * ldo;
+            const float dAs = dA * slope, dBs = dB * slope;
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                const bool isA = k < NVA;
+                const int u = lane + 32 * (isA ? k : k - NVA);
+                float4 gg = make_float4(0.f, 0.f, 0.f, 0.f);
+                if ((vmask >> k) & 1u)
+                    gg = __ldg(reinterpret_cast<const float4*>(g + (isA ? sa.out_off : sb.out_off) + 4 * u));
+                const float4 a = attv[k];
+                const uint32_t bits = ((k < 8) ? w0 : w1) >> (4 * (k & 7));
+                const float aw = isA ? aA : aB, d1 = isA ? dA : dB, d0 = isA ? dAs : dBs;
+                acc[k].x = fmaf(aw, gg.x, fmaf((bits & 1u) ? d1 : d0, a.x, acc[k].x));
+                acc[k].y = fmaf(aw, gg.y, fmaf((bits & 2u) ? d1 : d0, a.y, acc[k].y));
+                acc[k].z = fmaf(aw, gg.z, fmaf((bits & 4u) ? d1 : d0, a.z, acc[k].z));
+                acc[k].w = fmaf(aw, gg.w, fmaf((bits & 8u) ? d1 : d0, a.w, acc[k].w));
+            }
+        }
+        __nv_bfloat16* drow = dxl + (int64_t)j * ld;
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
             if ((vmask >> k) & 1u) {
                 const bool isA = k < NVA;
-                const int u = lane + 32 * (isA ? k : k - NVA);
-                const float4 gg = __ldg(reinterpret_cast<const float4*>(g + (isA ? sa.out_off : sb.out_off) + 4 * u));
-                const float4 a = __ldg(reinterpret_cast<const float4*>(att + (isA ? sa.off : sb.off) + 4 * u));
-                const uint32_t bits = ((k < 8) ? w0 : w1) >> (4 * (k & 7));
-                const float aw = isA ? aA : aB, d1 = isA ? dA : dB, d0 = isA ? dAs : dBs;
-                acc[k].x += aw * gg.x + ((bits & 1u) ? d1 : d0) * a.x;
-                acc[k].y += aw * gg.y + ((bits & 2u) ? d1 : d0) * a.y;
-                acc[k].z += aw * gg.z + ((bits & 4u) ? d1 : d0) * a.z;
-                acc[k].w += aw * gg.w + ((bits & 8u) ? d1 : d0) * a.w;
+                const int e = (isA ? sa.off : sb.off) + 4 * (lane + 32 * (isA ? k : k - NVA));
+                *reinterpret_cast<uint2*>(drow + e) = pack_bf4(acc[k]);
             }
         }
-    }
-    __nv_bfloat16* drow = dxl + (int64_t)j * ld;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        if ((vmask >> k) & 1u) {
-            const bool isA = k < NVA;
-            const int e = (isA ? sa.off : sb.off) + 4 * (lane + 32 * (isA ? k : k - NVA));
-            *reinterpret_cast<uint2*>(drow + e) = pack_bf4(acc[k]);
-        }
+        p0 = np0; p1 = np1;
     }
 }
 
 // ---------------------------------------------------------------------------------- host side
 struct RingCfg { RingPlan P; int nva, nvb; size_t smem; };
 
-void seg_window(RingSeg& s) {
-    if (s.C4 == 0) { s.win_start = s.win_bytes = s.st_off = 0; return; }
-    const int b0 = s.off * 2, b1 = (s.off + 4 * s.C4) * 2;
-    s.win_start = b0 / 16 * 16;
-    s.win_bytes = (b1 + 15) / 16 * 16 - s.win_start;
-    s.st_off = b0 - s.win_start;
-}
-
 // Builds the warp <-> segment plan; false when the shape is not one the ring kernels take.
 // fwd: the per-warp score arrays (attention logits of one target) live in shared memory as well.
 bool ring_plan(const int32_t* seg_host, int n_conv, int H, int64_t ld, int max_deg, bool fwd, RingCfg& cfg) {
     const int S = n_conv * H;
-    if (S < 1 || S > 2 * RW_MAX || ld % 8 != 0 || max_deg < 0) return false;
+    if (S < RW_MAX || S > 2 * RW_MAX || ld % 8 != 0 || max_deg < 0) return false;   // all 8 consumer warps busy
     RingSeg segs[2 * RW_MAX];
     int NL = 0, ow = 0;
     for (int c = 0; c < n_conv; ++c) {
         const int off = seg_host[c * 4], C = seg_host[c * 4 + 1], oo = seg_host[c * 4 + 2];
         if (C <= 0 || C % 4 != 0 || off % 4 != 0 || oo % 4 != 0 || off < 0 || oo < 0) return false;
-        for (int h = 0; h < H; ++h) segs[c * H + h] = RingSeg{off + h * C, C / 4, oo, c * H + h, 0, 0, 0};
+        for (int h = 0; h < H; ++h) segs[c * H + h] = RingSeg{off + h * C, C / 4, oo, c * H + h, (off + h * C) * 2};
         NL = off + H * C > NL ? off + H * C : NL;
         ow = oo + C > ow ? oo + C : ow;
     }
-    if (NL % 8 != 0 || NL > ld) return false;                // every copy window stays inside the row
+    if (NL % 8 != 0 || NL > ld) return false;                // the row copy is a multiple of 16 bytes inside the row
     for (int a = 1; a < S; ++a) {                            // stable insertion sort, longest segment first
         RingSeg key = segs[a];
         int b = a - 1;
@@ -605,20 +659,15 @@ bool ring_plan(const int32_t* seg_host, int n_conv, int H, int64_t ld, int max_d
     }
     RingPlan& P = cfg.P;
     P.n_warps = S < RW_MAX ? S : RW_MAX;
-    int maxA = 0, maxB = 0, stage = 0;
+    int maxA = 0, maxB = 0;
     for (int w = 0; w < RW_MAX; ++w) {
-        P.a[w] = RingSeg{0, 0, 0, 0, 0, 0, 0};
-        P.b[w] = RingSeg{0, 0, 0, 0, 0, 0, 0};
+        P.a[w] = RingSeg{0, 0, 0, 0, 0};
+        P.b[w] = RingSeg{0, 0, 0, 0, 0};
         if (w >= P.n_warps) continue;
         P.a[w] = segs[w];
         if (S - 1 - w >= RW_MAX) P.b[w] = segs[S - 1 - w];
-        seg_window(P.a[w]);
-        seg_window(P.b[w]);
-        P.b[w].st_off += P.a[w].win_bytes;                   // the second window follows the first in a stage
         maxA = P.a[w].C4 > maxA ? P.a[w].C4 : maxA;
         maxB = P.b[w].C4 > maxB ? P.b[w].C4 : maxB;
-        const int sb = P.a[w].win_bytes + P.b[w].win_bytes;
-        stage = sb > stage ? sb : stage;
     }
     const int nva = (maxA + 31) / 32, nvb = (maxB + 31) / 32;
     cfg.nva = nva <= 4 ? 4 : (nva <= 12 ? 12 : 0);
@@ -628,24 +677,21 @@ bool ring_plan(const int32_t* seg_host, int n_conv, int H, int64_t ld, int max_d
     P.NCH = S;
     P.out_width = ow;
     P.max_deg1 = max_deg + 1;
-    P.stage_bytes = (stage + 127) / 128 * 128;
-    const int sc_bytes = fwd ? ((2 * P.max_deg1 * 4 + 15) / 16 * 16) : 0;
-    const int per_stage = P.stage_bytes + 16 + 8;            // data + meta + barrier
-    const int budget = SMEM_MAX / P.n_warps / 128 * 128 - sc_bytes - 128;
-    const int ns = budget / per_stage;
+    P.row_bytes = NL * 2;
+    P.stage_bytes = (P.row_bytes + 127) / 128 * 128;
+    P.sc_stride = fwd ? ((2 * P.max_deg1 * 4 + 15) / 16 * 16) : 0;
+    const int fixed = P.sc_stride * P.n_warps + 256;
+    const int per_stage = P.stage_bytes + 16 + 16;          // data + meta + full / empty barriers
+    const int ns = (SMEM_MAX - fixed) / per_stage;
     if (ns < 3) return false;
     P.n_stages = ns > RS_MAX ? RS_MAX : ns;
     P.meta_off = P.n_stages * P.stage_bytes;
     P.bar_off = P.meta_off + P.n_stages * 16;
-    P.sc_off = (P.bar_off + P.n_stages * 8 + 15) / 16 * 16;
-    P.warp_bytes = (P.sc_off + sc_bytes + 127) / 128 * 128;
-    cfg.smem = (size_t)P.warp_bytes * P.n_warps;
+    P.sc_off = (P.bar_off + P.n_stages * 16 + 127) / 128 * 128;
+    cfg.smem = (size_t)P.sc_off + (size_t)P.sc_stride * P.n_warps;
     return cfg.smem <= (size_t)SMEM_MAX;
 }
 
-// TAG makes the per-device flag private to ONE kernel instantiation: every k_gat_ring_fwd<A, B> has the same
-// function type, so a flag keyed on the type alone would be shared by all of them (and only the first
-// instantiation launched would ever get its shared-memory limit raised -> "invalid argument" for the next).
 template <int TAG, typename K>
 bool ring_set_smem(K kernel) {
     static bool done[64] = {false};
@@ -687,7 +733,7 @@ int gat_ring_fwd(const void* xl, const void* xr, int64_t ld, const float* att, c
 #define CALL(A, B)                                                                                                   \
     do {                                                                                                             \
         if (!ring_set_smem<(A) * 16 + (B)>(k_gat_ring_fwd<A, B>)) return 1;                                                          \
-        k_gat_ring_fwd<A, B><<<grid, P.n_warps * 32, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
+        k_gat_ring_fwd<A, B><<<grid, RING_THREADS, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
             (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, dst_off, slope, head_ws, alpha);                  \
     } while (0)
     RING_DISPATCH(cfg, CALL);
@@ -725,11 +771,15 @@ int gat_ring_bwd(const void* xl, const void* xr, int64_t ld, const float* att, c
 #define CALL(A, B)                                                                                                   \
     do {                                                                                                             \
         if (!ring_set_smem<1024 + (A) * 16 + (B)>(k_gat_ring_bwd<A, B>)) return 1;                                                          \
-        k_gat_ring_bwd<A, B><<<grid, P.n_warps * 32, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
+        k_gat_ring_bwd<A, B><<<grid, RING_THREADS, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
             (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, slope, invH, dout, ldo, alpha, Dbuf, ds_ws,       \
             (__nv_bfloat16*)dxr, datt, mask);                                                                        \
-        k_gat_ring_bwd_src<A, B><<<n_src, P.n_warps * 32, 0, s>>>(P, att, rptr, rdst, rslot, slope, invH, dout, ldo, \
-            alpha, ds_ws, mask, (__nv_bfloat16*)dxl, ld);                                                            \
+        int occ_ = 1;                                                                                                \
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_, k_gat_ring_bwd_src<A, B>, P.n_warps * 32, 0) !=     \
+            cudaSuccess || occ_ < 1) { cudaGetLastError(); occ_ = 1; }                                               \
+        const int gsrc_ = n_src < occ_ * nc_num_sms() ? n_src : occ_ * nc_num_sms();   /* one resident wave */      \
+        k_gat_ring_bwd_src<A, B><<<gsrc_, P.n_warps * 32, 0, s>>>(                                                   \
+            P, att, rptr, rdst, rslot, slope, invH, dout, ldo, alpha, ds_ws, mask, (__nv_bfloat16*)dxl, ld, n_src);  \
     } while (0)
     RING_DISPATCH(cfg, CALL);
 #undef CALL
