@@ -686,7 +686,15 @@ def main():
         emit(res, out_fd)
     if world > 1:
         import torch.distributed as dist
-        dist.destroy_process_group()
+        # every rank still references the peers' arenas (cudaIpc mappings): drop the CUDA graphs that hold them, then
+        # unmap together before the process group goes away
+        tr._graph_buckets.clear()
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stderr.flush()
+        # leave without interpreter teardown: destructors of CUDA graphs / cudaIpc mappings / NCCL communicators of N
+        # processes that reference each other's memory have hung a rank at exit (after the result line was written)
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -381,12 +381,24 @@ int nc_peer_close(void* dev);
  * moments of this rank's shard only (ceil(numel / world / 4) * 4 floats); done_counter: one zeroed uint32.
  * Every rank calls with the same `step` sequence (1, 2, ...): it is the bias-correction step AND the
  * barrier epoch.  dyn != NULL: {lr, step} are read from device memory instead (and the step advanced by the
- * kernel), so that the launch can be replayed from a CUDA graph.  n_ctas <= 0: 64.                                                                     */
+ * kernel), so that the launch can be replayed from a CUDA graph.  aux_ptrs_host (nullable): `world` peer pointers to
+ * aux_n floats each (the |mu| running mean, modules/vgpgae.py:641-651) that are replaced by their mean over the ranks
+ * once every peer has read them (aux_avg: aux_n floats of local scratch); done_counter: TWO zeroed uint32.
+ * n_ctas <= 0: one CTA per SM.                                                                     */
 int nc_dp_adam_step(void* const* p_ptrs_host, void* const* g_ptrs_host, void* const* shadow_ptrs_host,
                     void* const* flag_ptrs_host, float* m, float* v, int64_t numel, int32_t rank,
                     int32_t world, float lr, float beta1, float beta2, float eps, float weight_decay,
                     int32_t step, float clip_value, uint32_t* done_counter, int32_t n_ctas, float* dyn,
-                    void* stream);
+                    void* const* aux_ptrs_host, float* aux_avg, int32_t aux_n, void* stream);
+
+/* Halo rows of a spatially partitioned full-graph pass read straight from their owners' HBM over NVLink
+ * (models/tiled_inference.py; the reference runs latent inference on one device, models/nichecompass.py:1264-1381):
+ * out[r, :row_bytes] = peer[owner[r]][pos[r], :row_bytes].  peer_ptrs_host: `world` device pointers (own buffer +
+ * nc_peer_open mappings), row pitch src_pitch bytes; all byte counts multiples of 16.  The caller orders the call
+ * after every owner has written its rows.                                                                    */
+int nc_halo_gather_rows(void* const* peer_ptrs_host, int32_t world, const int32_t* owner, const int64_t* pos,
+                        int64_t n_rows, int64_t src_pitch, int64_t row_bytes, void* out, int64_t out_pitch,
+                        void* stream);
 
 #ifdef __cplusplus
 }

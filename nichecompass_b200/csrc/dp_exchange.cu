@@ -31,6 +31,7 @@ struct DpPeers {
     float* g[DP_MAX_WORLD];
     __nv_bfloat16* sh[DP_MAX_WORLD];     // may be all NULL (fp32 mode)
     uint32_t* flags[DP_MAX_WORLD];       // [2 * world] per rank: [0, W) start flags, [W, 2W) end flags
+    float* aux[DP_MAX_WORLD];            // small per-rank statistic averaged with the step (may be all NULL)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -67,7 +68,7 @@ template <int W>
 __global__ void __launch_bounds__(512)
 k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t lo, int64_t hi, int rank, uint32_t epoch,
           float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt, float clip,
-          unsigned int* __restrict__ done_counter, float* __restrict__ dyn) {
+          unsigned int* __restrict__ done_counter, float* __restrict__ dyn, float* __restrict__ aux_avg, int aux_n) {
     if (dyn) {                      // {lr, step} on the device (CUDA-graph replay): step is also the barrier epoch
         lr = dyn[0];
         const double step = (double)dyn[1];
@@ -86,37 +87,65 @@ k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t
     }
     __syncthreads();
     const float lr_bc1 = lr / bc1, invW = 1.0f / (float)W;
+    // the |mu| running mean that drives gene-program pruning (modules/vgpgae.py:641-651 is per-process state in the
+    // reference): averaged over the ranks by the last CTA of the grid into a local scratch, published below
+    if (aux_n > 0 && blockIdx.x == gridDim.x - 1) {
+        for (int i = threadIdx.x; i < aux_n; i += blockDim.x) {
+            float a = 0.f;
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                float t;
+                asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(t) : "l"(P.aux[k] + i) : "memory");
+                a += t;
+            }
+            aux_avg[i] = a * invW;
+        }
+    }
     const bool shadow = P.sh[0] != nullptr;
     const int64_t n4 = (hi - lo) >> 2;                        // lo and the shard length are multiples of 4 (host)
     const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nt = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t q = t0; q < n4; q += nt) {
-        const int64_t i = lo + (q << 2);
-        float4 gs[W];
+    // two 128-bit chunks per thread and iteration: 2 W peer loads in flight per thread (an NVLink round trip is ~2 us;
+    // one chunk per thread left the links half empty)
+    for (int64_t q0 = t0; q0 < n4; q0 += 2 * nt) {
+        const int64_t q1 = q0 + nt;
+        const bool two = q1 < n4;
+        const int64_t i0 = lo + (q0 << 2), i1 = lo + ((two ? q1 : q0) << 2);
+        float4 ga[W], gb[W];
 #pragma unroll
-        for (int k = 0; k < W; ++k) gs[k] = ld_peer4(P.g[(rank + k) % W] + i);          // W loads in flight
-        float4 pp = *reinterpret_cast<const float4*>(P.p[rank] + i);
-        float4 mm = *reinterpret_cast<const float4*>(m + (i - lo));
-        float4 vv = *reinterpret_cast<const float4*>(v + (i - lo));
-        float4 g = gs[0];
+        for (int k = 0; k < W; ++k) ga[k] = ld_peer4(P.g[(rank + k) % W] + i0);
 #pragma unroll
-        for (int k = 1; k < W; ++k) { g.x += gs[k].x; g.y += gs[k].y; g.z += gs[k].z; g.w += gs[k].w; }
-        pp.x = adam1(pp.x, g.x * invW, mm.x, vv.x, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
-        pp.y = adam1(pp.y, g.y * invW, mm.y, vv.y, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
-        pp.z = adam1(pp.z, g.z * invW, mm.z, vv.z, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
-        pp.w = adam1(pp.w, g.w * invW, mm.w, vv.w, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
-        *reinterpret_cast<float4*>(m + (i - lo)) = mm;
-        *reinterpret_cast<float4*>(v + (i - lo)) = vv;
-        __nv_bfloat162 b_lo = __floats2bfloat162_rn(pp.x, pp.y), b_hi = __floats2bfloat162_rn(pp.z, pp.w);
-        uint2 sq;
-        sq.x = *reinterpret_cast<uint32_t*>(&b_lo);
-        sq.y = *reinterpret_cast<uint32_t*>(&b_hi);
-        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < W; ++k) gb[k] = ld_peer4(P.g[(rank + k) % W] + i1);
 #pragma unroll
-        for (int k = 0; k < W; ++k) {
-            const int peer = (rank + k) % W;
-            *reinterpret_cast<float4*>(P.p[peer] + i) = pp;
-            if (shadow) *reinterpret_cast<uint2*>(P.sh[peer] + i) = sq;
-            *reinterpret_cast<float4*>(P.g[peer] + i) = zero;
+        for (int half = 0; half < 2; ++half) {
+            if (half == 1 && !two) break;
+            const int64_t i = half ? i1 : i0;
+            float4 pp = *reinterpret_cast<const float4*>(P.p[rank] + i);
+            float4 mm = *reinterpret_cast<const float4*>(m + (i - lo));
+            float4 vv = *reinterpret_cast<const float4*>(v + (i - lo));
+            float4 g = half ? gb[0] : ga[0];
+#pragma unroll
+            for (int k = 1; k < W; ++k) {
+                const float4 t = half ? gb[k] : ga[k];
+                g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
+            }
+            pp.x = adam1(pp.x, g.x * invW, mm.x, vv.x, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+            pp.y = adam1(pp.y, g.y * invW, mm.y, vv.y, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+            pp.z = adam1(pp.z, g.z * invW, mm.z, vv.z, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+            pp.w = adam1(pp.w, g.w * invW, mm.w, vv.w, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
+            *reinterpret_cast<float4*>(m + (i - lo)) = mm;
+            *reinterpret_cast<float4*>(v + (i - lo)) = vv;
+            __nv_bfloat162 b_lo = __floats2bfloat162_rn(pp.x, pp.y), b_hi = __floats2bfloat162_rn(pp.z, pp.w);
+            uint2 sq;
+            sq.x = *reinterpret_cast<uint32_t*>(&b_lo);
+            sq.y = *reinterpret_cast<uint32_t*>(&b_hi);
+            const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                const int peer = (rank + k) % W;
+                *reinterpret_cast<float4*>(P.p[peer] + i) = pp;
+                if (shadow) *reinterpret_cast<uint2*>(P.sh[peer] + i) = sq;
+                *reinterpret_cast<float4*>(P.g[peer] + i) = zero;
+            }
         }
     }
     // ---- end barrier: the last CTA of this rank to finish publishes "my writes are done" and waits for the peers
@@ -131,7 +160,17 @@ k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t
             for (int k = 0; k < W; ++k) st_release_sys(P.flags[k] + W + rank, epoch);
             wait_all(P.flags[rank], W, W, epoch);
             if (dyn) dyn[1] += 1.0f;                     // every CTA has read the step: this is the last one running
+            __threadfence();
+            done_counter[1] = 1u;                        // every peer has read this rank's statistic: publish the mean
         }
+    }
+    if (aux_n > 0 && blockIdx.x == gridDim.x - 1) {      // the CTA that computed the mean waits for that signal
+        if (threadIdx.x == 0) {
+            while (*reinterpret_cast<volatile unsigned int*>(done_counter + 1) == 0u) __nanosleep(64);
+            done_counter[1] = 0u;
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < aux_n; i += blockDim.x) P.aux[rank][i] = aux_avg[i];
     }
 }
 }  // namespace
@@ -189,12 +228,14 @@ extern "C" int nc_dp_adam_step(void* const* p_ptrs_host, void* const* g_ptrs_hos
                                void* const* flag_ptrs_host, float* m, float* v, int64_t numel, int32_t rank,
                                int32_t world, float lr, float beta1, float beta2, float eps, float weight_decay,
                                int32_t step, float clip_value, uint32_t* done_counter, int32_t n_ctas, float* dyn,
-                               void* stream) {
+                               void* const* aux_ptrs_host, float* aux_avg, int32_t aux_n, void* stream) {
     NC_REQUIRE(world >= 1 && world <= DP_MAX_WORLD && rank >= 0 && rank < world && numel > 0 && (step >= 1 || dyn), NC_EINVAL,
                "nc_dp_adam_step: bad arguments (world=%d rank=%d numel=%lld step=%d)", world, rank, (long long)numel, step);
     NC_REQUIRE(numel % 4 == 0, NC_ESHAPE, "nc_dp_adam_step: the arena length must be a multiple of 4");
     DpPeers P;
-    for (int k = 0; k < DP_MAX_WORLD; ++k) { P.p[k] = nullptr; P.g[k] = nullptr; P.sh[k] = nullptr; P.flags[k] = nullptr; }
+    for (int k = 0; k < DP_MAX_WORLD; ++k) { P.p[k] = nullptr; P.g[k] = nullptr; P.sh[k] = nullptr; P.flags[k] = nullptr; P.aux[k] = nullptr; }
+    if (aux_ptrs_host == nullptr || aux_avg == nullptr) aux_n = 0;
+    for (int k = 0; k < world && aux_n > 0; ++k) P.aux[k] = (float*)aux_ptrs_host[k];
     for (int k = 0; k < world; ++k) {
         P.p[k] = (float*)p_ptrs_host[k];
         P.g[k] = (float*)g_ptrs_host[k];
@@ -206,11 +247,11 @@ extern "C" int nc_dp_adam_step(void* const* p_ptrs_host, void* const* g_ptrs_hos
     const int64_t lo = std::min<int64_t>((int64_t)rank * shard, numel), hi = std::min<int64_t>(lo + shard, numel);
     const float bc1 = dyn ? 1.f : (float)(1.0 - pow((double)beta1, (double)step));
     const float bc2_sqrt = dyn ? 1.f : (float)sqrt(1.0 - pow((double)beta2, (double)step));
-    if (n_ctas <= 0) n_ctas = 64;
+    if (n_ctas <= 0) n_ctas = nc_num_sms();
     cudaStream_t s = (cudaStream_t)stream;
 #define DP_LAUNCH(WW)                                                                                              \
     k_dp_adam<WW><<<n_ctas, 512, 0, s>>>(P, m, v, lo, hi, rank, (uint32_t)step, lr, beta1, beta2, eps, weight_decay, bc1, \
-                                         bc2_sqrt, clip_value, done_counter, dyn)
+                                         bc2_sqrt, clip_value, done_counter, dyn, aux_avg, aux_n)
     switch (world) {
         case 1: DP_LAUNCH(1); break;
         case 2: DP_LAUNCH(2); break;
@@ -221,5 +262,52 @@ extern "C" int nc_dp_adam_step(void* const* p_ptrs_host, void* const* g_ptrs_hos
 #undef DP_LAUNCH
     nc_count_launch(1);
     NC_CHECK_LAUNCH("nc_dp_adam_step");
+    return NC_OK;
+}
+
+// ---------------------------------------------------------------------------- halo rows straight from the peers' HBM
+// Full-atlas latent inference over spatial tiles (models/tiled_inference.py; the reference walks a NeighborLoader over
+// the whole graph on one device, models/nichecompass.py:1264-1381): every rank needs the `hidden` rows of the nodes
+// just outside its tile.  Instead of index exchange + pack + all_to_all + unpack, each rank reads those rows where
+// they are: out[r, :] = peer[owner[r]][pos[r], :] over NVLink, one warp per row, 128-bit loads.
+namespace {
+struct HaloPeers { const uint8_t* base[DP_MAX_WORLD]; };
+
+__global__ void __launch_bounds__(256)
+k_halo_gather(const HaloPeers P, const int32_t* __restrict__ owner, const int64_t* __restrict__ pos, int64_t n_rows,
+              int64_t src_pitch, int64_t row_bytes, uint8_t* __restrict__ out, int64_t out_pitch) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarp = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = warp; r < n_rows; r += nwarp) {
+        const uint8_t* src = P.base[owner[r]] + pos[r] * src_pitch;
+        uint8_t* dst = out + r * out_pitch;
+        for (int64_t b = (int64_t)lane * 16; b < row_bytes; b += 32 * 16) {
+            int4 v;
+            asm volatile("ld.relaxed.sys.global.v4.s32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + b) : "memory");
+            *reinterpret_cast<int4*>(dst + b) = v;
+        }
+    }
+}
+}  // namespace
+
+// peer_ptrs_host: `world` device pointers (own buffer + nc_peer_open mappings) to row-major buffers of pitch
+// src_pitch bytes; owner[r] / pos[r]: rank and row index (in the owner's buffer) of halo row r; row_bytes and both
+// pitches multiples of 16.  The caller guarantees that every owner has finished writing its rows (a barrier).
+extern "C" int nc_halo_gather_rows(void* const* peer_ptrs_host, int32_t world, const int32_t* owner, const int64_t* pos,
+                                   int64_t n_rows, int64_t src_pitch, int64_t row_bytes, void* out, int64_t out_pitch,
+                                   void* stream) {
+    NC_REQUIRE(world >= 1 && world <= DP_MAX_WORLD && n_rows >= 0 && row_bytes > 0 && row_bytes % 16 == 0 &&
+               src_pitch % 16 == 0 && out_pitch % 16 == 0 && src_pitch >= row_bytes && out_pitch >= row_bytes, NC_EINVAL,
+               "nc_halo_gather_rows: bad arguments (world=%d rows=%lld row_bytes=%lld)", world, (long long)n_rows,
+               (long long)row_bytes);
+    if (n_rows == 0) return NC_OK;
+    HaloPeers P;
+    for (int k = 0; k < DP_MAX_WORLD; ++k) P.base[k] = k < world ? (const uint8_t*)peer_ptrs_host[k] : nullptr;
+    const int grid = (int)std::min<int64_t>(nc_cdiv(n_rows, 8), 8 * (int64_t)nc_num_sms());
+    k_halo_gather<<<grid, 256, 0, (cudaStream_t)stream>>>(P, owner, pos, n_rows, src_pitch, row_bytes, (uint8_t*)out,
+                                                         out_pitch);
+    nc_count_launch(1);
+    NC_CHECK_LAUNCH("nc_halo_gather_rows");
     return NC_OK;
 }

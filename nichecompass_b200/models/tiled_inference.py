@@ -27,6 +27,7 @@ With the GATv2 encoder (1 layer) and all neighbours sampled, a node's ``mu`` dep
 The index plumbing (permutation, local CSR, halo lists) is torch tensor code and also runs on CPU
 tensors under ``gloo`` (tests/test_host_logic.py); all arithmetic is in the CUDA library.
 """
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -148,6 +149,29 @@ def exchange_halo_rows(own_rows: torch.Tensor, lg: LocalGraph, bounds: Sequence[
     return out
 
 
+def gather_halo_rows_peer(peer, n_own_rows: int, ld: int, dtype: torch.dtype, lg: LocalGraph, bounds: Sequence[int],
+                          out: torch.Tensor, group=None) -> torch.Tensor:
+    """The same rows without packing or a collective: every rank's ``hidden`` buffer lives in peer-mapped memory
+    (``train/optim.py: PeerBuffer``) and the halo rows are read where they are, over NVLink, by one kernel
+    (``nc_halo_gather_rows``).  ``peer``: this rank's PeerBuffer holding [>= n_own_rows, ld] rows of ``dtype``."""
+    import torch.distributed as dist
+    if lg.n_halo == 0:
+        dist.barrier(group=group)
+        return out
+    dev = out.device
+    b = torch.tensor(list(bounds), dtype=torch.int64, device=dev)
+    owner = torch.searchsorted(b, lg.halo_pos, right=True) - 1
+    pos = (lg.halo_pos - b[owner]).contiguous()                            # row index inside the owner's buffer
+    esz = torch.empty(0, dtype=dtype).element_size()
+    torch.cuda.synchronize()
+    dist.barrier(group=group)                                              # every owner has written its rows
+    call("nc_halo_gather_rows", peer.ptr_array, len(peer.ptrs), owner.to(torch.int32).contiguous(), pos, lg.n_halo,
+         ld * esz, ld * esz, out, out.stride(0) * esz)
+    torch.cuda.synchronize()
+    dist.barrier(group=group)                                              # nobody frees / rewrites while peers read
+    return out
+
+
 # ----------------------------------------------------------------------------- layer-wise encoder
 def supports(module) -> bool:
     """The layer-wise path reproduces the loader path exactly only where a node's output is
@@ -177,8 +201,26 @@ def encode_partition(module, store, lg: LocalGraph, own_old: torch.Tensor, bound
     # ---- 2. hidden = relu(fc_l1(log1p x)) for the owned nodes
     W1 = pack_rows((enc._key, "W1"), [enc.fc_l1.weight], act, enc.fc_l1.weight.size(1))
     b1 = enc.fc_l1.bias.detach().float()
-    Hall = torch.zeros(n_loc, ldh, dtype=act, device=dev) if ldh != Hd else \
-        torch.empty(n_loc, ldh, dtype=act, device=dev)
+    import torch.distributed as dist
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    peer = None
+    if multi and os.environ.get("NC_HALO_EXCHANGE", "peer") == "peer":
+        # hidden rows in peer-mapped memory: the halo is gathered straight from the owners' HBM (no pack, no collective)
+        from ..train.optim import PeerBuffer
+        try:
+            peer = PeerBuffer(max(n_loc, 1) * ldh * torch.empty(0, dtype=act).element_size(), group)
+        except Exception:                                                  # noqa: BLE001 -- e.g. no cudaIpc between the devices
+            peer = None
+        ok = torch.tensor([1 if peer is not None else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if int(ok.item()) == 0 and peer is not None:
+            peer.close()
+            peer = None
+    if peer is not None:
+        Hall = peer.tensor(act)[:n_loc * ldh].view(n_loc, ldh)
+    else:
+        Hall = torch.zeros(n_loc, ldh, dtype=act, device=dev) if ldh != Hd else \
+            torch.empty(n_loc, ldh, dtype=act, device=dev)
     ids32 = own_old.to(torch.int32)
     for c0 in range(0, n_own, chunk_rows):
         c1 = min(n_own, c0 + chunk_rows)
@@ -191,7 +233,10 @@ def encode_partition(module, store, lg: LocalGraph, own_old: torch.Tensor, bound
         ops.gemm(x_enc, W1, bias=b1, relu=True, out=Hall[c0:c1, :Hd], M=c1 - c0, N=Hd, K=enc.n_input)
 
     # ---- 3. halo rows of hidden from their owners
-    exchange_halo_rows(Hall[:n_own], lg, bounds, group=group, out=Hall[n_own:])
+    if peer is not None:
+        gather_halo_rows_peer(peer, n_own, ldh, act, lg, bounds, Hall[n_own:], group=group)
+    else:
+        exchange_halo_rows(Hall[:n_own], lg, bounds, group=group, out=Hall[n_own:])
 
     # ---- 4. x_l = lin_l(hidden) of the stacked convs, own + halo rows
     convs = [(c, o) for c, o in enc._convs() if want_logstd or o < P]
@@ -233,4 +278,8 @@ def encode_partition(module, store, lg: LocalGraph, own_old: torch.Tensor, bound
         o = out[t0:t1]
         call("nc_gatv2_fwd_tile", XL, XR, dtype_code(act), ldl, att, bias_out, lg.rowptr, lg.col, t0, t1 - t0,
              seg, HostPtr(seg_host), len(convs), heads, lg.max_deg, 0.2, o, o.stride(0), head_ws)
+    if peer is not None:
+        del Hall
+        dist.barrier(group=group)
+        peer.close()
     return out

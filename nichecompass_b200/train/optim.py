@@ -136,7 +136,7 @@ class FlatAdam:
                 shard = ((n + world - 1) // world + 3) // 4 * 4
                 self.peer = {"bufs": bufs, "world": world, "rank": rank, "group": grp, "shard": shard,
                              "ctas": int(peer_ctas),
-                             "done": torch.zeros(1, dtype=torch.int32, device=dev)}
+                             "done": torch.zeros(2, dtype=torch.int32, device=dev), "aux": None}
         if self.peer is None:
             self.flat_p = torch.zeros(n, dtype=torch.float32, device=dev)
             self.flat_g = torch.zeros(n, dtype=torch.float32, device=dev)
@@ -167,6 +167,33 @@ class FlatAdam:
         # training step can be replayed without any host-side argument going stale (train/trainer.py graph buckets)
         self.dyn = torch.tensor([float(lr), 1.0], dtype=torch.float32, device=dev)
         self._lr_on_device = float(lr)
+
+    def attach_aux(self, buf: torch.Tensor) -> torch.Tensor:
+        """Peer mode: a small fp32 statistic (the module's ``running_mean_abs_mu``) that every step replaces by its
+        mean over the ranks, inside the exchange kernel.  Returns the peer-mapped tensor that must take the place
+        of ``buf`` (same values)."""
+        if self.peer is None:
+            return buf
+        n = buf.numel()
+        pb = PeerBuffer(max(4 * n, 256), self.peer["group"])
+        t = pb.tensor(torch.float32)[:n]
+        t.copy_(buf.detach().float().reshape(-1))
+        self.peer["aux"] = (pb, torch.zeros(n, dtype=torch.float32, device=buf.device), n)
+        return t.view_as(buf)
+
+    def close(self):
+        """Peer mode: unmap / free the peer buffers (collective: every rank calls it once its last step is queued)."""
+        if getattr(self, "peer", None) is None:
+            return
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier(group=self.peer["group"])
+        bufs = list(self.peer["bufs"].values()) + ([self.peer["aux"][0]] if self.peer["aux"] else [])
+        self.flat_p = self.flat_g = self.flat_bf16 = None
+        for b in bufs:
+            b.close()
+        dist.barrier(group=self.peer["group"])
+        self.peer = None
 
     def sync_lr(self):
         """Push ``param_groups[0]["lr"]`` (the reference's ``param_group["lr"] *= factor`` idiom) to the device."""
@@ -209,7 +236,7 @@ class FlatAdam:
     def all_reduce_grads(self, group=None):
         """Data-parallel exchange: mean of the flat gradient buffer over the ranks (a no-op with peer arenas: the
         exchange is part of ``step``)."""
-        if self.peer is not None:
+        if getattr(self, "peer", None) is not None:
             return
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
@@ -230,7 +257,9 @@ class FlatAdam:
             call("nc_dp_adam_step", b["p"].ptr_array, b["g"].ptr_array, b["sh"].ptr_array if "sh" in b else None,
                  b["flags"].ptr_array, self.exp_avg, self.exp_avg_sq, self.numel, pr["rank"], pr["world"],
                  float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
-                 float(g["weight_decay"]), self.step_count, float(clip_value), pr["done"], pr["ctas"], self.dyn)
+                 float(g["weight_decay"]), self.step_count, float(clip_value), pr["done"], pr["ctas"], self.dyn,
+                 pr["aux"][0].ptr_array if pr["aux"] else None, pr["aux"][1] if pr["aux"] else None,
+                 pr["aux"][2] if pr["aux"] else 0)
             self._grads_clean = True
             Fn.bump_param_epoch()
             return

@@ -621,6 +621,12 @@ class Trainer(BaseTrainerMixin):
             flag = torch.tensor([ok], device=self.device)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             if int(flag.item()) == 1:
+                # the |mu| running mean is averaged over the ranks by the exchange kernel itself (no NCCL call in the
+                # iteration at all): the module's buffer moves into peer-mapped memory
+                ema = getattr(self.model, "running_mean_abs_mu", None)
+                if ema is not None:
+                    self.model.running_mean_abs_mu.data = opt.attach_aux(ema.data)
+                    self.model._dp_sync_ema = False
                 return opt
             self.dp_exchange_ = "nccl"
         return FlatAdam(params, lr=lr, weight_decay=weight_decay, groups=groups, bf16_shadow=shadow)
