@@ -66,7 +66,8 @@ __device__ __forceinline__ void wait_all(const uint32_t* flags, int lo, int W, u
 
 template <int W>
 __global__ void __launch_bounds__(512)
-k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t lo, int64_t hi, int rank, uint32_t epoch,
+k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t lo, int64_t hi, int64_t numel, int rank,
+          uint32_t epoch,
           float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt, float clip,
           unsigned int* __restrict__ done_counter, float* __restrict__ dyn, float* __restrict__ aux_avg, int aux_n) {
     if (dyn) {                      // {lr, step} on the device (CUDA-graph replay): step is also the barrier epoch
@@ -138,17 +139,17 @@ k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t
             uint2 sq;
             sq.x = *reinterpret_cast<uint32_t*>(&b_lo);
             sq.y = *reinterpret_cast<uint32_t*>(&b_hi);
-            const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
             for (int k = 0; k < W; ++k) {
                 const int peer = (rank + k) % W;
                 *reinterpret_cast<float4*>(P.p[peer] + i) = pp;
                 if (shadow) *reinterpret_cast<uint2*>(P.sh[peer] + i) = sq;
-                *reinterpret_cast<float4*>(P.g[peer] + i) = zero;
             }
         }
     }
-    // ---- end barrier: the last CTA of this rank to finish publishes "my writes are done" and waits for the peers
+    // ---- end barrier: the last CTA of this rank to finish publishes "my writes are done" and waits for the peers;
+    // every CTA then clears its stripe of THIS rank's gradient arena (all peers have read it by now): a local HBM
+    // write instead of 4 bytes per parameter and peer over the links
     __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -161,17 +162,18 @@ k_dp_adam(const DpPeers P, float* __restrict__ m, float* __restrict__ v, int64_t
             wait_all(P.flags[rank], W, W, epoch);
             if (dyn) dyn[1] += 1.0f;                     // every CTA has read the step: this is the last one running
             __threadfence();
-            done_counter[1] = 1u;                        // every peer has read this rank's statistic: publish the mean
+            atomicExch(done_counter + 1, epoch);         // go: peers are done with this rank's gradients and statistic
         }
+        while ((int32_t)(*reinterpret_cast<volatile unsigned int*>(done_counter + 1) - epoch) < 0) __nanosleep(64);
     }
-    if (aux_n > 0 && blockIdx.x == gridDim.x - 1) {      // the CTA that computed the mean waits for that signal
-        if (threadIdx.x == 0) {
-            while (*reinterpret_cast<volatile unsigned int*>(done_counter + 1) == 0u) __nanosleep(64);
-            done_counter[1] = 0u;
-        }
-        __syncthreads();
+    __syncthreads();
+    {
+        float4* gz = reinterpret_cast<float4*>(P.g[rank]);
+        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int64_t q = t0; q < (numel >> 2); q += nt) gz[q] = zero;
+    }
+    if (aux_n > 0 && blockIdx.x == gridDim.x - 1)        // (after the go signal above) publish the mean of the statistic
         for (int i = threadIdx.x; i < aux_n; i += blockDim.x) P.aux[rank][i] = aux_avg[i];
-    }
 }
 }  // namespace
 
@@ -249,8 +251,17 @@ extern "C" int nc_dp_adam_step(void* const* p_ptrs_host, void* const* g_ptrs_hos
     const float bc2_sqrt = dyn ? 1.f : (float)sqrt(1.0 - pow((double)beta2, (double)step));
     if (n_ctas <= 0) n_ctas = nc_num_sms();
     cudaStream_t s = (cudaStream_t)stream;
+    // every CTA waits for the last one after the end barrier: the whole grid must be resident at once
 #define DP_LAUNCH(WW)                                                                                              \
-    k_dp_adam<WW><<<n_ctas, 512, 0, s>>>(P, m, v, lo, hi, rank, (uint32_t)step, lr, beta1, beta2, eps, weight_decay, bc1, \
+    {                                                                                                              \
+        int occ_ = 1;                                                                                              \
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_, k_dp_adam<WW>, 512, 0) != cudaSuccess || occ_ < 1) { \
+            cudaGetLastError();                                                                                    \
+            occ_ = 1;                                                                                              \
+        }                                                                                                          \
+        if (n_ctas > occ_ * nc_num_sms()) n_ctas = occ_ * nc_num_sms();                                            \
+    }                                                                                                              \
+    k_dp_adam<WW><<<n_ctas, 512, 0, s>>>(P, m, v, lo, hi, numel, rank, (uint32_t)step, lr, beta1, beta2, eps, weight_decay, bc1, \
                                          bc2_sqrt, clip_value, done_counter, dyn, aux_avg, aux_n)
     switch (world) {
         case 1: DP_LAUNCH(1); break;

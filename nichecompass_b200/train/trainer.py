@@ -266,7 +266,7 @@ class Trainer(BaseTrainerMixin):
     # The reference loop (train/trainer.py:364-421) is ~70 kernel launches behind ~100 small torch ops and 16
     # autograd functions per iteration: 3.2-3.8 ms of Python for 3.2 ms of device work.  Every size of an iteration is
     # known on the host before it is launched (the sampler runs one batch ahead), so the iteration is captured ONCE
-    # per size bucket -- sub-graph rows rounded up to 256, live edges to 1024, edge seeds to 4 x edge batch -- and
+    # per size bucket -- sub-graph rows rounded up to 512, live edges to 2048, edge seeds to 4 x edge batch -- and
     # replayed: the host then only merges the two sampled sub-graphs into the bucket's padded buffers, gathers the
     # parameter-free label rows, draws the reparameterisation noise and launches the graph.  Padding rows repeat a
     # real node and are referenced by no edge: they cost (<= 3 %) work and change no result
@@ -288,8 +288,10 @@ class Trainer(BaseTrainerMixin):
     def _bucket_sizes(self, node_batch, edge_batch):
         gn, ge = node_batch.graph, edge_batch.graph
         B4 = 4 * int(self.edge_batch_size_)
-        n_sub_pad = (gn.n_nodes + ge.n_nodes + (B4 - ge.n_dst) + 255) // 256 * 256
-        e_pad = (max(gn.e_dst + ge.e_dst, 1) + 1023) // 1024 * 1024
+        # rows to 512, live edges to 2048: a handful of buckets per workload (every bucket is one capture), <= 3 %
+        # padding work on average at C2 (8.5 k rows, 12 k edges per iteration)
+        n_sub_pad = (gn.n_nodes + ge.n_nodes + (B4 - ge.n_dst) + 511) // 512 * 512
+        e_pad = (max(gn.e_dst + ge.e_dst, 1) + 2047) // 2048 * 2048
         return B4, n_sub_pad, e_pad
 
     def _graph_inputs(self, node_batch, edge_batch, out, background: bool):
@@ -381,11 +383,13 @@ class Trainer(BaseTrainerMixin):
         S.eps_e.normal_()
         opt.sync_lr()
         S.uses += 1
-        if S.graph is None and S.uses == 1:
-            # first visit of a bucket: a genuine eager iteration on the bucket's buffers (also the warm-up that
-            # every lazily initialised piece -- mask structure, function attributes -- needs before a capture)
+        if S.graph is None and not getattr(self, "_graph_warm", False):
+            # the very first iteration runs eagerly on the bucket's buffers: every lazily initialised piece (mask
+            # structure, kernel attributes, packed-weight caches) must exist before anything is captured
             self.graph_stats_["eager"] += 1
-            return self._graph_body(S, store)
+            out = self._graph_body(S, store)
+            self._graph_warm = True
+            return out
         if S.graph is None:
             if self._graph_pool is None:
                 self._graph_pool = torch.cuda.graph_pool_handle()
