@@ -7,6 +7,8 @@ so a seeded run yields the same train / validation partition as the reference.
 """
 from typing import List, Optional, Tuple
 
+import scipy.sparse as sp
+import numpy as np
 import torch
 
 from .datasets import SpatialAnnTorchDataset
@@ -63,9 +65,9 @@ def edge_level_split(data: GraphData, edge_label_adj=None, val_ratio: float = 0.
     re-appended to the message-passing edges afterwards; one direction (row <= col) of every
     undirected edge permuted and cut into train | val | test supervision edges; message passing
     on the TRAIN edges (both directions) for train and val, train + val edges for test."""
-    if edge_label_adj is not None or not is_undirected or neg_sampling_ratio != 0:
+    if not is_undirected or neg_sampling_ratio != 0:
         raise NotImplementedError("only the reference's configuration is implemented "
-                                  "(undirected split, no edge-label adjacency, loader-side negatives)")
+                                  "(undirected split, loader-side negatives)")
     n = data.num_nodes
     ei = data.edge_index
     ei = ei[:, ei[0] != ei[1]]
@@ -84,7 +86,18 @@ def edge_level_split(data: GraphData, edge_label_adj=None, val_ratio: float = 0.
         e = ei[:, mp_e]
         g = GraphData(data.dataset, torch.cat((e, e.flip([0]), loops), dim=1))
         g.edge_label_index = ei[:, label_e]
-        g.edge_label = torch.ones(label_e.numel())
+        if edge_label_adj is None:
+            g.edge_label = torch.ones(label_e.numel())
+        else:
+            # data/dataprocessors.py:72-78: 1 where the edge is also an edge of ``edge_label_adj``, else 0; the
+            # loaders then draw their positives from ``edge_label_index[:, edge_label.bool()]`` only
+            # (data/dataloaders.py:86,96).  One vectorised sparse lookup instead of a Python loop over the edges.
+            src, dst = g.edge_label_index[0].numpy().copy(), g.edge_label_index[1].numpy().copy()
+            if src.size == 0:
+                g.edge_label = torch.zeros(0)
+            else:
+                vals = np.asarray(sp.csr_matrix(edge_label_adj)[src, dst]).reshape(-1)
+                g.edge_label = torch.from_numpy((vals == 1.0).astype(np.float32))
         return g
 
     return build(train_e, train_e), build(val_e, train_e), build(test_e, perm[:num_train + num_val])

@@ -57,9 +57,8 @@ class SpatialAnnTorchDataset:
         self._store = None
         adj = adata.obsp[adj_key]
         adj = adj if sp.issparse(adj) else sp.csr_matrix(adj)
-        if edge_label_adj_key in adata.obsp:
-            raise NotImplementedError("a separate edge-label adjacency is not supported yet")
-        self.edge_label_adj = None
+        # data/datasets.py:79-83: an optional second adjacency restricting the edges that serve as positives
+        self.edge_label_adj = sp.csr_matrix(adata.obsp[edge_label_adj_key]) if edge_label_adj_key in adata.obsp else None
         # The reference's symmetry check compares nnz with nnz of the transpose (data/datasets.py:87-88),
         # which always holds: an asymmetric adjacency is accepted there, and therefore here too.
         if adj.nnz != adj.T.nnz:

@@ -206,9 +206,11 @@ class Trainer(BaseTrainerMixin):
         self.edge_val_loader = loader_dict.pop("edge_val_loader", None)
         self.node_train_loader = loader_dict["node_train_loader"]
         self.node_val_loader = loader_dict.pop("node_val_loader", None)
-        # data parallelism: the training loaders are strided over the ranks; validation is replicated
-        for ld in (self.edge_train_loader, self.node_train_loader):
-            ld.set_shard(self.rank_, self.world_size_)
+        # data parallelism: training AND validation loaders are strided over the ranks (validation losses are summed
+        # over the ranks, the edge probabilities gathered before the metrics: every rank sees the same numbers)
+        for ld in (self.edge_train_loader, self.node_train_loader, self.edge_val_loader, self.node_val_loader):
+            if ld is not None:
+                ld.set_shard(self.rank_, self.world_size_)
         # sampler kernels of the next batches are launched before the sizes of the current one are read back
         for ld in (self.edge_train_loader, self.node_train_loader, self.edge_val_loader, self.node_val_loader):
             if ld is not None:
@@ -641,20 +643,15 @@ class Trainer(BaseTrainerMixin):
             return
         names = sorted(acc.keys())
         vals = torch.stack([acc[k].float() for k in names])
+        n_train, n_val = float(self.iter_logs["n_train_iter"]), float(self.iter_logs["n_val_iter"])
         if self.world_size_ > 1:
             import torch.distributed as dist
-            cnt = torch.tensor([float(self.iter_logs["n_train_iter"])], device=vals.device)
-            is_train = torch.tensor([1.0 if k.startswith("train") else 0.0 for k in names], device=vals.device)
-            tr = vals * is_train
-            dist.all_reduce(tr, op=dist.ReduceOp.SUM)
-            dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-            vals = torch.where(is_train.bool(), tr, vals)
-            n_train = float(cnt.item())
-        else:
-            n_train = float(self.iter_logs["n_train_iter"])
+            packed = torch.cat((vals, torch.tensor([n_train, n_val], device=vals.device)))
+            dist.all_reduce(packed, op=dist.ReduceOp.SUM)         # sums and iteration counts of all ranks
+            vals, n_train, n_val = packed[:-2], float(packed[-2]), float(packed[-1])
         vals = vals.cpu().tolist()
         for k, v in zip(names, vals):
-            n = n_train if k.startswith("train") else float(self.iter_logs["n_val_iter"])
+            n = n_train if k.startswith("train") else n_val
             self.epoch_logs[k].append(v / max(n, 1.0))
 
     # ------------------------------------------------------------------ evaluation
@@ -674,9 +671,34 @@ class Trainer(BaseTrainerMixin):
     def _cat(ts):
         return torch.cat(ts) if len(ts) > 0 else None
 
+    def _gather_ranks(self, t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        """Concatenation over the ranks of a 1-D device tensor whose length differs per rank (validation shards)."""
+        if t is None or self.world_size_ == 1:
+            return t
+        import torch.distributed as dist
+        n = torch.tensor([t.numel()], device=t.device)
+        sizes = [torch.zeros_like(n) for _ in range(self.world_size_)]
+        dist.all_gather(sizes, n)
+        sizes = [int(x) for x in sizes]
+        buf = torch.zeros(max(sizes), dtype=t.dtype, device=t.device)
+        buf[:t.numel()] = t
+        parts = [torch.empty_like(buf) for _ in range(self.world_size_)]
+        dist.all_gather(parts, buf)
+        return torch.cat([p_[:k] for p_, k in zip(parts, sizes)])
+
     def _edge_metrics(self, store: dict, omics_pred_dict: Optional[dict] = None) -> dict:
         """AUROC / AUPRC / threshold sweeps on the device (``train/metrics.py: eval_metrics_device``): the edge
-        probabilities never leave HBM, one read-back of the finished scalars."""
+        probabilities never leave HBM, one read-back of the finished scalars.  With N ranks every rank evaluated
+        its shard of the validation batches: the per-edge outputs are gathered first."""
+        if self.world_size_ > 1:
+            store = {"probs": [self._gather_ranks(self._cat(store["probs"]))],
+                     "labels": [self._gather_ranks(self._cat(store["labels"]))],
+                     "incl": ([self._gather_ranks(self._cat(store["incl"]).to(torch.uint8)).bool()]
+                              if store["incl"] else []),
+                     "same": [[self._gather_ranks(self._cat(s_).to(torch.uint8)).bool()] if s_ else []
+                              for s_ in store["same"]]}
+            if omics_pred_dict is not None:
+                omics_pred_dict = {k: self._gather_ranks(v) for k, v in omics_pred_dict.items()}
         incl = self._cat(store["incl"])
         same = [self._cat(s) for s in store["same"]] if incl is not None else None
         return eval_metrics_device(edge_recon_probs=self._cat(store["probs"]), edge_labels=self._cat(store["labels"]),

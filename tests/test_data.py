@@ -90,3 +90,27 @@ def test_sampler_leaves_workspace_clean_and_handles_last_short_batch():
     assert n_edges == d["edge_train_data"].edge_label_index.size(1)
     for g in (d["node_masked_data"].device_graph(), d["edge_train_data"].device_graph()):
         assert bool((g.slot_ws() == 2 ** 31 - 1).all())
+
+
+def test_edge_label_adjacency_restricts_the_positive_edges():
+    """data/dataprocessors.py:72-78, data/dataloaders.py:86: with ``adata.obsp['edge_label_spatial_connectivities']``
+    only the edges that are also in that adjacency are labelled 1 and sampled as positives."""
+    import scipy.sparse as sp
+    adata = H.tiny_problem(n_cells=150, n_genes=30, k=4)
+    adj = sp.csr_matrix(adata.obsp["spatial_connectivities"])
+    keep = sp.triu(adj, k=1).tocoo()
+    sel = np.arange(keep.nnz) % 3 == 0                                     # a third of the undirected edges
+    lab = sp.csr_matrix((np.ones(sel.sum()), (keep.row[sel], keep.col[sel])), shape=adj.shape)
+    lab = lab.maximum(lab.T)
+    adata.obsp["edge_label_spatial_connectivities"] = lab
+    torch.manual_seed(0)
+    from nichecompass_b200.data.datasets import SpatialAnnTorchDataset
+    from nichecompass_b200.data.dataprocessors import GraphData, edge_level_split
+    ds = SpatialAnnTorchDataset(adata, [], counts_key=None, device="cpu")
+    assert ds.edge_label_adj is not None
+    train, val, _ = edge_level_split(GraphData(ds, ds.edge_index), ds.edge_label_adj, val_ratio=0.1)
+    for g in (train, val):
+        src, dst = g.edge_label_index[0].numpy().copy(), g.edge_label_index[1].numpy().copy()
+        want = np.asarray(lab[src, dst]).reshape(-1) == 1.0
+        assert np.array_equal(g.edge_label.numpy().astype(bool), want)
+    assert 0 < int(train.edge_label.sum()) < train.edge_label.numel()

@@ -81,3 +81,74 @@ def test_peer_exchange_equals_adam_on_the_mean_gradient(n_params):
             raise AssertionError("a rank hung (barrier flags?)")
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
     assert dict(out) == {0: "ok", 1: "ok"}
+
+
+def _train_worker(rank, world, port, out):
+    import contextlib
+    import io
+    import torch.distributed as dist
+    from oracle.vgpgae_ref import init_params
+    from tests import helpers as H
+    from tests.test_trainer_gpu import LAM, _module
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from nichecompass_b200.train import Trainer
+        adata = H.tiny_problem(n_cells=600, n_genes=44, n_prior_gp=12)
+        cfg = H.oracle_cfg_from_adata(adata, n_addon_gp=4)
+        p32 = init_params(cfg, seed=3)
+        with contextlib.redirect_stdout(io.StringIO()):
+            tr = Trainer(adata, _module(cfg, p32), edge_batch_size=32, seed=0, monitor=False, verbose=True,
+                         compute_dtype=torch.float32)
+            tr.setup_training(lr=1e-3, **LAM)
+        assert tr.optimizer.peer is not None and tr.world_size_ == 2
+        losses = []
+        for i, (eb, nb) in enumerate(tr.joint_batches(tr.edge_train_loader, tr.node_train_loader)):
+            losses.append(float(tr.train_iteration(eb, nb)["global_loss"]))
+            if i == 9:
+                break
+        # both ranks hold the same parameters and the same |mu| statistic after ten exchanged steps
+        flat = tr.optimizer.flat_p.clone()
+        others = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(others, flat)
+        assert all(torch.equal(o, flat) for o in others)
+        ema = tr.model.running_mean_abs_mu.clone()
+        emas = [torch.empty_like(ema) for _ in range(world)]
+        dist.all_gather(emas, ema)
+        assert all(torch.equal(e, ema) for e in emas) and float(ema.abs().sum()) > 0
+        assert tr.graph_stats_["replayed"] >= 5
+        # sharded validation: every rank reports the same losses and metrics
+        tr.iter_logs = {"n_train_iter": 10, "n_val_iter": 0}
+        acc = {}
+        metrics = tr.eval_epoch(acc)
+        tr._epoch_logs_from(acc)
+        got = torch.tensor([metrics["auroc_score"], metrics["auprc_score"], tr.epoch_logs["val_global_loss"][-1]],
+                           dtype=torch.float64, device="cuda")
+        gs = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(gs, got)
+        assert all(torch.equal(g, got) for g in gs), gs
+        assert 0.0 < float(got[0]) <= 1.0
+        out[rank] = "ok"
+        torch.cuda.synchronize()
+        dist.barrier()
+    finally:
+        os._exit(0 if out.get(rank) == "ok" else 1)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on one box")
+def test_two_rank_training_keeps_ranks_identical_and_shards_validation():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    out = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=_train_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+            raise AssertionError("a rank hung")
+    assert dict(out) == {0: "ok", 1: "ok"}, (dict(out), [p.exitcode for p in procs])
