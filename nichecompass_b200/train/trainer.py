@@ -385,12 +385,14 @@ class Trainer(BaseTrainerMixin):
         S.eps_e.normal_()
         opt.sync_lr()
         S.uses += 1
-        if S.graph is None and not getattr(self, "_graph_warm", False):
-            # the very first iteration runs eagerly on the bucket's buffers: every lazily initialised piece (mask
-            # structure, kernel attributes, packed-weight caches) must exist before anything is captured
+        warm = self.__dict__.setdefault("_graph_warm", set())
+        if S.graph is None and key[2:] not in warm:
+            # the first iteration of every phase (store location, active-GP / edge-loss / contrastive flags) runs
+            # eagerly on the bucket's buffers: every lazily initialised piece (mask structure, kernel attributes,
+            # packed-weight caches, device copies of the pruning state) must exist before anything is captured
             self.graph_stats_["eager"] += 1
             out = self._graph_body(S, store)
-            self._graph_warm = True
+            warm.add(key[2:])
             return out
         if S.graph is None:
             if self._graph_pool is None:
