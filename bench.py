@@ -354,8 +354,8 @@ def make_trainer(adata, wl, args, store_location="device"):
 
 def ncu_traffic():
     """DRAM bytes per GEMM launch (read + write) from the committed ncu capture of one C2-shaped step
-    (profiles/r1k_gemm_traffic.json, written from the launch list of tools/gpu_call5.sh); None if absent."""
-    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1k_gemm_traffic.json")
+    (profiles/r2f_gemm_traffic.json, from the full-metric capture of tools/r2/call_final1.sh); None if absent."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r2f_gemm_traffic.json")
     try:
         with open(path) as fh:
             return float(json.load(fh)["dram_bytes_per_launch"])
@@ -583,10 +583,10 @@ def run_ours(args):
         peak_tf = peaks["bf16_sustained"]
         roofline = {"kernel": "gemm_bf16_tcgen05 (nc_gemm_bf16)" if "nc_gemm_bf16" in kern else "gemm_f32_simt",
                     "bound": "tensor", "achieved": g["rate"], "peak": peak_tf, "unit": "TFLOP/s",
-                    "frac": g["rate"] / peak_tf if peak_tf else None, "traffic": None,
-                    "traffic_note": "not measured in this run (ncu cannot run inside a timed bench); the committed "
-                                    "capture profiles/r1k_gemm_traffic.json has 164.8 MB DRAM traffic per launch "
-                                    "against 127 MB algorithmic operand bytes",
+                    "frac": g["rate"] / peak_tf if peak_tf else None, "traffic": ncu_traffic(),
+                    "traffic_note": "dram__bytes_read + dram__bytes_write per launch from the committed ncu --set full "
+                                    "capture of the same 13 launches (profiles/r2f_gemm_traffic.json); ncu cannot run "
+                                    "inside a timed bench, so this figure moves only when the capture is redone",
                     "peak_source": f"{peaks['source']} bf16_tflops_sustained (kernel timed inside a long step)",
                     "launches_per_step": g["launches"] / args.steps, "share_of_step_kernel_time": g["share"],
                     "avg_launch_ms": g["ms"] / max(g["launches"], 1),
