@@ -9,14 +9,16 @@
 //   reduce-scatter  rank r reads shard r of the gradient arena of all W ranks through NVLink (128-bit loads,
 //                   coalesced, W independent streams in flight per thread) and averages them
 //   Adam            on its shard of p / m / v (the moments exist only where they are used)
-//   all-gather      the new fp32 parameters and their bf16 shadow are STORED into all W ranks' arenas, and shard
-//                   r of every rank's gradient arena is cleared for the next backward pass
+//   all-gather      the new fp32 parameters and their bf16 shadow are STORED into all W ranks' arenas
 //   end barrier     a rank's kernel ends only when every peer has finished writing into its arenas
+//   clear           every CTA clears its stripe of the LOCAL gradient arena (all peers have read it by now)
 //
-// No shared memory and a few dozen CTAs: the kernel can run beside persistent GEMM CTAs that own every SM's
-// shared memory (the reason NCCL's copy kernels could not be overlapped), and the transfers
-// are bound by the NVLink ports, not by SM count.  Per rank and step: 4 N bytes read and 10 N bytes written over
-// the links (N = parameters) against 8 N + 8 N for a ring all-reduce followed by a separate 34 N-byte Adam pass.
+// No shared memory: the kernel could run beside persistent GEMM CTAs that own every SM's shared memory (the reason
+// NCCL's copy kernels could not be overlapped); the grid is clamped to a co-resident size
+// because every CTA waits for the last one.  Per rank and step, with N parameters and W ranks: (W-1)/W * 4 N bytes
+// read and (W-1)/W * 6 N bytes written over the links (the same amounts arrive), plus one local pass over the
+// shard's p / m / v -- against ~2 (W-1)/W * 4 N per direction for an all-reduce followed by a separate 34 N-byte
+// Adam pass.  Measured: DESIGN.md section 6 (link-bound at W = 8).
 #include <math.h>
 
 #include "common.cuh"
