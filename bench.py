@@ -313,6 +313,17 @@ def dist_setup(n_gpus: int):
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    if world > 1 and os.environ.get("NC_PIN_CORES", "1") == "1" and hasattr(os, "sched_setaffinity"):
+        # N Python processes on one box: give every rank its own slice of the cores it may run on (they all start
+        # with the same affinity mask, and the slowest rank's enqueue loop sets the pace of a step)
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = len(cores) // world
+            if per >= 1:
+                os.sched_setaffinity(0, set(cores[local * per:(local + 1) * per]))
+                torch.set_num_threads(max(per, 1))
+        except OSError:
+            pass
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))

@@ -629,6 +629,22 @@ def mask_info(mask: Optional[torch.Tensor]):
     return info
 
 
+_EFF_MASK = {}
+
+
+def _effective_mask(m: torch.Tensor, d: torch.Tensor) -> torch.Tensor:
+    """static mask * dynamic mask, cached per pair of tensor versions (a new product every call would also defeat
+    ``mask_info``'s cache: one host read-back and one CSR build per decoder and iteration)."""
+    key = (m.data_ptr(), m._version, d.data_ptr(), d._version, tuple(m.shape))
+    hit = _EFF_MASK.pop(key, None)
+    if hit is None:
+        while len(_EFF_MASK) >= 16:
+            _EFF_MASK.pop(next(iter(_EFF_MASK)))
+        hit = (m * d, m, d)                    # operands kept: their addresses cannot be recycled while the entry lives
+    _EFF_MASK[key] = hit
+    return hit[0]
+
+
 class MaskedDecoderFn(torch.autograd.Function):
     """logits = cat(z, embed) @ (W * mask)^T for the decoder weight blocks
     [F, P_prior | P_addon | n_embed] (nn/layers.py:83-142, nn/layercomponents.py:53-81) as ONE
@@ -642,7 +658,7 @@ class MaskedDecoderFn(torch.autograd.Function):
         eff_masks = []
         for m, d in zip(masks, dyn_masks):
             if m is not None and d is not None:
-                m = m * d
+                m = _effective_mask(m, d)
             elif d is not None:
                 m = d
             eff_masks.append(m)

@@ -272,6 +272,17 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
             self.features_idx_dict_[f"{ent}_reconstructed_{mod}_idx"] = hit[2].tolist()
         return hit[1], hit[2]
 
+    def _atac_dynamic_mask_on_device(self, key: str) -> torch.Tensor:
+        """The [P, n_peaks] bool dynamic mask of an ATAC decoder, moved to the module's device ONCE (it is a plain
+        attribute, not a buffer, as in the reference: a ``.to(device)`` per forward was an 80 MB pageable
+        host-to-device copy per decoder and iteration at config 4)."""
+        name = f"{key}_dynamic_decoder_mask"
+        dyn = getattr(self, name)
+        if dyn.device != self.device:
+            dyn = dyn.to(self.device)
+            setattr(self, name, dyn)
+        return dyn
+
     # ------------------------------------------------------------------ batch normalisation
     def _embed(self, cats: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
         if self.n_cat_covariates_ == 0:
@@ -437,7 +448,7 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
                 key = f"{ent}_{mod}"
                 sel, ridx = self._reconstructed(key, self.materialize_outputs)
                 dec = getattr(self, f"{key}_decoder")
-                dyn = getattr(self, f"{key}_dynamic_decoder_mask").to(self.device) if mod == "atac" else None
+                dyn = self._atac_dynamic_mask_on_device(key) if mod == "atac" else None
                 e = emb_b if (emb_b is not None and inj[mod] in self.cat_covariates_embeds_injection_) else None
                 logits = dec.logits(z, e, dyn)
                 labels_full = xsrc[:, cols[mod]]
@@ -754,7 +765,7 @@ class VGPGAE(nn.Module, BaseModuleMixin, VGAEModuleMixin):
             for ent, xsrc in (("target", x_t), ("source", x_n)):
                 key = f"{ent}_{mod}"
                 dec = getattr(self, f"{key}_decoder")
-                dyn = getattr(self, f"{key}_dynamic_decoder_mask").to(self.device) if mod == "atac" else None
+                dyn = self._atac_dynamic_mask_on_device(key) if mod == "atac" else None
                 e = emb_b if (emb_b is not None and inj[mod] in self.cat_covariates_embeds_injection_) else None
                 logits = dec.logits(z, e, dyn)
                 labels = xsrc[:, cols[mod]].contiguous()
