@@ -281,11 +281,19 @@ class Trainer(BaseTrainerMixin):
         joint = getattr(m, "joint_supported", None)
         return (m.training and self.joint_encoder_ and joint is not None and joint(node_batch, edge_batch)
                 and m._eps_queue is None and getattr(self, "after_backward", None) is None and _lib._HOOK is None
-                and m.n_cat_covariates_ == 0 and m.node_label_method_ != "one-hop-attention"
+                and (m.n_cat_covariates_ == 0 or self._covariates_capturable())
+                and m.node_label_method_ != "one-hop-attention"
                 and "atac" not in m.modalities_
                 and int(node_batch.batch_size) == int(self.node_batch_size_)
                 and edge_batch.edge_label_index.size(1) == 2 * int(self.edge_batch_size_)
                 and getattr(edge_batch, "_joint_input", None) is None)
+
+    def _covariates_capturable(self) -> bool:
+        """Covariate embeddings (config 3) inside the captured iteration: the categories of the sampled cells become
+        static inputs.  Not with the contrastive loss (its top-k selection reads a count back on the host)."""
+        contrastive = ((self.lambda_cat_covariates_contrastive_ or 0) > 0
+                       and ((self.contrastive_logits_pos_ratio_ or 0) > 0 or (self.contrastive_logits_neg_ratio_ or 0) > 0))
+        return not contrastive
 
     def _bucket_sizes(self, node_batch, edge_batch):
         gn, ge = node_batch.graph, edge_batch.graph
@@ -368,6 +376,11 @@ class Trainer(BaseTrainerMixin):
             S.eli, S.elab = torch.zeros_like(eli), torch.zeros_like(edge_batch.edge_label)
             S.eps_n = torch.zeros(nb, P, dtype=torch.float32, device=dev)
             S.eps_e = torch.zeros(eli.size(1) * 2, P, dtype=torch.float32, device=dev)
+            S.cats_n = S.cats_e = None
+            if m.n_cat_covariates_ > 0:                    # categories of the node seeds / of every edge-batch cell
+                cn = node_batch.cat_covariates_cats
+                S.cats_n = torch.zeros(nb, cn.size(1), dtype=cn.dtype, device=dev)
+                S.cats_e = torch.zeros(n_sub_pad, cn.size(1), dtype=cn.dtype, device=dev)
         # ---- per-iteration inputs (eager, a handful of launches)
         staged = getattr(edge_batch, "_graph_staged", None)
         if staged is not None and staged[0].n_sub_pad == n_sub_pad and staged[0].e_pad == e_pad:
@@ -381,6 +394,9 @@ class Trainer(BaseTrainerMixin):
             self._graph_inputs(node_batch, edge_batch, S, background=False)
         S.eli.copy_(edge_batch.edge_label_index)
         S.elab.copy_(edge_batch.edge_label)
+        if S.cats_n is not None:
+            S.cats_n.copy_(node_batch.cat_covariates_cats[:S.cats_n.size(0)])
+            S.cats_e[:edge_batch.cat_covariates_cats.size(0)].copy_(edge_batch.cat_covariates_cats)
         S.eps_n.normal_()                                  # same draws, same order as the eager path's randn_like
         S.eps_e.normal_()
         opt.sync_lr()
@@ -430,9 +446,11 @@ class Trainer(BaseTrainerMixin):
         gm = SubgraphCSR(S.m_rowptr, S.m_col, S.n_sub_pad, S.n_dst_pad, self._graph_max_deg(), e_dst=S.e_pad)
         x_enc = S.x_enc if S.x_enc is not None else ops.csr_gather_rows(
             store, S.m_nid, S.n_sub_pad, m.log_variational_, m.compute_dtype, pad8(m.encoder.n_input))
-        node_b = SimpleNamespace(store=store, batch_size=nb, n_id=None, graph=SimpleNamespace(n_dst=nb, n_nodes=nb))
+        node_b = SimpleNamespace(store=store, batch_size=nb, n_id=None, graph=SimpleNamespace(n_dst=nb, n_nodes=nb),
+                                 cat_covariates_cats=S.cats_n)
         edge_b = SimpleNamespace(store=store, edge_label_index=S.eli, edge_label=S.elab, n_id=None,
-                                 graph=SimpleNamespace(n_dst=S.n_dst_pad - nb, n_nodes=S.n_sub_pad - nb))
+                                 graph=SimpleNamespace(n_dst=S.n_dst_pad - nb, n_nodes=S.n_sub_pad - nb),
+                                 cat_covariates_cats=S.cats_e)
         edge_b._joint_input = (node_b, gm, x_enc, None, (S.x_t, S.x_n))
         m._eps_queue = [S.eps_n, S.eps_e]
         try:

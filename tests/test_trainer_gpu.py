@@ -379,3 +379,35 @@ def test_cuda_graph_iterations_equal_eager_iterations(dtype, use_active, store):
                 assert float((sd_e[k] - sd_g[k]).abs().max()) <= 2e-3 * 8 * 1e-3 + 1e-6 * float(sd_e[k].abs().max()) + 1e-3 * 2 * 8, k
         assert tr_g.optimizer.step_count == tr_e.optimizer.step_count == 8
         assert abs(float(tr_g.optimizer.dyn[1]) - 9.0) < 1e-6
+
+
+def test_cuda_graph_iterations_with_covariate_embeddings_equal_eager_iterations():
+    """Config-3 shape (sample covariate, embedding injected into the decoders, no cross-sample edges) in the captured
+    iteration: the categories of the sampled cells are static inputs of the graph."""
+    from nichecompass_b200.models import NicheCompass
+    from nichecompass_b200.train import Trainer
+    adata = H.tiny_problem(n_cells=600, n_genes=44, n_prior_gp=12, n_samples=2)
+
+    def run(graphs):
+        with contextlib.redirect_stdout(io.StringIO()):
+            model = NicheCompass(adata, n_addon_gp=4, cat_covariates_keys=["batch"], seed=0)
+            tr = Trainer(adata, model.model, cat_covariates_keys=["batch"], edge_batch_size=32, seed=0, monitor=False,
+                         compute_dtype=torch.float32, cuda_graphs=graphs)
+            tr.setup_training(lr=1e-3, **LAM)
+        torch.manual_seed(11)
+        torch.cuda.manual_seed(11)
+        logs = []
+        for i, (eb, nb) in enumerate(tr.joint_batches(tr.edge_train_loader, tr.node_train_loader)):
+            logs.append({k: float(v) for k, v in tr.train_iteration(eb, nb).items()})
+            if i + 1 == 8:
+                break
+        return tr, logs
+    tr_e, eager = run(False)
+    tr_g, graph = run(True)
+    assert tr_g.model.n_cat_covariates_ == 1 and tr_g.graph_stats_["replayed"] >= 5, tr_g.graph_stats_
+    for it, (a, b) in enumerate(zip(graph, eager)):
+        for k in b:
+            assert abs(a[k] - b[k]) <= 2e-6 * abs(b[k]) * (1 + it) + 1e-10, (it, k, a[k], b[k])
+    we = tr_e.model.state_dict()["cat_covariate0_embedder.weight"]
+    wg = tr_g.model.state_dict()["cat_covariate0_embedder.weight"]
+    assert float((we - wg).abs().max()) <= 2e-3 * 8 * 1e-3 + 1.6e-2 and not torch.equal(wg, torch.zeros_like(wg))
