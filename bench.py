@@ -586,7 +586,8 @@ def run_ours(args):
                  "cells_per_s_train_only": wl["n_cells"] / t_train,
                  "cells_per_s_with_validation": wl["n_cells"] / (t_train + t_val),
                  "val_auroc": metrics.get("auroc_score"),
-                 "note": "measured over the whole epoch; validation is replicated on every rank"}
+                 "note": "measured over the whole epoch; the validation batches are sharded over the ranks and the metrics "
+                         "computed on the gathered logits"}
     result = None
     if rank == 0:
         peaks = measured_peaks()
