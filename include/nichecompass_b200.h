@@ -64,6 +64,17 @@ int nc_gcn_norm_weights(const int32_t* rowptr, const int32_t* col, int32_t n_nod
                         int32_t n_rows, int use_out_degree, int32_t* deg_ws, float* w,
                         float* wself, void* stream);
 
+/* nc_gcn_norm_weights without the deg_ws argument and without any allocation: the degree scratch
+ * is a static device array inside the library (4 MiB per GPU, held until exit), for callers
+ * that cannot allocate (stream capture, serving loops).  NO COUNTERPART IN THE REFERENCE.
+ * Limit: n_nodes <= 1 048 576 (NC_EUNSUPPORTED beyond
+ * it).  Same w / wself as nc_gcn_norm_weights.  All calls on a device share the scratch: it is
+ * cleared at the start of every call, and calls that overlap on the GPU (different streams
+ * without ordering) race on it.                                                              */
+int nc_gcn_norm_weights_noalloc(const int32_t* rowptr, const int32_t* col, int32_t n_nodes,
+                                int32_t n_rows, int use_out_degree, float* w, float* wself,
+                                void* stream);
+
 /* Reverse (by-source) view of the first n_rows rows of a dst-CSR.  add_self == 1: self entries
  * dropped and one self edge i->i appended for every i < n_rows (GATv2Conv); 0: self entries
  * dropped; 2: every entry kept as given, nothing appended (attention aggregator).

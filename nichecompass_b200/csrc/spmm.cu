@@ -54,6 +54,63 @@ extern "C" int nc_gcn_norm_weights(const int32_t* rowptr, const int32_t* col, in
     return NC_OK;
 }
 
+// ---------------------------------------------------------------------------- no-allocation variant
+// Same three kernels, degree scratch in a file-scope device array instead of a caller buffer: for callers that cannot
+// allocate (stream capture, serving loops).  No counterpart in the reference.
+// 4 MiB of every GPU that loads the library, held until exit.  Every call on a device shares the array:
+// it is cleared at the start of each call (k_zero_i32), and two calls that overlap on the GPU (different streams)
+// race on it.
+#define NC_NOALLOC_MAX_NODES (1 << 20)
+static __device__ __align__(256) int32_t g_noalloc_deg[NC_NOALLOC_MAX_NODES];
+
+// Device address of g_noalloc_deg on the CURRENT device (the name is only a host-side handle in host code),
+// resolved once per device.
+static int noalloc_deg_ptr(int32_t** out) {
+    static int32_t* ptrs[64] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        nc_set_error("nc_gcn_norm_weights_noalloc: cudaGetDevice failed or device index %d out of range: %s", dev,
+                     cudaGetErrorString(e));
+        return NC_ECUDA;
+    }
+    int32_t* p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        e = cudaGetSymbolAddress((void**)&p, g_noalloc_deg);
+        if (e != cudaSuccess || p == nullptr) {
+            cudaGetLastError();
+            nc_set_error("nc_gcn_norm_weights_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                         cudaGetErrorString(e));
+            return NC_ECUDA;
+        }
+        __atomic_store_n(&ptrs[dev], p, __ATOMIC_RELEASE);       // every thread resolves the same address
+    }
+    *out = p;
+    return NC_OK;
+}
+
+extern "C" int nc_gcn_norm_weights_noalloc(const int32_t* rowptr, const int32_t* col, int32_t n_nodes,
+                                           int32_t n_rows, int use_out_degree, float* w, float* wself,
+                                           void* stream) {
+    NC_REQUIRE(n_nodes >= 0 && n_rows >= 0 && n_rows <= n_nodes, NC_ESHAPE,
+               "nc_gcn_norm_weights_noalloc: need 0 <= n_rows <= n_nodes (got %d, %d)", n_rows, n_nodes);
+    NC_REQUIRE(n_nodes <= NC_NOALLOC_MAX_NODES, NC_EUNSUPPORTED,
+               "nc_gcn_norm_weights_noalloc: n_nodes = %d exceeds the static scratch of %d nodes; use "
+               "nc_gcn_norm_weights with a caller-provided deg_ws", n_nodes, NC_NOALLOC_MAX_NODES);
+    if (n_nodes == 0) return NC_OK;
+    int32_t* deg = nullptr;
+    int rc = noalloc_deg_ptr(&deg);
+    if (rc != NC_OK) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int T = 256;
+    k_zero_i32<<<nc_cdiv(n_nodes, T), T, 0, s>>>(deg, n_nodes);
+    k_degree<<<nc_cdiv(n_nodes, T), T, 0, s>>>(rowptr, col, n_nodes, use_out_degree, deg);
+    if (n_rows > 0) k_norm_weights<<<nc_cdiv(n_rows, T), T, 0, s>>>(rowptr, col, n_rows, deg, w, wself);
+    nc_count_launch(n_rows > 0 ? 3 : 2);
+    NC_CHECK_LAUNCH("nc_gcn_norm_weights_noalloc");
+    return NC_OK;
+}
+
 // ============================================================================ reverse CSR
 __global__ void k_rev_count(const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
                             int32_t n_rows, int add_self, int32_t* __restrict__ cnt) {
