@@ -40,6 +40,9 @@ struct RingSeg { int off, C4, out_off, ch, st_off; };   // st_off: byte offset o
 struct RingPlan {
     RingSeg a[RW_MAX], b[RW_MAX];                  // b[w].C4 == 0: warp w has one segment only
     int n_warps, NL, n_stages, stage_bytes, row_bytes, sc_stride, NCH, out_width, max_deg1, meta_off, bar_off, sc_off;
+    int lane_off;   // per-thread scratch [warp][chunk][lane] of 16 bytes: att (forward) / the target's dout (backward)
+    int full;       // every warp's segments fill all chunks but (possibly) the last one: compile-time row offsets
+    int e_mask_off, e_al_off;   // per-source kernel: offsets of the sign words / the alpha + d score rows in a stage
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -83,6 +86,27 @@ __device__ __forceinline__ uint2 pack_bf4(float4 v) {
     return r;
 }
 __device__ __forceinline__ float lrelu(float v, float slope) { return fmaxf(v, v * slope); }   // 0 < slope < 1
+
+// Packed fp32 pairs (FFMA2 / FADD2 on sm_100): half the issue slots of the scalar forms.  A 64-bit word of a row
+// holds four bf16: (lo, hi) of .x -> elements 0, 1; of .y -> elements 2, 3.
+__device__ __forceinline__ float2 bf2lo(uint2 r) { return make_float2(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u)); }
+__device__ __forceinline__ float2 bf2hi(uint2 r) { return make_float2(__uint_as_float(r.y << 16), __uint_as_float(r.y & 0xffff0000u)); }
+__device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
+
+// Sums of two values over the warp, both returned in every lane: lanes 0-15 reduce a, lanes 16-31 reduce b
+// (7 shuffles with a dependent chain of 6, instead of 10 in a chain of 10 for two butterflies).
+__device__ __forceinline__ void warp_sum2(float& a, float& b, int lane) {
+    const bool up = (lane & 16) != 0;
+    float v = up ? b : a;
+    const float o = up ? a : b;
+    v += __shfl_xor_sync(0xffffffffu, o, 16);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    a = __shfl_sync(0xffffffffu, v, 0);
+    b = __shfl_sync(0xffffffffu, v, 16);
+}
 
 // ---------------------------------------------------------------------------------- CTA pipeline
 // One producer warp per CTA enumerates, for the targets ir = blockIdx.x, + gridDim.x, ..., the rows
@@ -206,16 +230,28 @@ __device__ __forceinline__ void producer_loop(const Ring& R, const RingPlan& P, 
 }
 
 // ---------------------------------------------------------------------------------- forward
+// Byte offset of chunk k of this lane inside a stage.  FULL plans (every warp's segments fill all chunks but
+// possibly the last): compile-time offsets from one base register, only the last chunk of a segment selects
+// between its own address and a valid dummy (offS) for the lanes past the segment's end.
+#define ROFF(k)                                                                                                  \
+    (FULL ? ((k) < NVA ? ((k) == NVA - 1 ? offAl : offA + 256u * (uint32_t)(k))                                  \
+                       : ((k) == NV - 1 ? offBl : offB + 256u * (uint32_t)((k) - NVA)))                           \
+          : ((((vmask) >> (k)) & 1u) ? ((k) < NVA ? offA + 256u * (uint32_t)(k)                                  \
+                                                  : offB + 256u * (uint32_t)((k) - NVA)) : offS))
+
 // Instruction diet of the inner loop (the first version of this kernel issued 15 instructions per row element and
 // was bound by issue slots -- 2 warps per scheduler, IPC 0.5 -- not by memory; ncu: profiles/r2_gatv2_*):
 //   * leaky_relu(v) = c1 v + c2 |v| with c1 = (1 + slope) / 2, c2 = (1 - slope) / 2, so the score is
 //     c1 <att, x_l[j]> + c2 <att, |x_l[j] + x_r[i]|> (+ c1 <att, x_r[i]>, which is the same for every neighbour of i
-//     and cancels in the softmax): one add and two fused multiply-adds per element (|.| is an operand modifier),
-//     instead of add, multiply, max, multiply-add;
-//   * x_r[i] and att live in registers as fp32 for the whole target (no re-unpacking per row);
+//     and cancels in the softmax): half a packed add, half a packed multiply-add and one multiply-add with |.| as an
+//     operand modifier per element, instead of add, multiply, max, multiply-add;
+//   * a row is unpacked to fp32 ONCE and stays in registers from the score to the weighted accumulation (the stage
+//     is released as soon as it is unpacked); att moved from 52 registers to a per-thread shared-memory slot (one
+//     LDS.128 per chunk and row) to make room for it;
+//   * fp32 arithmetic in pairs (FFMA2 / FADD2); the two head scores of a warp are reduced in one butterfly;
 //   * lanes past the end of a segment read the first element of the slot (valid data) with att = 0 instead of
 //     branching around every 128-bit chunk.
-template <int NVA, int NVB>
+template <int NVA, int NVB, bool FULL>
 __global__ void __launch_bounds__(RING_THREADS, 1)
 k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restrict__ xl,
                const __nv_bfloat16* __restrict__ xr, int64_t ld, const float* __restrict__ att,
@@ -238,28 +274,30 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
     uint32_t vmask = 0;
     // offS: a valid, 8-byte aligned element of the slot for the lanes past the end of a segment
     const uint32_t offA = (uint32_t)(sa.st_off + 8 * lane), offB = (uint32_t)(sb.st_off + 8 * lane), offS = (uint32_t)sa.st_off;
-    float4 attv[NV];
+    // this thread's slot of the per-lane scratch: al_[k * 32] = att of chunk k (0 past the end of a segment)
+    float4* al_ = reinterpret_cast<float4*>(smem + P.lane_off) + (size_t)warp * NV * 32 + lane;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
         const bool isA = k < NVA;
-        const int kk = isA ? k : k - NVA;
-        const int u = lane + 32 * kk;
-        attv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int u = lane + 32 * (isA ? k : k - NVA);
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
         if (u < (isA ? sa.C4 : sb.C4)) {
             vmask |= 1u << k;
-            attv[k] = __ldg(reinterpret_cast<const float4*>(att + (isA ? sa.off : sb.off) + 4 * u));
+            a = __ldg(reinterpret_cast<const float4*>(att + (isA ? sa.off : sb.off) + 4 * u));
         }
+        al_[k * 32] = a;
     }
-#define BOFF(k) ((((vmask) >> (k)) & 1u) ? ((k) < NVA ? offA + 256u * (uint32_t)(k) : offB + 256u * (uint32_t)((k) - NVA)) : offS)
+    const uint32_t offAl = ((vmask >> (NVA - 1)) & 1u) ? offA + 256u * (uint32_t)(NVA - 1) : offS;
+    const uint32_t offBl = (NVB > 0 && ((vmask >> (NV - 1)) & 1u)) ? offB + 256u * (uint32_t)(NVB > 0 ? NVB - 1 : 0) : offS;
     float* scA = reinterpret_cast<float*>(smem + P.sc_off + (size_t)warp * P.sc_stride);
     float* scB = scA + P.max_deg1;
     if (alpha) {
         for (int t = lane; t < P.max_deg1; t += 32) { scA[t] = -INFINITY; scB[t] = -INFINITY; }
         __syncwarp();
     }
-    float4 xrv[NV], acc[NV];
+    float2 xrv[NV][2], acc[NV][2];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) { xrv[k] = make_float4(0.f, 0.f, 0.f, 0.f); acc[k] = make_float4(0.f, 0.f, 0.f, 0.f); }
+    for (int k = 0; k < NV; ++k) xrv[k][0] = xrv[k][1] = acc[k][0] = acc[k][1] = f2(0.f, 0.f);
     float mA = -INFINITY, lA = 0.f, mB = -INFINITY, lB = 0.f;
     int slot0 = 0, nE = 0;
     uint32_t stage = 0, round = 0;
@@ -267,37 +305,53 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
         mbar_wait(&R.full[stage], round & 1);
         const uint8_t* row = R.base + (size_t)stage * P.stage_bytes;
         const int4 meta = R.meta[stage];
-        uint2 raw[NV];
+        float2 fv[NV][2];
 #pragma unroll
-        for (int k = 0; k < NV; ++k) raw[k] = *reinterpret_cast<const uint2*>(row + BOFF(k));
+        for (int k = 0; k < NV; ++k) {
+            const uint2 raw = *reinterpret_cast<const uint2*>(row + ROFF(k));
+            fv[k][0] = bf2lo(raw);
+            fv[k][1] = bf2hi(raw);
+        }
         __syncwarp();                                        // the row now lives in registers: release the stage
         if (lane == 0) mbar_arrive(&R.empty[stage]);
         if ((meta.x & 255) == K_XR) {
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                xrv[k] = bf4(raw[k]);
-                acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                xrv[k][0] = fv[k][0];
+                xrv[k][1] = fv[k][1];
+                acc[k][0] = acc[k][1] = f2(0.f, 0.f);
             }
             mA = mB = -INFINITY;
             lA = lB = 0.f;
             slot0 = meta.z;
             nE = min(meta.w, P.max_deg1);
         } else {
-            // (the row stays packed in `raw` and is unpacked again for the accumulation: 26 registers instead of 52)
-            float s1A = 0.f, s2A = 0.f, s1B = 0.f, s2B = 0.f;
+            float2 s1A0 = f2(0.f, 0.f), s1A1 = f2(0.f, 0.f), s1B = f2(0.f, 0.f);
+            float s2A0 = 0.f, s2A1 = 0.f, s2A2 = 0.f, s2A3 = 0.f, s2B0 = 0.f, s2B1 = 0.f;
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                const float4 f = bf4(raw[k]);
-                const float4 a = attv[k], x = xrv[k];
-                float t1 = a.x * f.x, t2 = a.x * fabsf(f.x + x.x);
-                t1 = fmaf(a.y, f.y, t1); t2 = fmaf(a.y, fabsf(f.y + x.y), t2);
-                t1 = fmaf(a.z, f.z, t1); t2 = fmaf(a.z, fabsf(f.z + x.z), t2);
-                t1 = fmaf(a.w, f.w, t1); t2 = fmaf(a.w, fabsf(f.w + x.w), t2);
-                if (k < NVA) { s1A += t1; s2A += t2; } else { s1B += t1; s2B += t2; }
+                const float4 a = al_[k * 32];
+                const float2 v0 = __fadd2_rn(fv[k][0], xrv[k][0]), v1 = __fadd2_rn(fv[k][1], xrv[k][1]);
+                if (k < NVA) {
+                    s1A0 = __ffma2_rn(f2(a.x, a.y), fv[k][0], s1A0);
+                    s1A1 = __ffma2_rn(f2(a.z, a.w), fv[k][1], s1A1);
+                    s2A0 = fmaf(a.x, fabsf(v0.x), s2A0); s2A1 = fmaf(a.y, fabsf(v0.y), s2A1);
+                    s2A2 = fmaf(a.z, fabsf(v1.x), s2A2); s2A3 = fmaf(a.w, fabsf(v1.y), s2A3);
+                } else {
+                    s1B = __ffma2_rn(f2(a.x, a.y), fv[k][0], s1B);
+                    s1B = __ffma2_rn(f2(a.z, a.w), fv[k][1], s1B);
+                    s2B0 = fmaf(a.x, fabsf(v0.x), s2B0); s2B1 = fmaf(a.y, fabsf(v0.y), s2B1);
+                    s2B0 = fmaf(a.z, fabsf(v1.x), s2B0); s2B1 = fmaf(a.w, fabsf(v1.y), s2B1);
+                }
             }
-            float pA = warp_sum(fmaf(c1, s1A, c2 * s2A));
+            float pA = fmaf(c1, (s1A0.x + s1A0.y) + (s1A1.x + s1A1.y), c2 * ((s2A0 + s2A1) + (s2A2 + s2A3)));
             float pB = 0.f;
-            if (NVB > 0) pB = warp_sum(fmaf(c1, s1B, c2 * s2B));
+            if (NVB > 0) {
+                pB = fmaf(c1, s1B.x + s1B.y, c2 * (s2B0 + s2B1));
+                warp_sum2(pA, pB, lane);
+            } else {
+                pA = warp_sum(pA);
+            }
             const int t = meta.w;
             if (alpha && lane == 0 && t < P.max_deg1) { scA[t] = pA; scB[t] = pB; }
             {
@@ -305,25 +359,26 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
                 lA = lA * corr + w;
                 mA = mn;
                 if (corr != 1.f) {
+                    const float2 c = f2(corr, corr);
 #pragma unroll
-                    for (int k = 0; k < NVA; ++k) { acc[k].x *= corr; acc[k].y *= corr; acc[k].z *= corr; acc[k].w *= corr; }
+                    for (int k = 0; k < NVA; ++k) { acc[k][0] = __fmul2_rn(acc[k][0], c); acc[k][1] = __fmul2_rn(acc[k][1], c); }
                 }
+                const float2 w2 = f2(w, w);
 #pragma unroll
                 for (int k = 0; k < NVA; ++k) {
-                    const float4 f = bf4(raw[k]);
-                    acc[k].x = fmaf(w, f.x, acc[k].x); acc[k].y = fmaf(w, f.y, acc[k].y);
-                    acc[k].z = fmaf(w, f.z, acc[k].z); acc[k].w = fmaf(w, f.w, acc[k].w);
+                    acc[k][0] = __ffma2_rn(w2, fv[k][0], acc[k][0]);
+                    acc[k][1] = __ffma2_rn(w2, fv[k][1], acc[k][1]);
                 }
             }
             if (NVB > 0) {
                 const float mn = fmaxf(mB, pB), corr = __expf(mB - mn), w = __expf(pB - mn);
                 lB = lB * corr + w;
                 mB = mn;
+                const float2 c = f2(corr, corr), w2 = f2(w, w);
 #pragma unroll
                 for (int k = NVA; k < NV; ++k) {
-                    const float4 f = bf4(raw[k]);
-                    acc[k].x = fmaf(w, f.x, acc[k].x * corr); acc[k].y = fmaf(w, f.y, acc[k].y * corr);
-                    acc[k].z = fmaf(w, f.z, acc[k].z * corr); acc[k].w = fmaf(w, f.w, acc[k].w * corr);
+                    acc[k][0] = __ffma2_rn(w2, fv[k][0], __fmul2_rn(acc[k][0], c));
+                    acc[k][1] = __ffma2_rn(w2, fv[k][1], __fmul2_rn(acc[k][1], c));
                 }
             }
             if (meta.x & K_LAST) {
@@ -337,7 +392,7 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
                         const int u = lane + 32 * (isA ? k : k - NVA);
                         const float inv = isA ? iA : iB;
                         *reinterpret_cast<float4*>(orow + (isA ? sa.off : sb.off) + 4 * u) =
-                            make_float4(acc[k].x * inv, acc[k].y * inv, acc[k].z * inv, acc[k].w * inv);
+                            make_float4(acc[k][0].x * inv, acc[k][0].y * inv, acc[k][1].x * inv, acc[k][1].y * inv);
                     }
                 }
                 if (alpha) {
@@ -360,7 +415,7 @@ k_gat_ring_fwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
     }
 }
 
-#undef BOFF
+#undef ROFF
 
 // out[ir, out_off_c + k] = mean_h O[ir, off_c + h * C_c + k] + bias   (one CTA per target)
 __global__ void __launch_bounds__(256)
@@ -385,36 +440,33 @@ k_gat_head_mean(const float* __restrict__ head_out, int64_t ld, const int32_t* _
     }
 }
 
-// D[ir, c * H + h] = <dout[ir, out_off_c : + C_c], O[ir, off_c + h * C_c : + C_c]> / H  (= sum_t alpha_t dalpha_t)
-__global__ void __launch_bounds__(256)
-k_gat_D(const float* __restrict__ head_out, int64_t ld, const float* __restrict__ dout, int64_t ldo,
-        const int32_t* __restrict__ seg, int n_conv, int H, float* __restrict__ Dbuf) {
-    const int ir = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const float invH = 1.0f / (float)H;
-    for (int ch = warp; ch < n_conv * H; ch += 8) {
-        const int c = ch / H, h = ch - c * H;
-        const int off = seg[c * 4], C = seg[c * 4 + 1], oo = seg[c * 4 + 2];
-        const float* o = head_out + (int64_t)ir * ld + off + h * C;
-        const float* g = dout + (int64_t)ir * ldo + oo;
-        float p = 0.f;
-        for (int k = lane * 4; k < C; k += 128) {
-            const float4 a = *reinterpret_cast<const float4*>(o + k);
-            const float4 b = __ldg(reinterpret_cast<const float4*>(g + k));
-            p += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
-        }
-        p = warp_sum(p);
-        if (lane == 0) Dbuf[(int64_t)ir * n_conv * H + ch] = p * invH;
-    }
-}
-
 // ---------------------------------------------------------------------------------- backward, per target
-template <int NVA, int NVB>
+// Byte offset of chunk k of this lane inside a stage.  FULL plans (every warp's segments fill all chunks but
+// possibly the last): compile-time offsets from one base register, only the last chunk of a segment selects
+// between its own address and a valid dummy (offS) for the lanes past the segment's end.
+#define ROFF(k)                                                                                                  \
+    (FULL ? ((k) < NVA ? ((k) == NVA - 1 ? offAl : offA + 256u * (uint32_t)(k))                                  \
+                       : ((k) == NV - 1 ? offBl : offB + 256u * (uint32_t)((k) - NVA)))                           \
+          : ((((vmask) >> (k)) & 1u) ? ((k) < NVA ? offA + 256u * (uint32_t)(k)                                  \
+                                                  : offB + 256u * (uint32_t)((k) - NVA)) : offS))
+
+// Instruction diet (the first ring version of this kernel issued ~16 instructions per row element, kept 52 + 52 +
+// 52 + 26 values per thread live and spilled in the inner loop -- 3.9 long-scoreboard stall cycles per issue):
+//   * the target's dout segment lives in a per-thread shared-memory slot (written once per target, one LDS.128 per
+//     chunk and row) instead of 52 registers: no spills;
+//   * D_h = <g, O_h> / H is computed here when the target's x_r row arrives (was a kernel of its own + a round trip);
+//   * v = x_l[j] + x_r[i] is added in round-down mode, where an exact zero comes out as -0 (x_r is stored with its
+//     zeros as -0, so no pair of operands is (+0, +0)): the sign bit of v is exactly "v <= 0", what torch's
+//     leaky_relu backward tests.  The sign bits are shifted into the mask word with one funnel shift per element,
+//     and d lrelu = ds * (c1 + c2 * sgn v) is E + (q xor sign bit): one LOP3 and half a packed add per element;
+//   * all fp32 arithmetic in pairs (FFMA2 / FADD2).
+template <int NVA, int NVB, bool FULL>
 __global__ void __launch_bounds__(RING_THREADS, 1)
 k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restrict__ xl,
                const __nv_bfloat16* __restrict__ xr, int64_t ld, const float* __restrict__ att,
                const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col, int n_dst, float slope,
                float invH, const float* __restrict__ dout, int64_t ldo, const float* __restrict__ alpha,
-               const float* __restrict__ Dbuf, float* __restrict__ ds, __nv_bfloat16* __restrict__ dxr,
+               const float* __restrict__ head_out, float* __restrict__ ds, __nv_bfloat16* __restrict__ dxr,
                float* __restrict__ datt, uint32_t* __restrict__ mask) {
     constexpr int NV = NVA + NVB;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -429,8 +481,7 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
     }
     asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const RingSeg sa = P.a[warp], sb = P.b[warp];
-    // lanes past the end of a segment read the first element of the slot (valid data) and carry g = 0: no branch
-    // around the 128-bit chunks (same diet as the forward kernel)
+    const float c1 = 0.5f * (1.0f + slope), c2 = 0.5f * (1.0f - slope);
     uint32_t vmask = 0;
     const uint32_t offA = (uint32_t)(sa.st_off + 8 * lane), offB = (uint32_t)(sb.st_off + 8 * lane), offS = (uint32_t)sa.st_off;
 #pragma unroll
@@ -439,13 +490,14 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
         const int u = lane + 32 * (isA ? k : k - NVA);
         if (u < (isA ? sa.C4 : sb.C4)) vmask |= 1u << k;
     }
-#define BOFF(k) ((((vmask) >> (k)) & 1u) ? ((k) < NVA ? offA + 256u * (uint32_t)(k) : offB + 256u * (uint32_t)((k) - NVA)) : offS)
-    float4 gv[NV], dxa[NV], dat[NV];
-    uint2 xrv[NV];
+    const uint32_t offAl = ((vmask >> (NVA - 1)) & 1u) ? offA + 256u * (uint32_t)(NVA - 1) : offS;
+    const uint32_t offBl = (NVB > 0 && ((vmask >> (NV - 1)) & 1u)) ? offB + 256u * (uint32_t)(NVB > 0 ? NVB - 1 : 0) : offS;
+    // this thread's slot of the per-lane scratch: gl[k * 32] = dout of chunk k of the current target
+    float4* gl = reinterpret_cast<float4*>(smem + P.lane_off) + (size_t)warp * NV * 32 + lane;
+    float2 nx[NV][2], dxa[NV][2], dat[NV][2];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-        gv[k] = dxa[k] = dat[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        xrv[k] = make_uint2(0u, 0u);
+        nx[k][0] = nx[k][1] = dxa[k][0] = dxa[k][1] = dat[k][0] = dat[k][1] = f2(0.f, 0.f);
     }
     float DA = 0.f, DB = 0.f, alA = 0.f, alB = 0.f;       // alA / alB: alpha of entry `lane` of the current target
     int slot0 = 0;
@@ -458,18 +510,35 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
             const int ir = meta.y;
             slot0 = meta.z;
             const float* g = dout + (int64_t)ir * ldo;
+            const float* o = head_out + (int64_t)ir * ld;
+            float2 dA2 = f2(0.f, 0.f), dB2 = f2(0.f, 0.f);
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
                 const bool isA = k < NVA;
-                const int kk = isA ? k : k - NVA;
-                xrv[k] = *reinterpret_cast<const uint2*>(row + BOFF(k));
-                gv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if ((vmask >> k) & 1u)
-                    gv[k] = __ldg(reinterpret_cast<const float4*>(g + (isA ? sa.out_off : sb.out_off) + 4 * (lane + 32 * kk)));
-                dxa[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                const int u4 = 4 * (lane + 32 * (isA ? k : k - NVA));
+                const float4 f = bf4(*reinterpret_cast<const uint2*>(row + ROFF(k)));
+                nx[k][0] = f2(f.x == 0.f ? -0.f : f.x, f.y == 0.f ? -0.f : f.y);
+                nx[k][1] = f2(f.z == 0.f ? -0.f : f.z, f.w == 0.f ? -0.f : f.w);
+                float4 gg = make_float4(0.f, 0.f, 0.f, 0.f), oo = make_float4(0.f, 0.f, 0.f, 0.f);
+                if ((vmask >> k) & 1u) {
+                    gg = __ldg(reinterpret_cast<const float4*>(g + (isA ? sa.out_off : sb.out_off) + u4));
+                    oo = __ldg(reinterpret_cast<const float4*>(o + (isA ? sa.off : sb.off) + u4));
+                }
+                gl[k * 32] = gg;
+                dxa[k][0] = dxa[k][1] = f2(0.f, 0.f);
+                if (isA) {
+                    dA2 = __ffma2_rn(f2(gg.x, gg.y), f2(oo.x, oo.y), dA2);
+                    dA2 = __ffma2_rn(f2(gg.z, gg.w), f2(oo.z, oo.w), dA2);
+                } else {
+                    dB2 = __ffma2_rn(f2(gg.x, gg.y), f2(oo.x, oo.y), dB2);
+                    dB2 = __ffma2_rn(f2(gg.z, gg.w), f2(oo.z, oo.w), dB2);
+                }
             }
-            DA = __ldg(Dbuf + (int64_t)ir * P.NCH + sa.ch);
-            DB = (sb.C4 > 0) ? __ldg(Dbuf + (int64_t)ir * P.NCH + sb.ch) : 0.f;
+            DA = dA2.x + dA2.y;
+            DB = dB2.x + dB2.y;
+            if (NVB > 0) warp_sum2(DA, DB, lane); else DA = warp_sum(DA);
+            DA *= invH;
+            DB *= invH;
             alA = alB = 0.f;
             if (lane < meta.w) {
                 alA = __ldg(alpha + (int64_t)(slot0 + lane) * P.NCH + sa.ch);
@@ -479,46 +548,62 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
             if (lane == 0) mbar_arrive(&R.empty[stage]);
         } else {
             // sweep 1: d alpha = <g, x_l[j, head]> / H
-            float pA = 0.f, pB = 0.f;
+            float2 pa0 = f2(0.f, 0.f), pa1 = f2(0.f, 0.f), pb0 = f2(0.f, 0.f);
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                const float4 f = bf4(*reinterpret_cast<const uint2*>(row + BOFF(k)));
-                const float s = fmaf(f.x, gv[k].x, fmaf(f.y, gv[k].y, fmaf(f.z, gv[k].z, f.w * gv[k].w)));
-                if (k < NVA) pA += s; else pB += s;
+                const uint2 raw = *reinterpret_cast<const uint2*>(row + ROFF(k));
+                const float4 g4 = gl[k * 32];
+                if (k < NVA) {
+                    pa0 = __ffma2_rn(bf2lo(raw), f2(g4.x, g4.y), pa0);
+                    pa1 = __ffma2_rn(bf2hi(raw), f2(g4.z, g4.w), pa1);
+                } else {
+                    pb0 = __ffma2_rn(bf2lo(raw), f2(g4.x, g4.y), pb0);
+                    pb0 = __ffma2_rn(bf2hi(raw), f2(g4.z, g4.w), pb0);
+                }
             }
-            pA = warp_sum(pA);
-            if (NVB > 0) pB = warp_sum(pB);
+            float pA = (pa0.x + pa0.y) + (pa1.x + pa1.y), pB = pb0.x + pb0.y;
+            if (NVB > 0) warp_sum2(pA, pB, lane); else pA = warp_sum(pA);
             const int slot = meta.z, t = meta.w;
-            float aA, aB = 0.f;
-            if (t < 32) {
-                aA = __shfl_sync(0xffffffffu, alA, t);
-                aB = __shfl_sync(0xffffffffu, alB, t);
-            } else {
-                aA = __ldg(alpha + (int64_t)slot * P.NCH + sa.ch);
-                if (sb.C4 > 0) aB = __ldg(alpha + (int64_t)slot * P.NCH + sb.ch);
-            }
-            const float dsA = aA * (pA * invH - DA);
-            const float dsB = aB * (pB * invH - DB);
+            const bool far = t >= 32;                       // entries past the 32 held in alA / alB: read them
+            const float* al = alpha + (int64_t)slot * P.NCH;
+            const float fA = far ? __ldg(al + sa.ch) : 0.f;
+            const float fB = (far && sb.C4 > 0) ? __ldg(al + sb.ch) : 0.f;
+            const float sA = __shfl_sync(0xffffffffu, alA, t & 31), sB = __shfl_sync(0xffffffffu, alB, t & 31);
+            const float aA = far ? fA : sA, aB = far ? fB : sB;
+            const float dsA = aA * fmaf(pA, invH, -DA);
+            const float dsB = aB * fmaf(pB, invH, -DB);
             if (lane == 0) {
                 ds[(int64_t)slot * P.NCH + sa.ch] = dsA;
                 if (sb.C4 > 0) ds[(int64_t)slot * P.NCH + sb.ch] = dsB;
             }
             // sweep 2: d x_r, d att and the LeakyReLU sign bits of this edge
-            const float dsAs = dsA * slope, dsBs = dsB * slope;
+            const float2 EA = f2(dsA * c1, dsA * c1), EB = f2(dsB * c1, dsB * c1);
+            const uint32_t qA = __float_as_uint(dsA * c2), qB = __float_as_uint(dsB * c2);
             uint32_t w0 = 0u, w1 = 0u;
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
-                {
-                    const float4 f = bf4(*reinterpret_cast<const uint2*>(row + BOFF(k))), x = bf4(xrv[k]);
-                    const float d1 = k < NVA ? dsA : dsB, d0 = k < NVA ? dsAs : dsBs;
-                    uint32_t bits = 0u;
-                    float v, tt;
-                    v = f.x + x.x; tt = v > 0.f ? d1 : d0; bits |= v > 0.f ? 1u : 0u; dxa[k].x += tt; dat[k].x += tt * v;
-                    v = f.y + x.y; tt = v > 0.f ? d1 : d0; bits |= v > 0.f ? 2u : 0u; dxa[k].y += tt; dat[k].y += tt * v;
-                    v = f.z + x.z; tt = v > 0.f ? d1 : d0; bits |= v > 0.f ? 4u : 0u; dxa[k].z += tt; dat[k].z += tt * v;
-                    v = f.w + x.w; tt = v > 0.f ? d1 : d0; bits |= v > 0.f ? 8u : 0u; dxa[k].w += tt; dat[k].w += tt * v;
-                    if (k < 8) w0 |= bits << (4 * (k & 7)); else w1 |= bits << (4 * (k & 7));
+                const uint2 raw = *reinterpret_cast<const uint2*>(row + ROFF(k));
+                // round-down add: an exact zero comes out as -0 (x_r is never +0), so the sign bit is "v <= 0"
+                const float2 v0 = __fadd2_rd(bf2lo(raw), nx[k][0]), v1 = __fadd2_rd(bf2hi(raw), nx[k][1]);
+                const uint32_t b0 = __float_as_uint(v0.x), b1 = __float_as_uint(v0.y);
+                const uint32_t b2 = __float_as_uint(v1.x), b3 = __float_as_uint(v1.y);
+                if (k < 8) {
+                    w0 = __funnelshift_l(b0, w0, 1); w0 = __funnelshift_l(b1, w0, 1);
+                    w0 = __funnelshift_l(b2, w0, 1); w0 = __funnelshift_l(b3, w0, 1);
+                } else {
+                    w1 = __funnelshift_l(b0, w1, 1); w1 = __funnelshift_l(b1, w1, 1);
+                    w1 = __funnelshift_l(b2, w1, 1); w1 = __funnelshift_l(b3, w1, 1);
                 }
+                const uint32_t q = k < NVA ? qA : qB;
+                const float2 E = k < NVA ? EA : EB;
+                const float2 tt0 = __fadd2_rn(E, f2(__uint_as_float(q ^ (b0 & 0x80000000u)),
+                                                     __uint_as_float(q ^ (b1 & 0x80000000u))));
+                const float2 tt1 = __fadd2_rn(E, f2(__uint_as_float(q ^ (b2 & 0x80000000u)),
+                                                     __uint_as_float(q ^ (b3 & 0x80000000u))));
+                dxa[k][0] = __fadd2_rn(dxa[k][0], tt0);
+                dxa[k][1] = __fadd2_rn(dxa[k][1], tt1);
+                dat[k][0] = __ffma2_rn(tt0, v0, dat[k][0]);
+                dat[k][1] = __ffma2_rn(tt1, v1, dat[k][1]);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&R.empty[stage]);
@@ -534,8 +619,8 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
                         const bool isA = k < NVA;
                         const int e = (isA ? sa.off : sb.off) + 4 * (lane + 32 * (isA ? k : k - NVA));
                         const float4 a = __ldg(reinterpret_cast<const float4*>(att + e));
-                        *reinterpret_cast<uint2*>(drow + e) =
-                            pack_bf4(make_float4(a.x * dxa[k].x, a.y * dxa[k].y, a.z * dxa[k].z, a.w * dxa[k].w));
+                        *reinterpret_cast<uint2*>(drow + e) = pack_bf4(make_float4(
+                            a.x * dxa[k][0].x, a.y * dxa[k][0].y, a.z * dxa[k][1].x, a.w * dxa[k][1].y));
                     }
                 }
                 if (--n_left == 0) break;
@@ -548,29 +633,113 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
         if ((vmask >> k) & 1u) {
             const bool isA = k < NVA;
             float* da = datt + (isA ? sa.off : sb.off) + 4 * (lane + 32 * (isA ? k : k - NVA));
-            atomicAdd(da, dat[k].x); atomicAdd(da + 1, dat[k].y); atomicAdd(da + 2, dat[k].z); atomicAdd(da + 3, dat[k].w);
+            atomicAdd(da, dat[k][0].x); atomicAdd(da + 1, dat[k][0].y);
+            atomicAdd(da + 2, dat[k][1].x); atomicAdd(da + 3, dat[k][1].y);
+        }
+    }
+}
+#undef ROFF
+
+// ---------------------------------------------------------------------------------- backward, per source
+// d x_l[j] = sum over the out edges (j -> i, slot) of  alpha / H * g_i  +  d score * att * (bit ? slope : 1), bit = "v <= 0".
+// Same warp <-> segment plan as the per-target kernel (the sign bits are stored per warp and lane: element n of the
+// first 32 of a lane sits at bit M0 - 1 - n of word 0, element 32 + n at bit M1 - 1 - n of word 1, M0 = 4 * min(NV, 8),
+// M1 = 4 * (NV - 8): the order one funnel shift per element leaves them in).
+//
+// Third version.  The first two read (dst, slot) -> (alpha, d score, sign bits, dout row) with dependent global loads
+// inside every warp: 6 long-scoreboard stall cycles per issued instruction, 140 us.  Now the same producer / ring
+// scheme as the per-target kernels: a producer warp walks the reverse CSR of the sources b, b + grid, ... (index data
+// of 32 sources fetched at a time, one lane each) and, per out edge, bulk-copies [dout row of the target | the sign
+// words of the slot | alpha row | d score row] into the next free stage; the 8 consumer warps only touch shared
+// memory and registers.  A source without out edges gets a stage that carries no data (its row is written as zeros).
+// Arithmetic: with E = ds * c1, q = ds * c2 the coefficient of att is E + (bit ? -q : q); sum_e E_e is one scalar per
+// head, sum_e (+-q_e) one packed add per element pair, both folded into the row when its last edge has arrived.
+constexpr int E_DATA = 1, E_LAST = 2;
+
+__device__ __forceinline__ void src_producer(const Ring& R, const RingPlan& P, const int32_t* __restrict__ rptr,
+                                             const int32_t* __restrict__ rdst, const int32_t* __restrict__ rslot,
+                                             const float* __restrict__ dout, int64_t ldo,
+                                             const float* __restrict__ alpha, const float* __restrict__ ds,
+                                             const uint32_t* __restrict__ mask, int n_src, int lane) {
+    const int G = (int)gridDim.x;
+    const uint32_t g_bytes = (uint32_t)P.out_width * 4u, a_bytes = (uint32_t)P.NCH * 4u;
+    const uint32_t m_bytes = RW_MAX * 256u;
+    uint32_t stage = 0, round = 0;
+    for (int64_t jb = blockIdx.x; jb < n_src; jb += 32 * (int64_t)G) {
+        const int64_t jl = jb + (int64_t)lane * G;
+        int p0 = 0, p1 = 0;
+        if (jl < n_src) { p0 = __ldg(rptr + jl); p1 = __ldg(rptr + jl + 1); }
+        int d0 = 0, d1 = 0, d2 = 0, d3 = 0, s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+        if (p0 < p1) { d0 = __ldg(rdst + p0); s0 = __ldg(rslot + p0); }
+        if (p0 + 1 < p1) { d1 = __ldg(rdst + p0 + 1); s1 = __ldg(rslot + p0 + 1); }
+        if (p0 + 2 < p1) { d2 = __ldg(rdst + p0 + 2); s2 = __ldg(rslot + p0 + 2); }
+        if (p0 + 3 < p1) { d3 = __ldg(rdst + p0 + 3); s3 = __ldg(rslot + p0 + 3); }
+        for (int l = 0; l < 32; ++l) {
+            const int64_t j = jb + (int64_t)l * G;
+            if (j >= n_src) break;
+            const int q0 = __shfl_sync(0xffffffffu, p0, l), q1 = __shfl_sync(0xffffffffu, p1, l);
+            const int e0 = __shfl_sync(0xffffffffu, d0, l), e1 = __shfl_sync(0xffffffffu, d1, l);
+            const int e2 = __shfl_sync(0xffffffffu, d2, l), e3 = __shfl_sync(0xffffffffu, d3, l);
+            const int t0 = __shfl_sync(0xffffffffu, s0, l), t1 = __shfl_sync(0xffffffffu, s1, l);
+            const int t2 = __shfl_sync(0xffffffffu, s2, l), t3 = __shfl_sync(0xffffffffu, s3, l);
+            if (q0 == q1) {                                              // no out edge: a stage without data
+                mbar_wait(&R.empty[stage], (round & 1) ^ 1);
+                if (lane == 0) {
+                    R.meta[stage] = make_int4(E_LAST, (int)j, 0, 0);
+                    mbar_arrive(&R.full[stage]);
+                }
+                if (++stage == (uint32_t)P.n_stages) { stage = 0; ++round; }
+                continue;
+            }
+            for (int p = q0; p < q1; ++p) {
+                const int q = p - q0;
+                int i, slot;
+                if (q < 4) {
+                    i = q == 0 ? e0 : (q == 1 ? e1 : (q == 2 ? e2 : e3));
+                    slot = q == 0 ? t0 : (q == 1 ? t1 : (q == 2 ? t2 : t3));
+                } else {
+                    i = __ldg(rdst + p);
+                    slot = __ldg(rslot + p);
+                }
+                mbar_wait(&R.empty[stage], (round & 1) ^ 1);
+                if (lane == 0) {
+                    R.meta[stage] = make_int4(E_DATA | (p + 1 == q1 ? E_LAST : 0), (int)j, 0, 0);
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    uint8_t* dst = R.base + (size_t)stage * P.stage_bytes;
+                    mbar_expect_tx(&R.full[stage], g_bytes + m_bytes + 2u * a_bytes);
+                    bulk_load(dst, dout + (int64_t)i * ldo, g_bytes, &R.full[stage]);
+                    bulk_load(dst + P.e_mask_off, mask + (int64_t)slot * RW_MAX * 64, m_bytes, &R.full[stage]);
+                    bulk_load(dst + P.e_al_off, alpha + (int64_t)slot * P.NCH, a_bytes, &R.full[stage]);
+                    bulk_load(dst + P.e_al_off + a_bytes, ds + (int64_t)slot * P.NCH, a_bytes, &R.full[stage]);
+                }
+                if (++stage == (uint32_t)P.n_stages) { stage = 0; ++round; }
+            }
         }
     }
 }
 
-#undef BOFF
-
-// ---------------------------------------------------------------------------------- backward, per source
-// d x_l[j] = sum over the out edges (j -> i, slot) of  alpha / H * g_i  +  d score * att * (bit ? 1 : slope).
-// Same warp <-> segment plan as the per-target kernel (the sign bits are stored per warp and lane).
 template <int NVA, int NVB>
-__global__ void __launch_bounds__(RW_MAX * 32, 1)
+__global__ void __launch_bounds__(RING_THREADS, 1)
 k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__ att,
                    const int32_t* __restrict__ rptr, const int32_t* __restrict__ rdst,
                    const int32_t* __restrict__ rslot, float slope, float invH, const float* __restrict__ dout,
                    int64_t ldo, const float* __restrict__ alpha, const float* __restrict__ ds,
                    const uint32_t* __restrict__ mask, __nv_bfloat16* __restrict__ dxl, int64_t ld, int n_src) {
-    // persistent CTAs striding over the sources: att stays in registers (it was re-read from L2 for every edge),
-    // the reverse-CSR range of the NEXT source is fetched while the current one is reduced
     constexpr int NV = NVA + NVB;
+    constexpr int TOP0 = 4 * (NV < 8 ? NV : 8) - 1, TOP1 = NV > 8 ? 4 * (NV - 8) - 1 : 0;
+    extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (warp >= P.n_warps) return;
+    int n_left = (n_src > (int)blockIdx.x) ? (n_src - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    if (n_left == 0) return;
+    const Ring R = ring_setup(P, smem);
+    if (warp >= RW_MAX) {                                     // producer warpgroup: warp 8 works, 9..11 only donate
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+        if (warp == RW_MAX) src_producer(R, P, rptr, rdst, rslot, dout, ldo, alpha, ds, mask, n_src, lane);
+        return;
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     const RingSeg sa = P.a[warp], sb = P.b[warp];
+    const float c1 = 0.5f * (1.0f + slope), c2 = 0.5f * (1.0f - slope);
     uint32_t vmask = 0;
     float4 attv[NV];
 #pragma unroll
@@ -583,53 +752,69 @@ k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__
             attv[k] = __ldg(reinterpret_cast<const float4*>(att + (isA ? sa.off : sb.off) + 4 * u));
         }
     }
-    int j = blockIdx.x;
-    int p0 = 0, p1 = 0;
-    if (j < n_src) { p0 = __ldg(rptr + j); p1 = __ldg(rptr + j + 1); }
-    for (; j < n_src; j += (int)gridDim.x) {
-        const int jn = j + (int)gridDim.x;
-        int np0 = 0, np1 = 0;
-        if (jn < n_src) { np0 = __ldg(rptr + jn); np1 = __ldg(rptr + jn + 1); }
-        float4 acc[NV];
+    // lanes past the end of a segment read on into the stage (the dout row is followed by 2 KB of sign words): what
+    // they accumulate is never written
+    const uint32_t gA = (uint32_t)(sa.out_off + 4 * lane) * 4u, gB = (uint32_t)(sb.out_off + 4 * lane) * 4u;
+    float2 acc[NV][2], T[NV][2];
 #pragma unroll
-        for (int k = 0; k < NV; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int p = p0; p < p1; ++p) {
-            const int i = __ldg(rdst + p), slot = __ldg(rslot + p);
-            const float* al = alpha + (int64_t)slot * P.NCH;
-            const float* dsl = ds + (int64_t)slot * P.NCH;
-            const float aA = __ldg(al + sa.ch) * invH, dA = __ldg(dsl + sa.ch);
-            const float aB = (sb.C4 > 0) ? __ldg(al + sb.ch) * invH : 0.f, dB = (sb.C4 > 0) ? __ldg(dsl + sb.ch) : 0.f;
-            const uint32_t* mrow = mask + ((int64_t)slot * RW_MAX + warp) * 64;
-            const uint32_t w0 = __ldg(mrow + lane);
-            const uint32_t w1 = (NV > 8) ? __ldg(mrow + 32 + lane) : 0u;
-            const float* g = dout + (int64_t)i * ldo;
-            const float dAs = dA * slope, dBs = dB * slope;
+    for (int k = 0; k < NV; ++k) acc[k][0] = acc[k][1] = T[k][0] = T[k][1] = f2(0.f, 0.f);
+    float SEA = 0.f, SEB = 0.f;
+    uint32_t stage = 0, round = 0;
+    while (true) {
+        mbar_wait(&R.full[stage], round & 1);
+        const uint8_t* st = R.base + (size_t)stage * P.stage_bytes;
+        const int4 meta = R.meta[stage];
+        if (meta.x & E_DATA) {
+            const float* al = reinterpret_cast<const float*>(st + P.e_al_off);
+            const float* dsv = al + P.NCH;
+            const uint32_t* mw = reinterpret_cast<const uint32_t*>(st + P.e_mask_off) + warp * 64 + lane;
+            const float aA = al[sa.ch] * invH, dA = dsv[sa.ch];
+            const float aB = (NVB > 0) ? al[sb.ch] * invH : 0.f, dB = (NVB > 0) ? dsv[sb.ch] : 0.f;
+            const uint32_t w0 = mw[0];
+            const uint32_t w1 = (NV > 8) ? mw[32] : 0u;
+            SEA = fmaf(dA, c1, SEA);
+            SEB = fmaf(dB, c1, SEB);
+            const uint32_t qA = __float_as_uint(dA * c2), qB = __float_as_uint(dB * c2);
+            const float2 awA = f2(aA, aA), awB = f2(aB, aB);
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
                 const bool isA = k < NVA;
-                const int u = lane + 32 * (isA ? k : k - NVA);
-                float4 gg = make_float4(0.f, 0.f, 0.f, 0.f);
-                if ((vmask >> k) & 1u)
-                    gg = __ldg(reinterpret_cast<const float4*>(g + (isA ? sa.out_off : sb.out_off) + 4 * u));
-                const float4 a = attv[k];
-                const uint32_t bits = ((k < 8) ? w0 : w1) >> (4 * (k & 7));
-                const float aw = isA ? aA : aB, d1 = isA ? dA : dB, d0 = isA ? dAs : dBs;
-                acc[k].x = fmaf(aw, gg.x, fmaf((bits & 1u) ? d1 : d0, a.x, acc[k].x));
-                acc[k].y = fmaf(aw, gg.y, fmaf((bits & 2u) ? d1 : d0, a.y, acc[k].y));
-                acc[k].z = fmaf(aw, gg.z, fmaf((bits & 4u) ? d1 : d0, a.z, acc[k].z));
-                acc[k].w = fmaf(aw, gg.w, fmaf((bits & 8u) ? d1 : d0, a.w, acc[k].w));
+                const float4 gg = *reinterpret_cast<const float4*>(st + (isA ? gA + 512u * (uint32_t)k
+                                                                            : gB + 512u * (uint32_t)(k - NVA)));
+                const uint32_t wv = (k < 8) ? w0 : w1;
+                const int top = ((k < 8) ? TOP0 : TOP1) - 4 * (k & 7);          // bit of element 0 of this chunk
+                const uint32_t q = isA ? qA : qB;
+                const float2 aw = isA ? awA : awB;
+                const float2 sq0 = f2(__uint_as_float(q ^ ((wv << (31 - top)) & 0x80000000u)),
+                                      __uint_as_float(q ^ ((wv << (32 - top)) & 0x80000000u)));
+                const float2 sq1 = f2(__uint_as_float(q ^ ((wv << (33 - top)) & 0x80000000u)),
+                                      __uint_as_float(q ^ ((wv << (34 - top)) & 0x80000000u)));
+                T[k][0] = __fadd2_rn(T[k][0], sq0);
+                T[k][1] = __fadd2_rn(T[k][1], sq1);
+                acc[k][0] = __ffma2_rn(aw, f2(gg.x, gg.y), acc[k][0]);
+                acc[k][1] = __ffma2_rn(aw, f2(gg.z, gg.w), acc[k][1]);
             }
         }
-        __nv_bfloat16* drow = dxl + (int64_t)j * ld;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&R.empty[stage]);
+        if (meta.x & E_LAST) {
+            __nv_bfloat16* drow = dxl + (int64_t)meta.y * ld;
+            __nv_bfloat16* dA = drow + sa.off + 4 * lane;
+            __nv_bfloat16* dB = drow + sb.off + 4 * lane;
+            const float2 seA = f2(SEA, SEA), seB = f2(SEB, SEB);
 #pragma unroll
-        for (int k = 0; k < NV; ++k) {
-            if ((vmask >> k) & 1u) {
+            for (int k = 0; k < NV; ++k) {
                 const bool isA = k < NVA;
-                const int e = (isA ? sa.off : sb.off) + 4 * (lane + 32 * (isA ? k : k - NVA));
-                *reinterpret_cast<uint2*>(drow + e) = pack_bf4(acc[k]);
+                const float2 o0 = __ffma2_rn(f2(attv[k].x, attv[k].y), __fadd2_rn(T[k][0], isA ? seA : seB), acc[k][0]);
+                const float2 o1 = __ffma2_rn(f2(attv[k].z, attv[k].w), __fadd2_rn(T[k][1], isA ? seA : seB), acc[k][1]);
+                const uint2 pk = pack_bf4(make_float4(o0.x, o0.y, o1.x, o1.y));
+                if ((vmask >> k) & 1u) *reinterpret_cast<uint2*>(isA ? dA + 128 * k : dB + 128 * (k - NVA)) = pk;
+                acc[k][0] = acc[k][1] = T[k][0] = T[k][1] = f2(0.f, 0.f);
             }
+            SEA = SEB = 0.f;
+            if (--n_left == 0) break;
         }
-        p0 = np0; p1 = np1;
+        if (++stage == (uint32_t)P.n_stages) { stage = 0; ++round; }
     }
 }
 
@@ -680,7 +865,8 @@ bool ring_plan(const int32_t* seg_host, int n_conv, int H, int64_t ld, int max_d
     P.row_bytes = NL * 2;
     P.stage_bytes = (P.row_bytes + 127) / 128 * 128;
     P.sc_stride = fwd ? ((2 * P.max_deg1 * 4 + 15) / 16 * 16) : 0;
-    const int fixed = P.sc_stride * P.n_warps + 256;
+    const int lane_bytes = RW_MAX * (cfg.nva + cfg.nvb) * 512;
+    const int fixed = P.sc_stride * P.n_warps + lane_bytes + 512;
     const int per_stage = P.stage_bytes + 16 + 16;          // data + meta + full / empty barriers
     const int ns = (SMEM_MAX - fixed) / per_stage;
     if (ns < 3) return false;
@@ -688,7 +874,13 @@ bool ring_plan(const int32_t* seg_host, int n_conv, int H, int64_t ld, int max_d
     P.meta_off = P.n_stages * P.stage_bytes;
     P.bar_off = P.meta_off + P.n_stages * 16;
     P.sc_off = (P.bar_off + P.n_stages * 16 + 127) / 128 * 128;
-    cfg.smem = (size_t)P.sc_off + (size_t)P.sc_stride * P.n_warps;
+    P.lane_off = (P.sc_off + P.sc_stride * P.n_warps + 127) / 128 * 128;
+    cfg.smem = (size_t)P.lane_off + (size_t)lane_bytes;
+    P.full = (P.n_warps == RW_MAX) ? 1 : 0;
+    for (int w = 0; w < P.n_warps && P.full; ++w) {
+        if ((P.a[w].C4 + 31) / 32 != cfg.nva) P.full = 0;
+        if (cfg.nvb > 0 && (P.b[w].C4 + 31) / 32 != cfg.nvb) P.full = 0;
+    }
     return cfg.smem <= (size_t)SMEM_MAX;
 }
 
@@ -730,21 +922,27 @@ int gat_ring_fwd(const void* xl, const void* xr, int64_t ld, const float* att, c
     const RingPlan& P = cfg.P;
     cudaStream_t s = (cudaStream_t)stream;
     const int grid = n_dst < nc_num_sms() ? n_dst : nc_num_sms();
+#define CALL_F(A, B, F)                                                                                              \
+    do {                                                                                                             \
+        if (!ring_set_smem<(A) * 32 + (B) * 2 + (F)>(k_gat_ring_fwd<A, B, F != 0>)) return 1;                        \
+        k_gat_ring_fwd<A, B, F != 0><<<grid, RING_THREADS, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,             \
+            (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, dst_off, slope, head_ws, alpha);                  \
+    } while (0)
 #define CALL(A, B)                                                                                                   \
     do {                                                                                                             \
-        if (!ring_set_smem<(A) * 16 + (B)>(k_gat_ring_fwd<A, B>)) return 1;                                                          \
-        k_gat_ring_fwd<A, B><<<grid, RING_THREADS, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
-            (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, dst_off, slope, head_ws, alpha);                  \
+        if (P.full) CALL_F(A, B, 1); else CALL_F(A, B, 0);                                                           \
     } while (0)
     RING_DISPATCH(cfg, CALL);
 #undef CALL
+#undef CALL_F
     k_gat_head_mean<<<n_dst, 256, 0, s>>>(head_ws, ld, seg, n_conv, H, bias, out, ldo);
     nc_count_launch(2);
     NC_CHECK_LAUNCH("nc_gatv2_fwd (ring)");
     return NC_OK;
 }
 
-// bwd_ws: n_slots * RW_MAX * 256 bytes of sign bits, then n_dst * n_conv * H floats (D).
+// bwd_ws: n_slots * RW_MAX * 256 bytes of sign bits (+ n_dst * n_conv * H floats that the first ring version kept
+// D in; the size stays so that callers' workspaces do not change).
 int64_t gat_ring_bwd_ws_bytes(int64_t n_slots, int64_t n_dst, int n_conv, int H) {
     return n_slots * RW_MAX * 256 + (n_dst * n_conv * H * 4 + 255) / 256 * 256;
 }
@@ -764,26 +962,40 @@ int gat_ring_bwd(const void* xl, const void* xr, int64_t ld, const float* att, c
     const RingPlan& P = cfg.P;
     cudaStream_t s = (cudaStream_t)stream;
     uint32_t* mask = (uint32_t*)bwd_ws;
-    float* Dbuf = (float*)((uint8_t*)bwd_ws + n_slots * RW_MAX * 256);
     const float invH = 1.0f / (float)H;
-    k_gat_D<<<n_dst, 256, 0, s>>>(head_ws, ld, dout, ldo, seg, n_conv, H, Dbuf);
     const int grid = n_dst < nc_num_sms() ? n_dst : nc_num_sms();
+    // per-source kernel: its own ring, one stage per out edge = [dout row | sign words | alpha row | d score row]
+    RingPlan P2 = P;
+    P2.e_mask_off = (P.out_width * 4 + 127) / 128 * 128;
+    P2.e_al_off = P2.e_mask_off + RW_MAX * 256;
+    P2.stage_bytes = (P2.e_al_off + 2 * P.NCH * 4 + 127) / 128 * 128;
+    const int tail = 512 * (cfg.nva > cfg.nvb ? cfg.nva : cfg.nvb) + 512;   // lanes past a segment's end read on
+    int ns2 = (SMEM_MAX - 1024 - tail) / (P2.stage_bytes + 32);
+    ns2 = ns2 > RS_MAX ? RS_MAX : ns2;
+    if (ns2 < 3 || P.NCH % 4 != 0 || (uintptr_t)alpha % 16 || (uintptr_t)ds_ws % 16) return 1;
+    P2.n_stages = ns2;
+    P2.meta_off = ns2 * P2.stage_bytes;
+    P2.bar_off = P2.meta_off + ns2 * 16;
+    const size_t src_smem = (size_t)P2.bar_off + (size_t)ns2 * 16 + (size_t)tail;
+#define CALL_F(A, B, F)                                                                                              \
+    do {                                                                                                             \
+        if (!ring_set_smem<1024 + (A) * 32 + (B) * 2 + (F)>(k_gat_ring_bwd<A, B, F != 0>)) return 1;                 \
+        k_gat_ring_bwd<A, B, F != 0><<<grid, RING_THREADS, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,             \
+            (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, slope, invH, dout, ldo, alpha, head_ws, ds_ws,    \
+            (__nv_bfloat16*)dxr, datt, mask);                                                                        \
+    } while (0)
 #define CALL(A, B)                                                                                                   \
     do {                                                                                                             \
-        if (!ring_set_smem<1024 + (A) * 16 + (B)>(k_gat_ring_bwd<A, B>)) return 1;                                                          \
-        k_gat_ring_bwd<A, B><<<grid, RING_THREADS, cfg.smem, s>>>(P, (const __nv_bfloat16*)xl,                     \
-            (const __nv_bfloat16*)xr, ld, att, rowptr, col, n_dst, slope, invH, dout, ldo, alpha, Dbuf, ds_ws,       \
-            (__nv_bfloat16*)dxr, datt, mask);                                                                        \
-        int occ_ = 1;                                                                                                \
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_, k_gat_ring_bwd_src<A, B>, P.n_warps * 32, 0) !=     \
-            cudaSuccess || occ_ < 1) { cudaGetLastError(); occ_ = 1; }                                               \
-        const int gsrc_ = n_src < occ_ * nc_num_sms() ? n_src : occ_ * nc_num_sms();   /* one resident wave */      \
-        k_gat_ring_bwd_src<A, B><<<gsrc_, P.n_warps * 32, 0, s>>>(                                                   \
-            P, att, rptr, rdst, rslot, slope, invH, dout, ldo, alpha, ds_ws, mask, (__nv_bfloat16*)dxl, ld, n_src);  \
+        if (!ring_set_smem<2048 + (A) * 32 + (B) * 2>(k_gat_ring_bwd_src<A, B>)) return 1;                           \
+        if (P.full) CALL_F(A, B, 1); else CALL_F(A, B, 0);                                                           \
+        const int gsrc_ = n_src < nc_num_sms() ? n_src : nc_num_sms();                                               \
+        k_gat_ring_bwd_src<A, B><<<gsrc_, RING_THREADS, src_smem, s>>>(                                              \
+            P2, att, rptr, rdst, rslot, slope, invH, dout, ldo, alpha, ds_ws, mask, (__nv_bfloat16*)dxl, ld, n_src); \
     } while (0)
     RING_DISPATCH(cfg, CALL);
 #undef CALL
-    nc_count_launch(3);
+#undef CALL_F
+    nc_count_launch(2);
     NC_CHECK_LAUNCH("nc_gatv2_bwd (ring)");
     if (dbias) {
         int rc = nc_col_sum(dout, NC_F32, ldo, n_dst, P.out_width, dbias, stream);
