@@ -149,10 +149,23 @@ __device__ __forceinline__ void cur_init(Cursor& c, const int32_t* rowptr, const
 
 // Producer warp: starts the copy of the next row of the sequence into stage `ps` (all lanes call; lane 0 issues).
 // Returns false when the sequence is exhausted.
+// What the consumers of the per-target backward read from global memory when a target's x_r row arrives: its dout
+// row, its per-head forward outputs and its alpha rows.  The producer asks for them in L2 (one bulk prefetch each)
+// when it issues the x_r row, several rows before the consumers get there.
+struct TargetPrefetch {
+    const float* g; int64_t ldg_; uint32_t g_bytes;
+    const float* o; int64_t ldo_; uint32_t o_bytes;
+    const float* alpha; uint32_t a_row_bytes;
+};
+__device__ __forceinline__ void l2_prefetch(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 __device__ __forceinline__ bool issue_next(Cursor& c, const Ring& R, const RingPlan& P, uint32_t ps,
                                            const __nv_bfloat16* __restrict__ xl, const __nv_bfloat16* __restrict__ xr,
                                            int64_t ld, const int32_t* __restrict__ rowptr,
-                                           const int32_t* __restrict__ col, int n_dst, int dst_off, int lane) {
+                                           const int32_t* __restrict__ col, int n_dst, int dst_off, int lane,
+                                           const TargetPrefetch* pf) {
     const __nv_bfloat16* src;
     int4 meta;
     while (true) {
@@ -162,6 +175,11 @@ __device__ __forceinline__ bool issue_next(Cursor& c, const Ring& R, const RingP
             src = xr + (int64_t)c.ir * ld;
             meta = make_int4(K_XR, c.ir, c.e0 + i, deg + 1);
             c.t = 0;
+            if (pf != nullptr && lane == 0) {
+                l2_prefetch(pf->g + (int64_t)c.ir * pf->ldg_, pf->g_bytes);
+                l2_prefetch(pf->o + (int64_t)c.ir * pf->ldo_, pf->o_bytes);
+                l2_prefetch(pf->alpha + (int64_t)(c.e0 + i) * (pf->a_row_bytes / 4u), (uint32_t)(deg + 1) * pf->a_row_bytes);
+            }
             break;
         }
         if (c.t < deg) {
@@ -218,13 +236,13 @@ __device__ __forceinline__ Ring ring_setup(const RingPlan& P, uint8_t* smem) {
 __device__ __forceinline__ void producer_loop(const Ring& R, const RingPlan& P, const __nv_bfloat16* __restrict__ xl,
                                               const __nv_bfloat16* __restrict__ xr, int64_t ld,
                                               const int32_t* __restrict__ rowptr, const int32_t* __restrict__ col,
-                                              int n_dst, int dst_off, int lane) {
+                                              int n_dst, int dst_off, int lane, const TargetPrefetch* pf = nullptr) {
     Cursor cur;
     cur_init(cur, rowptr, col, n_dst, dst_off, lane);
     uint32_t stage = 0, round = 0;
     while (true) {
         mbar_wait(&R.empty[stage], (round & 1) ^ 1);                 // passes at once in the first round
-        if (!issue_next(cur, R, P, stage, xl, xr, ld, rowptr, col, n_dst, dst_off, lane)) break;
+        if (!issue_next(cur, R, P, stage, xl, xr, ld, rowptr, col, n_dst, dst_off, lane, pf)) break;
         if (++stage == (uint32_t)P.n_stages) { stage = 0; ++round; }
     }
 }
@@ -476,7 +494,13 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
     const Ring R = ring_setup(P, smem);
     if (warp >= RW_MAX) {                                     // producer warpgroup: warp 8 works, 9..11 only donate
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-        if (warp == RW_MAX) producer_loop(R, P, xl, xr, ld, rowptr, col, n_dst, 0, lane);
+        if (warp == RW_MAX) {
+            TargetPrefetch pf;
+            pf.g = dout; pf.ldg_ = ldo; pf.g_bytes = (uint32_t)P.out_width * 4u;
+            pf.o = head_out; pf.ldo_ = ld; pf.o_bytes = (uint32_t)P.NL * 4u;
+            pf.alpha = alpha; pf.a_row_bytes = (uint32_t)P.NCH * 4u;
+            producer_loop(R, P, xl, xr, ld, rowptr, col, n_dst, 0, lane, (P.NCH % 4 == 0) ? &pf : nullptr);
+        }
         return;
     }
     asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
@@ -611,17 +635,26 @@ k_gat_ring_bwd(const __grid_constant__ RingPlan P, const __nv_bfloat16* __restri
             mrow[lane] = w0;
             if (NV > 8) mrow[32 + lane] = w1;
             if (meta.x & K_LAST) {
+                // d x_r = att * sum tt: all att chunks are requested before the first one is used (one L2 latency per
+                // target, not one per chunk); the two offsets are kept opaque so that they stay in registers
                 const int ir = meta.y;
-                __nv_bfloat16* drow = dxr + (int64_t)ir * ld;
+                int oA = sa.off + 4 * lane, oB = sb.off + 4 * lane;
+                asm volatile("" : "+r"(oA), "+r"(oB));
+                __nv_bfloat16* dA = dxr + (int64_t)ir * ld + oA;
+                __nv_bfloat16* dB = dxr + (int64_t)ir * ld + oB;
+                const float* tA = att + oA;
+                const float* tB = att + oB;
+                float4 av[NV];
 #pragma unroll
                 for (int k = 0; k < NV; ++k) {
-                    if ((vmask >> k) & 1u) {
-                        const bool isA = k < NVA;
-                        const int e = (isA ? sa.off : sb.off) + 4 * (lane + 32 * (isA ? k : k - NVA));
-                        const float4 a = __ldg(reinterpret_cast<const float4*>(att + e));
-                        *reinterpret_cast<uint2*>(drow + e) = pack_bf4(make_float4(
-                            a.x * dxa[k][0].x, a.y * dxa[k][0].y, a.z * dxa[k][1].x, a.w * dxa[k][1].y));
-                    }
+                    const float* tp = ((vmask >> k) & 1u) ? (k < NVA ? tA + 128 * k : tB + 128 * (k - NVA)) : att;
+                    av[k] = __ldg(reinterpret_cast<const float4*>(tp));
+                }
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+                    const uint2 pk = pack_bf4(make_float4(av[k].x * dxa[k][0].x, av[k].y * dxa[k][0].y,
+                                                          av[k].z * dxa[k][1].x, av[k].w * dxa[k][1].y));
+                    if ((vmask >> k) & 1u) *reinterpret_cast<uint2*>(k < NVA ? dA + 128 * k : dB + 128 * (k - NVA)) = pk;
                 }
                 if (--n_left == 0) break;
             }
@@ -718,6 +751,42 @@ __device__ __forceinline__ void src_producer(const Ring& R, const RingPlan& P, c
     }
 }
 
+// One out edge of the current source: acc += alpha / H * g, T += (bit ? -q : q).  FIRST: the source's first edge
+// initialises the two accumulators instead (no zeroing of 104 registers per source).
+template <int NVA, int NVB, bool FIRST>
+__device__ __forceinline__ void src_edge(const uint8_t* st, uint32_t gA, uint32_t gB, uint32_t w0, uint32_t w1,
+                                         uint32_t qA, uint32_t qB, float aA, float aB,
+                                         float2 (&acc)[NVA + NVB][2], float2 (&T)[NVA + NVB][2]) {
+    constexpr int NV = NVA + NVB;
+    constexpr int TOP0 = 4 * (NV < 8 ? NV : 8) - 1, TOP1 = NV > 8 ? 4 * (NV - 8) - 1 : 0;
+    const float2 awA = f2(aA, aA), awB = f2(aB, aB);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const bool isA = k < NVA;
+        const float4 gg = *reinterpret_cast<const float4*>(st + (isA ? gA + 512u * (uint32_t)k
+                                                                    : gB + 512u * (uint32_t)(k - NVA)));
+        const uint32_t wv = (k < 8) ? w0 : w1;
+        const int top = ((k < 8) ? TOP0 : TOP1) - 4 * (k & 7);          // bit of element 0 of this chunk
+        const uint32_t q = isA ? qA : qB;
+        const float2 aw = isA ? awA : awB;
+        const float2 sq0 = f2(__uint_as_float(q ^ ((wv << (31 - top)) & 0x80000000u)),
+                              __uint_as_float(q ^ ((wv << (32 - top)) & 0x80000000u)));
+        const float2 sq1 = f2(__uint_as_float(q ^ ((wv << (33 - top)) & 0x80000000u)),
+                              __uint_as_float(q ^ ((wv << (34 - top)) & 0x80000000u)));
+        if (FIRST) {
+            T[k][0] = sq0;
+            T[k][1] = sq1;
+            acc[k][0] = __fmul2_rn(aw, f2(gg.x, gg.y));
+            acc[k][1] = __fmul2_rn(aw, f2(gg.z, gg.w));
+        } else {
+            T[k][0] = __fadd2_rn(T[k][0], sq0);
+            T[k][1] = __fadd2_rn(T[k][1], sq1);
+            acc[k][0] = __ffma2_rn(aw, f2(gg.x, gg.y), acc[k][0]);
+            acc[k][1] = __ffma2_rn(aw, f2(gg.z, gg.w), acc[k][1]);
+        }
+    }
+}
+
 template <int NVA, int NVB>
 __global__ void __launch_bounds__(RING_THREADS, 1)
 k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__ att,
@@ -726,7 +795,6 @@ k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__
                    int64_t ldo, const float* __restrict__ alpha, const float* __restrict__ ds,
                    const uint32_t* __restrict__ mask, __nv_bfloat16* __restrict__ dxl, int64_t ld, int n_src) {
     constexpr int NV = NVA + NVB;
-    constexpr int TOP0 = 4 * (NV < 8 ? NV : 8) - 1, TOP1 = NV > 8 ? 4 * (NV - 8) - 1 : 0;
     extern __shared__ __align__(128) uint8_t smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int n_left = (n_src > (int)blockIdx.x) ? (n_src - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
@@ -759,6 +827,7 @@ k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k][0] = acc[k][1] = T[k][0] = T[k][1] = f2(0.f, 0.f);
     float SEA = 0.f, SEB = 0.f;
+    bool first = true;                                       // the next edge is the first one of its source
     uint32_t stage = 0, round = 0;
     while (true) {
         mbar_wait(&R.full[stage], round & 1);
@@ -772,35 +841,29 @@ k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__
             const float aB = (NVB > 0) ? al[sb.ch] * invH : 0.f, dB = (NVB > 0) ? dsv[sb.ch] : 0.f;
             const uint32_t w0 = mw[0];
             const uint32_t w1 = (NV > 8) ? mw[32] : 0u;
-            SEA = fmaf(dA, c1, SEA);
-            SEB = fmaf(dB, c1, SEB);
             const uint32_t qA = __float_as_uint(dA * c2), qB = __float_as_uint(dB * c2);
-            const float2 awA = f2(aA, aA), awB = f2(aB, aB);
-#pragma unroll
-            for (int k = 0; k < NV; ++k) {
-                const bool isA = k < NVA;
-                const float4 gg = *reinterpret_cast<const float4*>(st + (isA ? gA + 512u * (uint32_t)k
-                                                                            : gB + 512u * (uint32_t)(k - NVA)));
-                const uint32_t wv = (k < 8) ? w0 : w1;
-                const int top = ((k < 8) ? TOP0 : TOP1) - 4 * (k & 7);          // bit of element 0 of this chunk
-                const uint32_t q = isA ? qA : qB;
-                const float2 aw = isA ? awA : awB;
-                const float2 sq0 = f2(__uint_as_float(q ^ ((wv << (31 - top)) & 0x80000000u)),
-                                      __uint_as_float(q ^ ((wv << (32 - top)) & 0x80000000u)));
-                const float2 sq1 = f2(__uint_as_float(q ^ ((wv << (33 - top)) & 0x80000000u)),
-                                      __uint_as_float(q ^ ((wv << (34 - top)) & 0x80000000u)));
-                T[k][0] = __fadd2_rn(T[k][0], sq0);
-                T[k][1] = __fadd2_rn(T[k][1], sq1);
-                acc[k][0] = __ffma2_rn(aw, f2(gg.x, gg.y), acc[k][0]);
-                acc[k][1] = __ffma2_rn(aw, f2(gg.z, gg.w), acc[k][1]);
+            if (first) {
+                SEA = dA * c1;
+                SEB = dB * c1;
+                src_edge<NVA, NVB, true>(st, gA, gB, w0, w1, qA, qB, aA, aB, acc, T);
+            } else {
+                SEA = fmaf(dA, c1, SEA);
+                SEB = fmaf(dB, c1, SEB);
+                src_edge<NVA, NVB, false>(st, gA, gB, w0, w1, qA, qB, aA, aB, acc, T);
             }
+            first = false;
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&R.empty[stage]);
         if (meta.x & E_LAST) {
+            if (first) {                                     // a source without out edges: its row is zero
+#pragma unroll
+                for (int k = 0; k < NV; ++k) acc[k][0] = acc[k][1] = T[k][0] = T[k][1] = f2(0.f, 0.f);
+                SEA = SEB = 0.f;
+            }
             __nv_bfloat16* drow = dxl + (int64_t)meta.y * ld;
-            __nv_bfloat16* dA = drow + sa.off + 4 * lane;
-            __nv_bfloat16* dB = drow + sb.off + 4 * lane;
+            int oA = sa.off + 4 * lane, oB = sb.off + 4 * lane;
+            asm volatile("" : "+r"(oA), "+r"(oB));           // keep the two offsets in registers
             const float2 seA = f2(SEA, SEA), seB = f2(SEB, SEB);
 #pragma unroll
             for (int k = 0; k < NV; ++k) {
@@ -808,10 +871,9 @@ k_gat_ring_bwd_src(const __grid_constant__ RingPlan P, const float* __restrict__
                 const float2 o0 = __ffma2_rn(f2(attv[k].x, attv[k].y), __fadd2_rn(T[k][0], isA ? seA : seB), acc[k][0]);
                 const float2 o1 = __ffma2_rn(f2(attv[k].z, attv[k].w), __fadd2_rn(T[k][1], isA ? seA : seB), acc[k][1]);
                 const uint2 pk = pack_bf4(make_float4(o0.x, o0.y, o1.x, o1.y));
-                if ((vmask >> k) & 1u) *reinterpret_cast<uint2*>(isA ? dA + 128 * k : dB + 128 * (k - NVA)) = pk;
-                acc[k][0] = acc[k][1] = T[k][0] = T[k][1] = f2(0.f, 0.f);
+                if ((vmask >> k) & 1u) *reinterpret_cast<uint2*>(drow + (isA ? oA + 128 * k : oB + 128 * (k - NVA))) = pk;
             }
-            SEA = SEB = 0.f;
+            first = true;
             if (--n_left == 0) break;
         }
         if (++stage == (uint32_t)P.n_stages) { stage = 0; ++round; }
