@@ -154,6 +154,12 @@ k_adam(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m, floa
         const float4 gg = reinterpret_cast<const float4*>(g)[i];
         float4 mm = reinterpret_cast<float4*>(m)[i];
         float4 vv = reinterpret_cast<float4*>(v)[i];
+        // A chunk that has never seen a gradient (g = m = v = 0: the masked-out entries of the gene-program decoders,
+        // about a quarter of the arena at the 5 k-gene configuration) keeps its value exactly: update = 0 / (0 + eps).
+        // Nothing to write back, the bf16 shadow included.
+        if (wd == 0.f && gg.x == 0.f && gg.y == 0.f && gg.z == 0.f && gg.w == 0.f && mm.x == 0.f && mm.y == 0.f &&
+            mm.z == 0.f && mm.w == 0.f && vv.x == 0.f && vv.y == 0.f && vv.z == 0.f && vv.w == 0.f)
+            continue;
         pp.x = adam_elem(pp.x, gg.x, mm.x, vv.x, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
         pp.y = adam_elem(pp.y, gg.y, mm.y, vv.y, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);
         pp.z = adam_elem(pp.z, gg.z, mm.z, vv.z, lr_bc1, b1, b2, eps, wd, bc2_sqrt, clip);

@@ -251,7 +251,9 @@ class FlatAdam:
         self.step_count += 1
         self.sync_lr()
         if self.flat_bf16 is not None and not self.shadow_is_current():
-            self._shadow_versions = self._versions()       # the kernel below rewrites the whole shadow
+            # parameters were edited in place since the last step: the Adam kernel refreshes the shadow only where it
+            # changes a value (chunks that never saw a gradient are skipped), so bring all of it up to date first
+            self.refresh_shadow()
         if self.peer is not None:
             pr, b = self.peer, self.peer["bufs"]
             call("nc_dp_adam_step", b["p"].ptr_array, b["g"].ptr_array, b["sh"].ptr_array if "sh" in b else None,
