@@ -2,22 +2,21 @@
 // Same arithmetic as gatv2.cu (PyG GATv2Conv message passing, nn/encoders.py:124-140,197-207, SURVEY.md
 // App. A.1), different machine mapping -- built for HBM throughput:
 //
-//   * persistent CTAs, one per SM, 8 warps that never synchronise with each other.  Warp w owns one
-//     or two (conv, head) segments of the x_l / x_r rows (a long one and a short one: the plan below
-//     pairs them so that every warp touches the same number of bytes) for every target of its CTA;
-//   * each warp runs its own software pipeline: a private shared-memory ring of n_stages slots that
-//     holds ITS column slice of the next rows ([x_r slice | every neighbour's x_l slice | the self
-//     row's slice] per target), filled by cp.async.bulk + mbarrier; the warp refills a slot right
-//     after it has consumed it.  8 warps x 8 slots x 3.2 KB = 205 KB in flight per SM at C2 (before: 4
-//     rows of 12 KB behind a __syncthreads per neighbour);
+//   * persistent CTAs, one per SM: 8 consumer warps that never synchronise with each other, one producer warp and
+//     three warps that only hand their registers over (setmaxnreg).  Consumer warp w owns one or two (conv, head)
+//     segments of the x_l / x_r rows (a long one and a short one: the plan below pairs them so that every warp
+//     touches the same number of bytes) for every target of its CTA;
+//   * the producer warp copies whole rows ([x_r[i] | x_l[j] for every neighbour j | x_l[i]] per target) with one
+//     cp.async.bulk each into a shared-memory ring of full / empty mbarriers: 6 stages x 25.6 KB in flight per SM at
+//     the 1 M-cell configuration (round 1: 4 rows of 12 KB behind a __syncthreads per neighbour);
 //   * scores, online softmax and the alpha-weighted sum of a head live inside one warp (shuffles only);
 //   * forward writes the per-head outputs O (fp32) and the attention coefficients; the head mean
 //     + bias is a second, tiny kernel;
 //   * backward, per target: D_h = sum_t alpha_t dalpha_t = <g, O_h> / H is known BEFORE the
-//     neighbours stream in (k_gat_D), so d score, d x_r, d att and the LeakyReLU sign bits of every
-//     (edge, element) are produced in ONE pass over the rows; the per-source pass then needs only the
-//     sign bits (1 bit per element instead of re-reading x_l[j] + x_r[i]): d x_l[j] = sum over out
-//     edges of alpha/H * g_i + d score * att * (bit ? 1 : slope).
+//     neighbours stream in (computed when the target's x_r row arrives), so d score, d x_r, d att and the LeakyReLU
+//     sign bits of every (edge, element) are produced in ONE pass over the rows; the per-source pass then needs only
+//     the sign bits (1 bit per element instead of re-reading x_l[j] + x_r[i]): d x_l[j] = sum over out
+//     edges of alpha/H * g_i + d score * att * (bit ? slope : 1), and is fed by a producer ring of its own.
 //
 // Generic shapes (fp32 rows, widths that are not multiples of 4, more than 16 segments, very long
 // segments) stay on the kernels of gatv2.cu: gat_ring_* return 1 ("not applicable") for them.
