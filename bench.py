@@ -221,6 +221,7 @@ class KernelTimer:
         self.records = []          # (name, start_event, end_event, work, unit)
         self.nnz_row = store_nnz_per_row
         self._start = None
+        self._adam_untouched = {}  # exp_avg_sq pointer -> parameters in chunks the Adam kernel skips
 
     @staticmethod
     def _esize(code):
@@ -258,7 +259,15 @@ class KernelTimer:
         if name == "nc_adam_step":
             return a[4] * 28.0, "byte"
         if name == "nc_adam_step_dyn":              # p, g, m, v read; p, m, v, bf16 shadow written; g cleared
-            return a[4] * 34.0, "byte"
+            # 16-byte chunks whose g, m and v are all zero (masked-out decoder entries: they never see a gradient) are
+            # read (16 B per parameter) and left alone by the kernel: count them once, from the moment buffers
+            n, key = a[4], a[3].data_ptr()
+            if key not in self._adam_untouched:
+                n4 = (n // 4) * 4
+                idle = (a[3][:n4].view(-1, 4) == 0).all(1) & (a[2][:n4].view(-1, 4) == 0).all(1)
+                self._adam_untouched[key] = int(idle.sum().item()) * 4 if float(a[9]) == 0.0 else 0
+            u = self._adam_untouched[key]
+            return (n - u) * 34.0 + u * 16.0, "byte"
         if name == "nc_dp_adam_step":               # per rank: HBM + NVLink bytes of its shard (see csrc/dp_exchange.cu)
             n, w = a[6], a[8]
             return n * (4.0 + 20.0 / w + 10.0), "byte"

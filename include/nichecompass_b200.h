@@ -306,7 +306,10 @@ int nc_weight_reg_grad(const float* W, int64_t ld, int32_t F, int32_t P, float l
 /* Fused Adam over a flat parameter segment with torch.optim.Adam semantics
  * (train/trainer.py:339-342,418-421): optional clip_grad_value_ (clip_value > 0), optional
  * refresh of the bf16 shadow copy used by the tensor-core GEMMs; zero_grad != 0 clears g after
- * it has been consumed (optimizer.zero_grad() of the next iteration, train/trainer.py:414).   */
+ * it has been consumed (optimizer.zero_grad() of the next iteration, train/trainer.py:414).
+ * With weight_decay == 0 a 16-byte group of parameters whose g, m and v are all zero keeps its
+ * value bit for bit (torch's update is 0 / (0 + eps) there) and is not written back -- p_bf16
+ * must therefore already hold the cast of p when the first step is taken.                     */
 int nc_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1,
                  float beta2, float eps, float weight_decay, int32_t step, float clip_value,
                  void* p_bf16, int zero_grad, void* stream);
