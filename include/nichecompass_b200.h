@@ -195,9 +195,10 @@ int nc_gatv2_fwd_tile(const void* xl, const void* xr, int dtype, int64_t ld, con
  * head_ws: what nc_gatv2_fwd wrote (NULL: generic kernels).  bwd_ws / bwd_ws_bytes: scratch of
  * nc_gatv2_bwd_ws_bytes(n_slots, n_dst, n_conv, H) bytes, 256-byte aligned (LeakyReLU sign bits of
  * every (edge, element) + per-target softmax-backward constants); n_slots >= rowptr[n_dst] + n_dst.
- * With both given (and the shape conditions of nc_gatv2_fwd) the ring kernels run: one streaming
- * pass per target (d score, d x_r, d att, sign bits) and one pass per source that reads the sign
- * bits instead of x_l[j] + x_r[i].                                                            */
+ * With both given (and the shape conditions of nc_gatv2_fwd, n_conv * H a multiple of 4, alpha and
+ * ds_ws 16-byte aligned) the ring kernels run: one streaming pass per target (d score, d x_r,
+ * d att, sign bits) and one pass per source that reads the sign bits instead of
+ * x_l[j] + x_r[i]; otherwise the generic kernels.                                             */
 int nc_gatv2_bwd(const void* xl, const void* xr, int dtype, int64_t ld, const float* att,
                  const int32_t* rowptr, const int32_t* col, int32_t n_dst, int32_t n_src,
                  const int32_t* rptr, const int32_t* rdst, const int32_t* rslot,
