@@ -85,7 +85,7 @@ def test_noalloc_allocates_nothing_and_rejects_oversize():
     for _ in range(3):
         call("nc_gcn_norm_weights_noalloc", rowptr, col, 2000, 2000, 1, w, wself)
     torch.cuda.synchronize()
-    assert torch.cuda.mem_get_info()[0] == free0                                    # no cudaMalloc behind our back
+    assert torch.cuda.mem_get_info()[0] >= free0                                    # no cudaMalloc behind our back
     assert torch.cuda.memory_stats().get("allocation.all.allocated", 0) == n_alloc0  # nor through torch
     with pytest.raises(Exception, match="exceeds the static scratch"):
         call("nc_gcn_norm_weights_noalloc", rowptr, col, MAX_NODES + 1, 0, 1, w, wself)
